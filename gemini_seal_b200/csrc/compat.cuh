@@ -1,0 +1,37 @@
+// Build-mode shim.  The product is compiled by nvcc for sm_100a.  The same kernel sources can also
+// be compiled by g++ against tests/cusim/cusim.h (GSB_CUSIM), a TEST-ONLY fiber emulation of the
+// CUDA execution model used to debug kernel indexing on the GPU-less dev container.  The simulator
+// is never shipped, never loaded by the package, and is not a CPU fallback: gemini_seal_b200/_lib.py
+// only ever loads the nvcc-built library and raises if it is missing.
+#pragma once
+#include <cstddef>
+#include <cstdint>
+
+#ifdef GSB_CUSIM
+#include "cusim.h"
+#define GSB_LAUNCH(kfn, grid, block, smem, stream, ...) \
+    (++::gsb::launch_counter(), ::cusim::launch((grid), (block), (smem), [&]() { kfn(__VA_ARGS__); }))
+#else
+#include <cuda_runtime.h>
+#define GSB_LAUNCH(kfn, grid, block, smem, stream, ...) \
+    (++::gsb::launch_counter(), kfn<<<(grid), (block), (smem), (stream)>>>(__VA_ARGS__))
+#endif
+
+#define GSB_DEV __device__ __forceinline__
+
+namespace gsb
+{
+    // Kernel launches issued by this library in this process (gsb_launch_count()).
+    unsigned long long &launch_counter();
+
+    // Dynamic shared memory base (one extern array per translation unit).
+    GSB_DEV uint64_t *dyn_smem()
+    {
+#ifdef GSB_CUSIM
+        return reinterpret_cast<uint64_t *>(::cusim::dyn_smem_ptr());
+#else
+        extern __shared__ __align__(16) uint64_t gsb_dyn_smem[];
+        return gsb_dyn_smem;
+#endif
+    }
+} // namespace gsb

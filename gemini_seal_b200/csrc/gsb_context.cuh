@@ -1,0 +1,94 @@
+// Device context: immutable device copies of everything SEALContext::ContextData owns for the hot
+// path (per-modulus constants, NTT tables), uploaded switching keys, Galois permutation tables and
+// lazily built per-level key-switch / rescale constants.
+#pragma once
+#include "../../include/gseal_b200.h"
+#include "host_tables.h"
+#include "ntt_kernels.cuh"
+#include <map>
+#include <mutex>
+#include <string>
+#include <vector>
+
+namespace gsb
+{
+    struct ApiError
+    {
+        int code;
+        std::string msg;
+    };
+
+    void set_error(const std::string &msg);
+    unsigned long long &launch_counter();
+
+#define GSB_CUDA_CHECK(expr)                                                                       \
+    do                                                                                             \
+    {                                                                                              \
+        cudaError_t e__ = (expr);                                                                  \
+        if (e__ != cudaSuccess)                                                                    \
+            throw ::gsb::ApiError{ GSB_E_CUDA, std::string(#expr) + ": " + cudaGetErrorString(e__) }; \
+    } while (0)
+
+    inline void require(bool ok, int code, const char *msg)
+    {
+        if (!ok)
+            throw ApiError{ code, msg };
+    }
+
+    // Constants of the hybrid key switch at one ciphertext level L (multi_special_primes.cpp).
+    struct KsLevelConsts
+    {
+        // mod-up, bundle j with |S_j| > 1 (multi_special_primes.cpp:113-126):
+        //   a[j][i]      = (prod_{i' in S_j \ i} q_i')^-1 mod q_i   (+ Shoup)
+        //   b[j][i][kap] = prod_{i' in S_j \ i} q_i' mod q_kap
+        uint64_t *d_modup_a = nullptr;  // [beta][k][2]
+        uint64_t *d_modup_b = nullptr;  // [beta][k][L+k]
+        // mod-down (multi_special_primes.cpp:186-234, 292-299):
+        uint64_t *d_inv_hat = nullptr;  // [k][2]  (prod_{j'!=j} p_j')^-1 mod p_j (+ Shoup)
+        uint64_t *d_neg_hat = nullptr;  // [L][k]  -(prod_{j'!=j} p_j') mod q_i
+        uint64_t *d_inv_p = nullptr;    // [L][2]  (prod_j p_j)^-1 mod q_i (+ Shoup)
+        // rescale (util/rns.cpp:719-728, 824): q_last^-1 mod q_i ; q_i - (half mod q_i)
+        uint64_t *d_inv_qlast = nullptr; // [L-1]
+        uint64_t *d_neg_half = nullptr;  // [L-1]
+    };
+
+    struct SwitchKey
+    {
+        uint64_t *d = nullptr; // [beta0][2][K][N]
+        size_t bundles = 0;
+    };
+} // namespace gsb
+
+struct gsb_ws
+{
+    gsb_ctx *ctx = nullptr;
+    void *buf = nullptr;
+    size_t cap = 0;
+    void *pinned = nullptr;
+    size_t pinned_cap = 0;
+    void *reserve(size_t bytes);
+    void *reserve_pinned(size_t bytes);
+};
+
+struct gsb_ctx
+{
+    int device = 0;
+    int logn = 0;
+    size_t N = 0, K = 0, k = 0, L0 = 0;
+    std::vector<gsb::host::LimbTables> tables; // host copies (introspection + constants)
+    gsb::Twiddle *d_WW = nullptr, *d_VV = nullptr;
+    gsb::LimbC *d_limb = nullptr;
+    std::map<size_t, gsb::KsLevelConsts> level_consts;
+    gsb::SwitchKey relin;
+    std::map<uint32_t, gsb::SwitchKey> galois;
+    std::map<uint32_t, uint32_t *> galois_tables; // device permutation tables per element
+    std::mutex mu;
+    gsb_ws default_ws;
+
+    gsb::NttTables ntt_tables() const
+    {
+        return gsb::NttTables{ d_WW, d_VV, d_limb, static_cast<uint32_t>(N), logn };
+    }
+    const gsb::KsLevelConsts &consts_for(size_t L);
+    const uint32_t *galois_table(uint32_t elt);
+};

@@ -1,0 +1,201 @@
+// See host_tables.h.  Setup-time only; nothing here is on the timed path.
+#include "host_tables.h"
+
+namespace gsb
+{
+    namespace host
+    {
+        static inline uint64_t hi64(uint64_t a, uint64_t b)
+        {
+            return static_cast<uint64_t>((static_cast<u128>(a) * b) >> 64);
+        }
+
+        // Modulus::set_value (modulus.cpp:87-98): const_ratio = floor(2^128 / q), remainder.
+        ModConst make_mod(uint64_t q)
+        {
+            ModConst m;
+            m.q = q;
+            const u128 top = ~static_cast<u128>(0); // 2^128 - 1
+            u128 quo = top / q;
+            uint64_t rem = static_cast<uint64_t>(top % q) + 1;
+            if (rem == q)
+            {
+                quo += 1;
+                rem = 0;
+            }
+            m.cr0 = static_cast<uint64_t>(quo);
+            m.cr1 = static_cast<uint64_t>(quo >> 64);
+            m.cr2 = rem;
+            return m;
+        }
+
+        // shoupify (util/ntt.cpp:19-24)
+        uint64_t shoup(uint64_t x, uint64_t q)
+        {
+            return static_cast<uint64_t>((static_cast<u128>(x) << 64) / q);
+        }
+
+        // multiply_uint_mod via barrett_reduce_128 (util/uintarithsmallmod.h:140-178,209-221)
+        uint64_t mul_mod(uint64_t a, uint64_t b, const ModConst &m)
+        {
+            const u128 z = static_cast<u128>(a) * b;
+            const uint64_t z0 = static_cast<uint64_t>(z), z1 = static_cast<uint64_t>(z >> 64);
+            uint64_t carry = hi64(z0, m.cr0);
+            u128 t = static_cast<u128>(z0) * m.cr1;
+            uint64_t tmp1 = static_cast<uint64_t>(t) + carry;
+            uint64_t tmp3 = static_cast<uint64_t>(t >> 64) + (tmp1 < carry ? 1 : 0);
+            t = static_cast<u128>(z1) * m.cr0;
+            uint64_t s = tmp1 + static_cast<uint64_t>(t);
+            carry = static_cast<uint64_t>(t >> 64) + (s < tmp1 ? 1 : 0);
+            uint64_t quot = z1 * m.cr1 + tmp3 + carry;
+            uint64_t r = z0 - quot * m.q;
+            return r >= m.q ? r - m.q : r;
+        }
+
+        uint64_t barrett63(uint64_t x, const ModConst &m)
+        {
+            uint64_t r = x - hi64(x, m.cr1) * m.q;
+            return r >= m.q ? r - m.q : r;
+        }
+
+        uint64_t pow_mod(uint64_t a, uint64_t e, const ModConst &m)
+        {
+            uint64_t r = 1 % m.q, b = a % m.q;
+            for (; e; e >>= 1)
+            {
+                if (e & 1)
+                    r = mul_mod(r, b, m);
+                b = mul_mod(b, b, m);
+            }
+            return r;
+        }
+
+        bool inv_mod(uint64_t a, uint64_t q, uint64_t &out)
+        {
+            a %= q;
+            if (!a)
+                return false;
+            __int128 t0 = 0, t1 = 1;
+            uint64_t r0 = q, r1 = a;
+            while (r1)
+            {
+                uint64_t d = r0 / r1, r2 = r0 - d * r1;
+                __int128 t2 = t0 - static_cast<__int128>(d) * t1;
+                r0 = r1, r1 = r2, t0 = t1, t1 = t2;
+            }
+            if (r0 != 1)
+                return false;
+            out = static_cast<uint64_t>(t0 < 0 ? t0 + q : t0);
+            return true;
+        }
+
+        uint32_t reverse_bits(uint32_t x, int bits)
+        {
+            uint32_t r = 0;
+            for (int i = 0; i < bits; i++)
+                r |= ((x >> i) & 1u) << (bits - 1 - i);
+            return r;
+        }
+
+        // The reference takes the numerically smallest primitive 2N-th root (numth.cpp:398-425).
+        // All primitive 2N-th roots are the odd powers of any one of them, so scan those.
+        static bool minimal_root(uint64_t two_n, const ModConst &m, uint64_t &root)
+        {
+            if ((m.q - 1) % two_n)
+                return false;
+            const uint64_t cofactor = (m.q - 1) / two_n;
+            uint64_t g = 0;
+            for (uint64_t cand = 2; cand < 4096 && !g; cand++)
+            {
+                uint64_t r = pow_mod(cand, cofactor, m);
+                if (pow_mod(r, two_n >> 1, m) == m.q - 1)
+                    g = r;
+            }
+            if (!g)
+                return false;
+            const uint64_t g2 = mul_mod(g, g, m);
+            uint64_t best = g, cur = g;
+            for (uint64_t i = 1; i < (two_n >> 1); i++)
+            {
+                cur = mul_mod(cur, g2, m);
+                if (cur < best)
+                    best = cur;
+            }
+            root = best;
+            return true;
+        }
+
+        bool build_limb_tables(int logn, uint64_t q, LimbTables &t)
+        {
+            const size_t n = size_t(1) << logn;
+            t.mod = make_mod(q);
+            if (!minimal_root(2 * static_cast<uint64_t>(n), t.mod, t.root))
+                return false;
+            uint64_t inv_root = 0;
+            if (!inv_mod(t.root, q, inv_root) || !inv_mod(static_cast<uint64_t>(n), q, t.inv_n))
+                return false;
+            t.inv_n_s = shoup(t.inv_n, q);
+            t.rdp = shoup(1, q);
+            t.w.assign(n, 0);
+            t.ws.assign(n, 0);
+            t.v.assign(n, 0);
+            t.vs.assign(n, 0);
+            // forward: w[bitrev(i)] = root^i (util/ntt.cpp:101-111)
+            std::vector<uint64_t> inv_br(n);
+            uint64_t pf = 1, pi = 1;
+            t.w[0] = 1;
+            inv_br[0] = 1;
+            for (size_t i = 1; i < n; i++)
+            {
+                pf = mul_mod(pf, t.root, t.mod);
+                pi = mul_mod(pi, inv_root, t.mod);
+                const uint32_t r = reverse_bits(static_cast<uint32_t>(i), logn);
+                t.w[r] = pf;
+                inv_br[r] = pi;
+            }
+            // inverse: stage-major re-ordering (util/ntt.cpp:85-96) and n^-1 merged into the last
+            // entry (util/ntt.cpp:98)
+            t.v[0] = inv_br[0];
+            size_t pos = 1;
+            for (size_t m = n >> 1; m >= 1; m >>= 1)
+                for (size_t i = 0; i < m; i++)
+                    t.v[pos++] = inv_br[m + i];
+            t.v[n - 1] = mul_mod(t.v[n - 1], t.inv_n, t.mod);
+            for (size_t i = 0; i < n; i++)
+            {
+                t.ws[i] = shoup(t.w[i], q);
+                t.vs[i] = shoup(t.v[i], q);
+            }
+            return true;
+        }
+
+        void galois_table_ntt(int logn, uint32_t elt, std::vector<uint32_t> &table)
+        {
+            const uint32_t n = 1u << logn;
+            table.resize(n);
+            for (uint32_t i = 0; i < n; i++)
+            {
+                const uint32_t rev = reverse_bits(n + i, logn + 1);
+                const uint64_t raw = (static_cast<uint64_t>(elt) * rev) >> 1;
+                table[i] = reverse_bits(static_cast<uint32_t>(raw & (n - 1)), logn);
+            }
+        }
+
+        uint32_t galois_elt_from_step(int logn, int step)
+        {
+            const uint32_t n = 1u << logn;
+            const uint64_t m = 2ull * n;
+            if (step == 0)
+                return static_cast<uint32_t>(m - 1);
+            const bool neg = step < 0;
+            const uint32_t pos = static_cast<uint32_t>(neg ? -static_cast<int64_t>(step) : step);
+            if (pos >= (n >> 1))
+                return 0;
+            uint32_t count = neg ? (n >> 1) - pos : pos;
+            uint64_t e = 1;
+            while (count--)
+                e = (e * 5u) & (m - 1); // GaloisTool::generator_ = 5 (util/galois.h:169)
+            return static_cast<uint32_t>(e);
+        }
+    } // namespace host
+} // namespace gsb

@@ -1,0 +1,107 @@
+/* gseal_b200.h -- C ABI of the B200-native RNS polynomial-arithmetic hot path for Gemini-SEAL.
+ *
+ * This is the drop-in boundary: plain pointers and sizes, no C++ or torch types.  Each entry
+ * point names the reference interface it replaces (paths relative to
+ * /root/reference/native/src/seal/).  The C++ shim (gemini_seal_b200/shim) and the Python host
+ * mirror (gemini_seal_b200/evaluator.py) are thin callers of exactly these functions.
+ *
+ * Conventions (modelled on the reference's own C layer, c/defines.h:27-56, c/evaluator.cpp:31-58):
+ *   - every function returns an int status: GSB_OK or a negative GSB_E_* class; no exception ever
+ *     crosses the ABI; gsb_last_error() returns the message of the calling thread's last failure;
+ *   - the caller owns every buffer it passes; the context owns device copies of tables and keys;
+ *   - polynomial data is limb-major uint64_t exactly as in seal::Ciphertext (ciphertext.h:357-381):
+ *     a batch of B ciphertexts of `size` polynomials over L limbs is [B][size][L][N];
+ *   - *_dev functions take DEVICE pointers and enqueue on `stream` (a cudaStream_t, NULL = default
+ *     stream) without synchronising; *_host functions take HOST pointers, copy in, run, copy out
+ *     and synchronise before returning;
+ *   - a context is immutable after creation/key upload and may be shared by host threads as long
+ *     as each thread uses its own stream AND its own workspace (gsb_ws_*); the built-in default
+ *     workspace serialises callers that pass ws = NULL.
+ *   - there is no CPU fallback: every compute entry point fails with GSB_E_CUDA if no CUDA
+ *     device is usable.
+ */
+#ifndef GSEAL_B200_H
+#define GSEAL_B200_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GSB_OK 0
+#define GSB_E_INVALID_ARG (-1) /* std::invalid_argument in the reference (evaluator.cpp:238-249 ...) */
+#define GSB_E_LOGIC (-2)       /* std::logic_error in the reference                                 */
+#define GSB_E_RANGE (-3)       /* std::out_of_range                                                 */
+#define GSB_E_CUDA (-4)        /* CUDA runtime failure / no device (std::runtime_error in the shim) */
+#define GSB_E_NOMEM (-5)
+
+typedef struct gsb_ctx gsb_ctx;
+typedef struct gsb_ws gsb_ws;
+
+/* gsb_ntt_* `mode` */
+#define GSB_NTT_STRICT 0 /* ntt_negacyclic_harvey / inverse_ntt_negacyclic_harvey  (util/ntt.h:225,318) */
+#define GSB_NTT_LAZY 1   /* ..._lazy: forward in [0,4q), inverse in [0,2q)         (util/ntt.cpp:292,345) */
+
+/* gsb_poly_op `op` (util/polyarithsmallmod.{h,cpp}) */
+#define GSB_OP_DYADIC 0     /* dyadic_product_coeffmod        .cpp:63-117  */
+#define GSB_OP_ADD 1        /* add_poly_coeffmod              .h:261-300   */
+#define GSB_OP_SUB 2        /* sub_poly_coeffmod              .h:366-405   */
+#define GSB_OP_NEGATE 3     /* negate_poly_coeffmod           .h:176-206   */
+#define GSB_OP_MUL_SCALAR 4 /* multiply_poly_scalar_coeffmod  .cpp:15-61 (one scalar per limb) */
+
+/* key kinds for gsb_key_upload */
+#define GSB_KEY_RELIN 0  /* RelinKeys::get_index(2) -> key for s^2     (relinkeys.h:61)   */
+#define GSB_KEY_GALOIS 1 /* GaloisKeys::get_index(elt)                 (galoiskeys.h:52)  */
+
+const char *gsb_last_error(void);
+int gsb_version(void);
+/* number of kernel launches this library has issued in this process (bench.py "gpu_launches") */
+unsigned long long gsb_launch_count(void);
+
+/* ---- context: replaces SEALContext::ContextData tables (context.cpp:135-420) --------------------
+ * moduli[0..K) is the key-level coeff_modulus; its last k_special entries are the special primes
+ * (encryptionparams.h:205-214).  Ciphertext levels have L = K-k_special, K-k_special-1, ... limbs
+ * over moduli[0..L).  Tables are built on the host exactly as NTTTables::initialize does
+ * (util/ntt.cpp:37-99) and uploaded once.  N = 2^logn, 10 <= logn <= 16. */
+int gsb_ctx_create(int device, int logn, const uint64_t *moduli, size_t K, size_t k_special, gsb_ctx **out);
+void gsb_ctx_destroy(gsb_ctx *ctx);
+/* Introspection (tests compare these with the reference's NTTTables accessors, util/ntt.h:46-60,
+ * 84-92,116).  Each array argument may be NULL.  scalars[0..6] = q, const_ratio[0], const_ratio[1],
+ * root, inv_degree_modulo, scaled_inv_degree, reduce_precomp. */
+int gsb_ctx_get_tables(
+    const gsb_ctx *ctx, size_t mod_index, uint64_t *root_powers, uint64_t *scaled_root_powers,
+    uint64_t *inv_root_powers, uint64_t *scaled_inv_root_powers, uint64_t *scalars);
+int gsb_ctx_info(const gsb_ctx *ctx, int *logn, size_t *K, size_t *k_special);
+
+/* ---- workspaces (the device-side stand-in for the MemoryPoolHandle argument) -------------------- */
+int gsb_ws_create(gsb_ctx *ctx, gsb_ws **out);
+void gsb_ws_destroy(gsb_ws *ws);
+
+/* ---- device memory helpers for callers without their own CUDA allocator ----------------------- */
+int gsb_malloc(gsb_ctx *ctx, size_t bytes, void **out);
+int gsb_free(gsb_ctx *ctx, void *ptr);
+int gsb_malloc_host(size_t bytes, void **out); /* pinned */
+int gsb_free_host(void *ptr);
+int gsb_memcpy_h2d(gsb_ctx *ctx, void *dst, const void *src, size_t bytes, void *stream);
+int gsb_memcpy_d2h(gsb_ctx *ctx, void *dst, const void *src, size_t bytes, void *stream);
+int gsb_stream_sync(gsb_ctx *ctx, void *stream);
+
+/* ---- NTT: util::ntt_negacyclic_harvey[_lazy] / inverse_... over RNSIter / PolyIter --------------
+ * (util/ntt.h:189-368).  data = [n_polys][n_limbs][N]; limb y of every polynomial uses modulus
+ * index limb_offset + y.  In place. */
+int gsb_ntt_forward_dev(gsb_ctx *ctx, uint64_t *data, size_t n_polys, size_t n_limbs, size_t limb_offset, int mode, void *stream);
+int gsb_ntt_inverse_dev(gsb_ctx *ctx, uint64_t *data, size_t n_polys, size_t n_limbs, size_t limb_offset, int mode, void *stream);
+int gsb_ntt_forward_host(gsb_ctx *ctx, uint64_t *data, size_t n_polys, size_t n_limbs, size_t limb_offset, int mode);
+int gsb_ntt_inverse_host(gsb_ctx *ctx, uint64_t *data, size_t n_polys, size_t n_limbs, size_t limb_offset, int mode);
+
+/* ---- elementwise kernels (util/polyarithsmallmod.*) -------------------------------------------
+ * a, b, out = [n_polys][n_limbs][N]; b is ignored for NEGATE / MUL_SCALAR; scalars = n_limbs host
+ * words (one per limb) for MUL_SCALAR, else NULL.  out may alias a or b. */
+int gsb_poly_op_dev(
+    gsb_ctx *ctx, int op, const uint64_t *a, const uint64_t *b, const uint64_t *scalars, uint64_t *out,
+    size_t n_polys, size_t n_limbs, size_t limb_offset, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GSEAL_B200_H */
