@@ -21,6 +21,8 @@ PROTOTYPES = {
     "gsb_last_error": (C.c_char_p, []),
     "gsb_version": (i32, []),
     "gsb_launch_count": (C.c_ulonglong, []),
+    "gsb_prof_enable": (i32, [i32]),
+    "gsb_prof_report": (C.c_long, [C.c_char_p, sz]),
     "gsb_ctx_create": (i32, [i32, i32, u64p, sz, sz, C.POINTER(vp)]),
     "gsb_ctx_destroy": (None, [vp]),
     "gsb_ctx_get_tables": (i32, [vp, sz, u64p, u64p, u64p, u64p, u64p]),

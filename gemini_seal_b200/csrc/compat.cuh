@@ -9,12 +9,23 @@
 
 #ifdef GSB_CUSIM
 #include "cusim.h"
-#define GSB_LAUNCH(kfn, grid, block, smem, stream, ...) \
+#define GSB_LAUNCH(pass, tag, kfn, grid, block, smem, stream, ...) \
     (++::gsb::launch_counter(), ::cusim::launch((grid), (block), (smem), [&]() { kfn(__VA_ARGS__); }))
 #else
 #include <cuda_runtime.h>
-#define GSB_LAUNCH(kfn, grid, block, smem, stream, ...) \
-    (++::gsb::launch_counter(), kfn<<<(grid), (block), (smem), (stream)>>>(__VA_ARGS__))
+// Every launch goes through here: counted (gsb_launch_count) and, when gsb_prof_enable(1) is on,
+// bracketed by CUDA events on the launching stream (gsb_prof_report), labelled "<pass>/<tag>".
+#define GSB_LAUNCH(pass, tag, kfn, grid, block, smem, stream, ...)       \
+    do                                                                   \
+    {                                                                    \
+        ++::gsb::launch_counter();                                       \
+        const bool prof__ = ::gsb::prof_on();                            \
+        if (prof__)                                                      \
+            ::gsb::prof_begin((pass), (tag), (stream));                  \
+        kfn<<<(grid), (block), (smem), (stream)>>>(__VA_ARGS__);         \
+        if (prof__)                                                      \
+            ::gsb::prof_end((stream));                                   \
+    } while (0)
 #endif
 
 #define GSB_DEV __device__ __forceinline__
@@ -23,6 +34,9 @@ namespace gsb
 {
     // Kernel launches issued by this library in this process (gsb_launch_count()).
     unsigned long long &launch_counter();
+    bool prof_on();
+    void prof_begin(const char *pass, const char *tag, cudaStream_t st);
+    void prof_end(cudaStream_t st);
 
     // Dynamic shared memory base (one extern array per translation unit).
     GSB_DEV uint64_t *dyn_smem()

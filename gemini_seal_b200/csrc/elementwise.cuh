@@ -62,11 +62,11 @@ namespace gsb
         const unsigned grid = grid_for(args.total >> 1, 256);
         switch (op)
         {
-        case GSB_OP_DYADIC: GSB_LAUNCH(poly_op_kernel<GSB_OP_DYADIC>, dim3(grid), dim3(256), 0, st, args); break;
-        case GSB_OP_ADD: GSB_LAUNCH(poly_op_kernel<GSB_OP_ADD>, dim3(grid), dim3(256), 0, st, args); break;
-        case GSB_OP_SUB: GSB_LAUNCH(poly_op_kernel<GSB_OP_SUB>, dim3(grid), dim3(256), 0, st, args); break;
-        case GSB_OP_NEGATE: GSB_LAUNCH(poly_op_kernel<GSB_OP_NEGATE>, dim3(grid), dim3(256), 0, st, args); break;
-        default: GSB_LAUNCH(poly_op_kernel<GSB_OP_MUL_SCALAR>, dim3(grid), dim3(256), 0, st, args); break;
+        case GSB_OP_DYADIC: GSB_LAUNCH("poly_op", "", poly_op_kernel<GSB_OP_DYADIC>, dim3(grid), dim3(256), 0, st, args); break;
+        case GSB_OP_ADD: GSB_LAUNCH("poly_op", "", poly_op_kernel<GSB_OP_ADD>, dim3(grid), dim3(256), 0, st, args); break;
+        case GSB_OP_SUB: GSB_LAUNCH("poly_op", "", poly_op_kernel<GSB_OP_SUB>, dim3(grid), dim3(256), 0, st, args); break;
+        case GSB_OP_NEGATE: GSB_LAUNCH("poly_op", "", poly_op_kernel<GSB_OP_NEGATE>, dim3(grid), dim3(256), 0, st, args); break;
+        default: GSB_LAUNCH("poly_op", "", poly_op_kernel<GSB_OP_MUL_SCALAR>, dim3(grid), dim3(256), 0, st, args); break;
         }
     }
 } // namespace gsb

@@ -2,6 +2,7 @@
 // points.  Key switching / multiply / rescale / Galois live in gsb_evaluator.cuh, included below.
 #include "gsb_context.cuh"
 #include "elementwise.cuh"
+#include <cstdio>
 #include <cstring>
 #include <memory>
 
@@ -16,6 +17,45 @@ namespace gsb
     {
         static unsigned long long n = 0;
         return n;
+    }
+
+    // ---- optional per-launch CUDA-event timing (gsb_prof_*) -------------------------------------
+    struct ProfRec
+    {
+        std::string label;
+        cudaEvent_t e0, e1;
+    };
+    static bool g_prof = false;
+    static std::mutex g_prof_mu;
+    static std::vector<ProfRec> g_prof_recs;
+    bool prof_on()
+    {
+        return g_prof;
+    }
+    void prof_begin(const char *pass, const char *tag, cudaStream_t st)
+    {
+        ProfRec r;
+        r.label = std::string(pass) + (tag && *tag ? std::string("/") + tag : std::string());
+        cudaEventCreate(&r.e0);
+        cudaEventCreate(&r.e1);
+        cudaEventRecord(r.e0, st);
+        std::lock_guard<std::mutex> lock(g_prof_mu);
+        g_prof_recs.push_back(r);
+    }
+    void prof_end(cudaStream_t st)
+    {
+        std::lock_guard<std::mutex> lock(g_prof_mu);
+        cudaEventRecord(g_prof_recs.back().e1, st);
+    }
+    static void prof_clear()
+    {
+        std::lock_guard<std::mutex> lock(g_prof_mu);
+        for (auto &r : g_prof_recs)
+        {
+            cudaEventDestroy(r.e0);
+            cudaEventDestroy(r.e1);
+        }
+        g_prof_recs.clear();
     }
 
     template <class F>
@@ -108,6 +148,48 @@ unsigned long long gsb_launch_count(void)
     return launch_counter();
 }
 
+int gsb_prof_enable(int on)
+{
+    prof_clear();
+    g_prof = on != 0;
+    return GSB_OK;
+}
+
+long gsb_prof_report(char *buf, size_t cap)
+{
+    long need = -1;
+    guarded([&] {
+        GSB_CUDA_CHECK(cudaDeviceSynchronize());
+        std::map<std::string, std::pair<unsigned long long, double>> agg;
+        std::vector<std::string> order;
+        {
+            std::lock_guard<std::mutex> lock(g_prof_mu);
+            for (auto &r : g_prof_recs)
+            {
+                float ms = 0.f;
+                GSB_CUDA_CHECK(cudaEventElapsedTime(&ms, r.e0, r.e1));
+                if (!agg.count(r.label))
+                    order.push_back(r.label);
+                agg[r.label].first++;
+                agg[r.label].second += ms;
+            }
+        }
+        std::string js = "{";
+        for (size_t i = 0; i < order.size(); i++)
+        {
+            char tmp[256];
+            snprintf(tmp, sizeof(tmp), "%s\"%s\": {\"launches\": %llu, \"ms\": %.6f}", i ? ", " : "", order[i].c_str(),
+                     agg[order[i]].first, agg[order[i]].second);
+            js += tmp;
+        }
+        js += "}";
+        need = static_cast<long>(js.size()) + 1;
+        if (buf && cap >= js.size() + 1)
+            memcpy(buf, js.c_str(), js.size() + 1);
+    });
+    return need;
+}
+
 int gsb_ctx_create(int device, int logn, const uint64_t *moduli, size_t K, size_t k_special, gsb_ctx **out)
 {
     return guarded([&] {
@@ -156,6 +238,7 @@ int gsb_ctx_create(int device, int logn, const uint64_t *moduli, size_t K, size_
         ctx->d_VV = upload(vv);
         ctx->d_limb = upload(limb);
         ctx->default_ws.ctx = ctx.get();
+        ctx->host_io.ctx = ctx.get();
         *out = ctx.release();
     });
 }
@@ -184,6 +267,7 @@ void gsb_ctx_destroy(gsb_ctx *ctx)
     for (auto &kv : ctx->galois_tables)
         cudaFree(kv.second);
     cudaFree(ctx->default_ws.buf);
+    cudaFree(ctx->host_io.buf);
     if (ctx->default_ws.pinned)
         cudaFreeHost(ctx->default_ws.pinned);
     delete ctx;
@@ -324,11 +408,11 @@ static void ntt_dev(
         uint64_t *p = data + p0 * per;
         if (inverse)
         {
-            GSB_DISPATCH_LOGN(ctx->logn, ntt_inverse_plain<LOGN>(tab, mm, p, p, static_cast<int>(n_limbs), nz, lazy, st));
+            GSB_DISPATCH_LOGN(ctx->logn, ntt_inverse_plain<LOGN>(tab, mm, p, per, p, per, static_cast<int>(n_limbs), nz, lazy, st));
         }
         else
         {
-            GSB_DISPATCH_LOGN(ctx->logn, ntt_forward_plain<LOGN>(tab, mm, p, p, static_cast<int>(n_limbs), nz, lazy, st));
+            GSB_DISPATCH_LOGN(ctx->logn, ntt_forward_plain<LOGN>(tab, mm, p, per, p, per, static_cast<int>(n_limbs), nz, lazy, st));
         }
     }
     GSB_CUDA_CHECK(cudaGetLastError());
@@ -348,10 +432,10 @@ static void ntt_host(gsb_ctx *ctx, uint64_t *data, size_t n_polys, size_t n_limb
 {
     check_limbs(ctx, n_polys, n_limbs, limb_offset);
     require(data != nullptr, GSB_E_INVALID_ARG, "data is null");
-    std::lock_guard<std::mutex> lock(ctx->mu);
+    std::lock_guard<std::mutex> lock(ctx->host_mu);
     GSB_CUDA_CHECK(cudaSetDevice(ctx->device));
     const size_t bytes = n_polys * n_limbs * ctx->N * sizeof(uint64_t);
-    uint64_t *d = static_cast<uint64_t *>(ctx->default_ws.reserve(bytes));
+    uint64_t *d = static_cast<uint64_t *>(ctx->host_io.reserve(bytes));
     GSB_CUDA_CHECK(cudaMemcpyAsync(d, data, bytes, cudaMemcpyHostToDevice, nullptr));
     ntt_dev(ctx, d, n_polys, n_limbs, limb_offset, mode, inverse, nullptr);
     GSB_CUDA_CHECK(cudaMemcpyAsync(data, d, bytes, cudaMemcpyDeviceToHost, nullptr));

@@ -5,6 +5,7 @@
 #include "../../include/gseal_b200.h"
 #include "host_tables.h"
 #include "ntt_kernels.cuh"
+#include <functional>
 #include <map>
 #include <mutex>
 #include <string>
@@ -82,8 +83,10 @@ struct gsb_ctx
     gsb::SwitchKey relin;
     std::map<uint32_t, gsb::SwitchKey> galois;
     std::map<uint32_t, uint32_t *> galois_tables; // device permutation tables per element
-    std::mutex mu;
-    gsb_ws default_ws;
+    std::mutex mu;      // guards the lazily built maps below
+    std::mutex host_mu; // serialises the *_host entry points (they share host_io / default_ws)
+    gsb_ws default_ws;  // compute scratch for callers that pass ws = NULL
+    gsb_ws host_io;     // device staging of the *_host entry points
 
     gsb::NttTables ntt_tables() const
     {

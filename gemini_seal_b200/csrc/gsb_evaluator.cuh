@@ -1,1 +1,646 @@
-// (filled in next)
+// CKKS evaluator hot path on the device: tensor product, hybrid key switching (k >= 1 special
+// primes), mod-down, rescale and Galois rotation, built from the NTT rounds of ntt_core.cuh with
+// fused prologues / epilogues.  Reference: native/src/seal/evaluator.cpp:447-527 (ckks_multiply),
+// :772-827 (relinearize_internal), :829-892 (mod_switch_scale_to_next), :1841-1943
+// (apply_galois_inplace), :2259-2368 (switch_key_inplace); multi_special_primes.cpp:80-304;
+// util/rns.cpp:777-851; util/galois.cpp:18-47,188-214.  Included at the end of gsb_api.cu.
+#pragma once
+#include "gsb_context.cuh"
+#include "gsb_ks_kernels.cuh"
+#include <algorithm>
+
+namespace gsb
+{
+    // ---- per-level constants (host, once per level; multi_special_primes.cpp / util/rns.cpp) ------
+    static uint64_t reduce_mod(uint64_t x, const host::ModConst &m)
+    {
+        return x % m.q;
+    }
+
+    static uint64_t *upload_words(const std::vector<uint64_t> &h)
+    {
+        uint64_t *d = nullptr;
+        const size_t n = h.empty() ? 1 : h.size();
+        GSB_CUDA_CHECK(cudaMalloc(reinterpret_cast<void **>(&d), n * sizeof(uint64_t)));
+        if (!h.empty())
+            GSB_CUDA_CHECK(cudaMemcpy(d, h.data(), h.size() * sizeof(uint64_t), cudaMemcpyHostToDevice));
+        return d;
+    }
+} // namespace gsb
+
+const gsb::KsLevelConsts &gsb_ctx::consts_for(size_t L)
+{
+    using namespace gsb;
+    std::lock_guard<std::mutex> lock(mu);
+    auto it = level_consts.find(L);
+    if (it != level_consts.end())
+        return it->second;
+    require(L >= 1 && L <= L0, GSB_E_INVALID_ARG, "no ciphertext level with that many limbs");
+    const size_t E = L + k, beta = (L + k - 1) / k;
+    auto modc = [&](size_t idx) -> const host::ModConst & { return tables[idx].mod; };
+    auto ext_mod = [&](size_t kap) { return kap < L ? kap : L0 + (kap - L); };
+    std::vector<uint64_t> a(beta * k * 2, 0), b(beta * k * E, 0);
+    // mod-up constants (multi_special_primes.cpp:113-126)
+    for (size_t j = 0; j < beta; j++)
+    {
+        const size_t s0 = j * k, s1 = std::min(s0 + k, L);
+        if (s1 - s0 < 2)
+            continue; // single-limb bundle: copy / barrett_reduce_63 path (:99-108)
+        for (size_t i = s0; i < s1; i++)
+        {
+            uint64_t inv_prod = 1;
+            for (size_t i2 = s0; i2 < s1; i2++)
+                if (i2 != i)
+                    inv_prod = host::mul_mod(inv_prod, reduce_mod(modc(i2).q, modc(i)), modc(i));
+            uint64_t inv = 0;
+            require(host::inv_mod(inv_prod, modc(i).q, inv), GSB_E_LOGIC, "modup: inv_mod fail");
+            a[(j * k + (i - s0)) * 2] = inv;
+            a[(j * k + (i - s0)) * 2 + 1] = host::shoup(inv, modc(i).q);
+            for (size_t kap = 0; kap < E; kap++)
+            {
+                const host::ModConst &md = modc(ext_mod(kap));
+                uint64_t prod = 1;
+                for (size_t i2 = s0; i2 < s1; i2++)
+                    if (i2 != i)
+                        prod = host::mul_mod(prod, reduce_mod(modc(i2).q, md), md);
+                b[(j * k + (i - s0)) * E + kap] = prod;
+            }
+        }
+    }
+    // mod-down constants (multi_special_primes.cpp:186-234, 292-299)
+    std::vector<uint64_t> inv_hat(k * 2, 0), neg_hat(L * k, 0), inv_p(L * 2, 0);
+    for (size_t j = 0; j < k; j++)
+    {
+        const host::ModConst &pj = modc(L0 + j);
+        uint64_t prod = 1;
+        for (size_t j2 = 0; j2 < k; j2++)
+            if (j2 != j)
+                prod = host::mul_mod(prod, reduce_mod(modc(L0 + j2).q, pj), pj);
+        uint64_t inv = 0;
+        require(host::inv_mod(prod, pj.q, inv), GSB_E_LOGIC, "moddown: inv_mod fail");
+        inv_hat[2 * j] = inv;
+        inv_hat[2 * j + 1] = host::shoup(inv, pj.q);
+    }
+    for (size_t i = 0; i < L; i++)
+    {
+        const host::ModConst &qi = modc(i);
+        uint64_t P = 1;
+        for (size_t j = 0; j < k; j++)
+        {
+            uint64_t prod = 1;
+            for (size_t j2 = 0; j2 < k; j2++)
+                if (j2 != j)
+                    prod = host::mul_mod(prod, reduce_mod(modc(L0 + j2).q, qi), qi);
+            neg_hat[i * k + j] = prod ? qi.q - prod : 0;
+            P = host::mul_mod(P, reduce_mod(modc(L0 + j).q, qi), qi);
+        }
+        uint64_t inv = 0;
+        require(host::inv_mod(P, qi.q, inv), GSB_E_LOGIC, "moddown: inv_mod fail");
+        inv_p[2 * i] = inv;
+        inv_p[2 * i + 1] = host::shoup(inv, qi.q);
+    }
+    // rescale constants (util/rns.cpp:719-728, 824)
+    std::vector<uint64_t> inv_qlast, neg_half;
+    if (L >= 2)
+    {
+        const uint64_t qL = modc(L - 1).q, half = qL >> 1;
+        for (size_t i = 0; i + 1 < L; i++)
+        {
+            uint64_t inv = 0;
+            require(host::inv_mod(qL, modc(i).q, inv), GSB_E_LOGIC, "invalid rns bases");
+            inv_qlast.push_back(inv);
+            neg_half.push_back(modc(i).q - host::barrett63(half, modc(i)));
+        }
+    }
+    GSB_CUDA_CHECK(cudaSetDevice(device));
+    KsLevelConsts c;
+    c.d_modup_a = upload_words(a);
+    c.d_modup_b = upload_words(b);
+    c.d_inv_hat = upload_words(inv_hat);
+    c.d_neg_hat = upload_words(neg_hat);
+    c.d_inv_p = upload_words(inv_p);
+    c.d_inv_qlast = upload_words(inv_qlast);
+    c.d_neg_half = upload_words(neg_half);
+    return level_consts.emplace(L, c).first->second;
+}
+
+const uint32_t *gsb_ctx::galois_table(uint32_t elt)
+{
+    using namespace gsb;
+    std::lock_guard<std::mutex> lock(mu);
+    auto it = galois_tables.find(elt);
+    if (it != galois_tables.end())
+        return it->second;
+    // GaloisTool::generate_table_ntt argument checks (util/galois.cpp:20-24, galois.h:139-148)
+    require((elt & 1u) && elt < 2u * N, GSB_E_INVALID_ARG, "Galois element is not valid");
+    std::vector<uint32_t> t;
+    host::galois_table_ntt(logn, elt, t);
+    uint32_t *d = nullptr;
+    GSB_CUDA_CHECK(cudaSetDevice(device));
+    GSB_CUDA_CHECK(cudaMalloc(reinterpret_cast<void **>(&d), N * sizeof(uint32_t)));
+    GSB_CUDA_CHECK(cudaMemcpy(d, t.data(), N * sizeof(uint32_t), cudaMemcpyHostToDevice));
+    galois_tables[elt] = d;
+    return d;
+}
+
+namespace gsb
+{
+    // ---- workspace carving ---------------------------------------------------------------------
+    struct Arena
+    {
+        char *base;
+        size_t off = 0;
+        explicit Arena(void *p) : base(static_cast<char *>(p)) {}
+        uint64_t *words(size_t n)
+        {
+            uint64_t *r = reinterpret_cast<uint64_t *>(base + off);
+            off += (n * sizeof(uint64_t) + 255) / 256 * 256;
+            return r;
+        }
+    };
+    static size_t arena_words(size_t n)
+    {
+        return ((n * sizeof(uint64_t) + 255) / 256 * 256) / sizeof(uint64_t);
+    }
+
+    static KsDev make_ksdev(gsb_ctx *ctx, size_t L)
+    {
+        const KsLevelConsts &lc = ctx->consts_for(L);
+        KsDev ks;
+        ks.limb = ctx->d_limb;
+        ks.modup_a = lc.d_modup_a;
+        ks.modup_b = lc.d_modup_b;
+        ks.inv_hat = lc.d_inv_hat;
+        ks.neg_hat = lc.d_neg_hat;
+        ks.inv_p = lc.d_inv_p;
+        ks.L = static_cast<uint32_t>(L);
+        ks.L0 = static_cast<uint32_t>(ctx->L0);
+        ks.k = static_cast<uint32_t>(ctx->k);
+        ks.E = static_cast<uint32_t>(L + ctx->k);
+        ks.beta = static_cast<uint32_t>((L + ctx->k - 1) / ctx->k);
+        ks.N = static_cast<uint32_t>(ctx->N);
+        return ks;
+    }
+
+    // Words of scratch one ciphertext needs inside switch_key_core.
+    static size_t ks_words_per_ct(const gsb_ctx *ctx, size_t L)
+    {
+        const size_t N = ctx->N, E = L + ctx->k, beta = (L + ctx->k - 1) / ctx->k;
+        const bool two = ctx->logn >= 13;
+        return L * N + (two ? beta * E * N : 0) + 2 * E * N + (two ? 2 * L * N : 0);
+    }
+
+    struct KsOutput // where the key-switch result is added and stored (see MdStoreArgs)
+    {
+        const uint64_t *add_src;
+        size_t add_bs, add_ls;
+        uint64_t *dst;
+        size_t dst_bs, dst_ls;
+        const uint32_t *table;
+    };
+
+    // switch_key_inplace for `B` ciphertexts (evaluator.cpp:2259-2368).  scratch must hold
+    // B * ks_words_per_ct words (+ alignment slack).
+    template <int LOGN>
+    static void switch_key_core(
+        gsb_ctx *ctx, void *scratch, const uint64_t *target, size_t target_stride, const SwitchKey &key, const KsOutput &o,
+        size_t B, size_t L, cudaStream_t st)
+    {
+        constexpr bool two = Split<LOGN>::two_pass;
+        const size_t N = ctx->N;
+        const KsDev ks = make_ksdev(ctx, L);
+        const size_t E = ks.E, beta = ks.beta, k = ks.k;
+        require(key.d != nullptr && key.bundles >= beta, GSB_E_INVALID_ARG, "kswitch_keys is not valid for encryption parameters");
+        const NttTables tab = ctx->ntt_tables();
+        Arena ar(scratch);
+        uint64_t *coef = ar.words(B * L * N);
+        uint64_t *ext1 = two ? ar.words(B * beta * E * N) : nullptr;
+        uint64_t *red = ar.words(B * 2 * E * N);
+        uint64_t *tmp = two ? ar.words(B * 2 * L * N) : nullptr;
+        const int iB = static_cast<int>(B), iL = static_cast<int>(L), iE = static_cast<int>(E);
+
+        // Step 1 (:2302-2307): strict inverse NTT of every target limb (all bundles at once).
+        ntt_inverse_plain<LOGN>(tab, ModMap{ 1 << 30, 0, 0 }, target, target_stride, coef, L * N, iL, iB, false, st, "ks_target");
+
+        // Step 2 + first NTT pass of step 3 (:2310, :2322): mod-up fused into the column pass.
+        if constexpr (two)
+        {
+            IoPair<ModupLoad, PlainStore<OUT_RAW>> io{ ModupArgs{ ks, coef }, PlainStoreArgs{ ext1, E * N } };
+            launch_fwd_cols<LOGN>(io, tab, ModMap{ iL, static_cast<int>(ctx->L0), 0 }, iE, static_cast<int>(B * beta), st, "modup");
+        }
+        // Step 3 + Barrett part of step 4: last NTT pass fused with the key inner product.
+        {
+            typedef MacPlan<LOGN> MP;
+            KsMacArgs a{ ks, target, target_stride, coef, ext1, key.d, red, static_cast<uint32_t>(ctx->K) };
+            auto kfn = ks_mac_kernel<LOGN>;
+            allow_smem(kfn, tile_smem_bytes<MP::T>());
+            dim3 grid(static_cast<unsigned>(B), 1u << (LOGN - MP::T - 3), static_cast<unsigned>(E));
+            GSB_LAUNCH("ks_mac", "", kfn, grid, dim3(1 << MP::T), tile_smem_bytes<MP::T>(), st, a, tab);
+        }
+        // Step 4 (:2353-2357): lazy inverse NTT of the special slots.
+        ntt_inverse_plain<LOGN>(
+            tab, ModMap{ 0, static_cast<int>(ctx->L0), 0 }, red + L * N, E * N, red + L * N, E * N, static_cast<int>(k),
+            static_cast<int>(2 * B), true, st, "ks_special");
+        // Step 5 (mod-down) + final add (:2360-2366).
+        const MdLoadArgs la{ ks, red };
+        const MdStoreArgs sa{ ks, red, o.add_src, o.add_bs, o.add_ls, o.dst, o.dst_bs, o.dst_ls, o.table };
+        const ModMap mm{ 1 << 30, 0, 0 };
+        if constexpr (two)
+        {
+            IoPair<MdLoad, PlainStore<OUT_RAW>> io1{ la, PlainStoreArgs{ tmp, L * N } };
+            launch_fwd_cols<LOGN>(io1, tab, mm, iL, static_cast<int>(2 * B), st, "moddown");
+            IoPair<PlainLoad, MdStore> io2{ PlainArgs{ tmp, L * N }, sa };
+            launch_fwd_contig<LOGN>(io2, tab, mm, iL, static_cast<int>(2 * B), st, "moddown");
+        }
+        else
+        {
+            IoPair<MdLoad, MdStore> io{ la, sa };
+            launch_fwd_contig<LOGN>(io, tab, mm, iL, static_cast<int>(2 * B), st, "moddown");
+        }
+    }
+
+    // rescale for n_polys polynomials of L limbs (util/rns.cpp:777-851). t = n_polys*N words scratch.
+    template <int LOGN>
+    static void rescale_core(gsb_ctx *ctx, uint64_t *t, const uint64_t *in, uint64_t *out, size_t n_polys, size_t L, cudaStream_t st)
+    {
+        constexpr bool two = Split<LOGN>::two_pass;
+        const size_t N = ctx->N;
+        const KsLevelConsts &lc = ctx->consts_for(L);
+        const NttTables tab = ctx->ntt_tables();
+        const int nz = static_cast<int>(n_polys);
+        const ModMap mlast{ 1 << 30, 0, static_cast<int>(L - 1) };
+        // stage 1: t = barrett63(strict_iNTT(last limb) + half)
+        if constexpr (two)
+        {
+            launch_inv_contig<LOGN>(IoPlain<OUT_RAW>{ in + (L - 1) * N, t, L * N, N }, tab, mlast, 1, nz, st, "rescale_last");
+            IoPair<PlainLoad, RsLastStore> io{ PlainArgs{ t, N }, PlainStoreArgs{ t, N } };
+            launch_inv_cols<LOGN>(io, tab, mlast, 1, nz, st, "rescale_last");
+        }
+        else
+        {
+            IoPair<PlainLoad, RsLastStore> io{ PlainArgs{ in + (L - 1) * N, L * N }, PlainStoreArgs{ t, N } };
+            launch_inv_contig<LOGN>(io, tab, mlast, 1, nz, st, "rescale_last");
+        }
+        // stage 2: per remaining limb
+        const RsLoadArgs la{ t, lc.d_neg_half, ctx->tables[L - 1].mod.q };
+        const RsStoreArgs sa{ in, out, lc.d_inv_qlast, static_cast<uint32_t>(L) };
+        const ModMap mm{ 1 << 30, 0, 0 };
+        const int ny = static_cast<int>(L - 1);
+        if constexpr (two)
+        {
+            // `out` doubles as the buffer between the two passes (same element, same thread)
+            IoPair<RsLoad, PlainStore<OUT_RAW>> io1{ la, PlainStoreArgs{ out, (L - 1) * N } };
+            launch_fwd_cols<LOGN>(io1, tab, mm, ny, nz, st, "rescale");
+            IoPair<PlainLoad, RsStore> io2{ PlainArgs{ out, (L - 1) * N }, sa };
+            launch_fwd_contig<LOGN>(io2, tab, mm, ny, nz, st, "rescale");
+        }
+        else
+        {
+            IoPair<RsLoad, RsStore> io{ la, sa };
+            launch_fwd_contig<LOGN>(io, tab, mm, ny, nz, st, "rescale");
+        }
+    }
+
+    static void ckks_multiply_core(gsb_ctx *ctx, const uint64_t *a, const uint64_t *b, uint64_t *out, size_t B, size_t L, cudaStream_t st)
+    {
+        CkksMulArgs p{ a, b, out, ctx->d_limb, static_cast<uint32_t>(ctx->N), static_cast<uint32_t>(L), B * L * ctx->N / 2 };
+        GSB_LAUNCH("ckks_multiply", "", ckks_multiply_kernel, dim3(grid_for(p.pairs, 256)), dim3(256), 0, st, p);
+    }
+
+    static void gather_core(
+        gsb_ctx *ctx, const uint64_t *in, size_t in_zs, uint64_t *out, const uint32_t *table, size_t n, size_t L, cudaStream_t st)
+    {
+        GatherArgs p{ in, in_zs, out, table, static_cast<uint32_t>(ctx->N), static_cast<uint32_t>(L), n * L * ctx->N };
+        GSB_LAUNCH("galois_gather", "", galois_gather_kernel, dim3(grid_for(p.total, 256)), dim3(256), 0, st, p);
+    }
+
+    // How many ciphertexts to push through one pass of the pipeline: bounded scratch (<= ~6 GiB).
+    static size_t chunk_for(size_t words_per_ct, size_t B)
+    {
+        const size_t budget = (size_t(6) << 30) / sizeof(uint64_t);
+        size_t c = budget / (words_per_ct + 64);
+        c = c < 1 ? 1 : c;
+        if (c >= B)
+            return B;
+        const size_t n_chunks = (B + c - 1) / c; // balance the chunks
+        return (B + n_chunks - 1) / n_chunks;
+    }
+
+    static const SwitchKey &find_key(gsb_ctx *ctx, int kind, uint32_t elt)
+    {
+        std::lock_guard<std::mutex> lock(ctx->mu);
+        if (kind == GSB_KEY_RELIN)
+        {
+            require(ctx->relin.d != nullptr, GSB_E_INVALID_ARG, "Not enough relinearization keys");
+            return ctx->relin;
+        }
+        require(kind == GSB_KEY_GALOIS, GSB_E_INVALID_ARG, "key kind");
+        auto it = ctx->galois.find(elt);
+        require(it != ctx->galois.end(), GSB_E_INVALID_ARG, "Galois key not present");
+        return it->second;
+    }
+
+    static gsb_ws *pick_ws(gsb_ctx *ctx, gsb_ws *ws)
+    {
+        require(ws == nullptr || ws->ctx == ctx, GSB_E_INVALID_ARG, "workspace belongs to another context");
+        return ws ? ws : &ctx->default_ws;
+    }
+
+    static void check_batch(const gsb_ctx *ctx, size_t batch, size_t L, size_t min_L)
+    {
+        require(ctx != nullptr, GSB_E_INVALID_ARG, "ctx is null");
+        require(batch >= 1 && batch <= (size_t(1) << 20), GSB_E_INVALID_ARG, "batch out of range");
+        require(L >= min_L && L <= ctx->L0, GSB_E_INVALID_ARG, "no ciphertext level with that many limbs");
+    }
+} // namespace gsb
+
+using namespace gsb;
+
+extern "C" {
+
+int gsb_poly_op_host(
+    gsb_ctx *ctx, int op, const uint64_t *a, const uint64_t *b, const uint64_t *scalars, uint64_t *out, size_t n_polys,
+    size_t n_limbs, size_t limb_offset)
+{
+    int rc = GSB_OK;
+    int g = guarded([&] {
+        check_limbs(ctx, n_polys, n_limbs, limb_offset);
+        require(a != nullptr && out != nullptr, GSB_E_INVALID_ARG, "null operand");
+        const bool binary = op == GSB_OP_DYADIC || op == GSB_OP_ADD || op == GSB_OP_SUB;
+        require(!binary || b != nullptr, GSB_E_INVALID_ARG, "operand2 is null");
+        std::lock_guard<std::mutex> lock(ctx->host_mu);
+        GSB_CUDA_CHECK(cudaSetDevice(ctx->device));
+        const size_t words = n_polys * n_limbs * ctx->N, bytes = words * sizeof(uint64_t);
+        uint64_t *d = static_cast<uint64_t *>(ctx->host_io.reserve(3 * bytes));
+        GSB_CUDA_CHECK(cudaMemcpyAsync(d, a, bytes, cudaMemcpyHostToDevice, nullptr));
+        if (binary)
+            GSB_CUDA_CHECK(cudaMemcpyAsync(d + words, b, bytes, cudaMemcpyHostToDevice, nullptr));
+        rc = gsb_poly_op_dev(ctx, op, d, binary ? d + words : nullptr, scalars, d + 2 * words, n_polys, n_limbs, limb_offset, nullptr);
+        if (rc == GSB_OK)
+        {
+            GSB_CUDA_CHECK(cudaMemcpyAsync(out, d + 2 * words, bytes, cudaMemcpyDeviceToHost, nullptr));
+            GSB_CUDA_CHECK(cudaStreamSynchronize(nullptr));
+        }
+    });
+    return g != GSB_OK ? g : rc;
+}
+
+int gsb_key_upload(gsb_ctx *ctx, int kind, uint32_t galois_elt, const uint64_t *key_host, size_t n_bundles)
+{
+    return guarded([&] {
+        require(ctx != nullptr && key_host != nullptr, GSB_E_INVALID_ARG, "null argument");
+        require(kind == GSB_KEY_RELIN || kind == GSB_KEY_GALOIS, GSB_E_INVALID_ARG, "key kind");
+        // keygenerator.cpp:333-343: one PublicKey per bundle of the first-level modulus
+        const size_t beta0 = (ctx->L0 + ctx->k - 1) / ctx->k;
+        require(n_bundles == beta0, GSB_E_INVALID_ARG, "kswitch_keys is not valid for encryption parameters");
+        if (kind == GSB_KEY_GALOIS)
+            (void)ctx->galois_table(galois_elt); // validates the element and builds its permutation
+        GSB_CUDA_CHECK(cudaSetDevice(ctx->device));
+        const size_t words = n_bundles * 2 * ctx->K * ctx->N;
+        // is_buffer_valid (valcheck.cpp): every key word must be a canonical residue
+        for (size_t j = 0; j < n_bundles * 2; j++)
+            for (size_t i = 0; i < ctx->K; i++)
+            {
+                const uint64_t q = ctx->tables[i].mod.q;
+                const uint64_t *p = key_host + (j * ctx->K + i) * ctx->N;
+                for (size_t d = 0; d < ctx->N; d++)
+                    require(p[d] < q, GSB_E_INVALID_ARG, "kswitch_keys is not valid for encryption parameters");
+            }
+        uint64_t *d = nullptr;
+        GSB_CUDA_CHECK(cudaMalloc(reinterpret_cast<void **>(&d), words * sizeof(uint64_t)));
+        GSB_CUDA_CHECK(cudaMemcpy(d, key_host, words * sizeof(uint64_t), cudaMemcpyHostToDevice));
+        std::lock_guard<std::mutex> lock(ctx->mu);
+        SwitchKey &slot = kind == GSB_KEY_RELIN ? ctx->relin : ctx->galois[galois_elt];
+        if (slot.d)
+            cudaFree(slot.d);
+        slot.d = d;
+        slot.bundles = n_bundles;
+    });
+}
+
+int gsb_key_drop(gsb_ctx *ctx, int kind, uint32_t galois_elt)
+{
+    return guarded([&] {
+        require(ctx != nullptr, GSB_E_INVALID_ARG, "ctx is null");
+        std::lock_guard<std::mutex> lock(ctx->mu);
+        if (kind == GSB_KEY_RELIN)
+        {
+            cudaFree(ctx->relin.d);
+            ctx->relin = SwitchKey();
+        }
+        else
+        {
+            auto it = ctx->galois.find(galois_elt);
+            require(it != ctx->galois.end(), GSB_E_INVALID_ARG, "Galois key not present");
+            cudaFree(it->second.d);
+            ctx->galois.erase(it);
+        }
+    });
+}
+
+int gsb_galois_elt_from_step(const gsb_ctx *ctx, int step, uint32_t *elt)
+{
+    return guarded([&] {
+        require(ctx != nullptr && elt != nullptr, GSB_E_INVALID_ARG, "null argument");
+        const uint32_t e = host::galois_elt_from_step(ctx->logn, step);
+        require(e != 0, GSB_E_INVALID_ARG, "step count too large"); // util/galois.cpp:62-65
+        *elt = e;
+    });
+}
+
+int gsb_galois_table(const gsb_ctx *ctx, uint32_t galois_elt, uint32_t *table_out)
+{
+    return guarded([&] {
+        require(ctx != nullptr && table_out != nullptr, GSB_E_INVALID_ARG, "null argument");
+        require((galois_elt & 1u) && galois_elt < 2u * ctx->N, GSB_E_INVALID_ARG, "Galois element is not valid");
+        std::vector<uint32_t> t;
+        host::galois_table_ntt(ctx->logn, galois_elt, t);
+        memcpy(table_out, t.data(), t.size() * sizeof(uint32_t));
+    });
+}
+
+int gsb_ckks_multiply_dev(gsb_ctx *ctx, const uint64_t *a, const uint64_t *b, uint64_t *out, size_t batch, size_t L, void *stream)
+{
+    return guarded([&] {
+        check_batch(ctx, batch, L, 1);
+        require(a && b && out, GSB_E_INVALID_ARG, "null operand");
+        ckks_multiply_core(ctx, a, b, out, batch, L, static_cast<cudaStream_t>(stream));
+        GSB_CUDA_CHECK(cudaGetLastError());
+    });
+}
+
+int gsb_switch_key_dev(
+    gsb_ctx *ctx, gsb_ws *ws, uint64_t *enc, size_t enc_size, const uint64_t *target, size_t target_stride, int key_kind,
+    uint32_t galois_elt, size_t batch, size_t L, void *stream)
+{
+    return guarded([&] {
+        check_batch(ctx, batch, L, 1);
+        require(enc && target && enc_size >= 2, GSB_E_INVALID_ARG, "invalid ciphertext");
+        const SwitchKey &key = find_key(ctx, key_kind, galois_elt);
+        gsb_ws *w = pick_ws(ctx, ws);
+        cudaStream_t st = static_cast<cudaStream_t>(stream);
+        const size_t N = ctx->N, per = ks_words_per_ct(ctx, L), chunk = chunk_for(per, batch);
+        void *scratch = w->reserve((chunk * per + 1024) * sizeof(uint64_t));
+        for (size_t b0 = 0; b0 < batch; b0 += chunk)
+        {
+            const size_t B = std::min(chunk, batch - b0);
+            uint64_t *e = enc + b0 * enc_size * L * N;
+            const KsOutput o{ e, enc_size * L * N, L * N, e, enc_size * L * N, L * N, nullptr };
+            GSB_DISPATCH_LOGN(ctx->logn, switch_key_core<LOGN>(ctx, scratch, target + b0 * target_stride, target_stride, key, o, B, L, st));
+        }
+        GSB_CUDA_CHECK(cudaGetLastError());
+    });
+}
+
+int gsb_relinearize_dev(gsb_ctx *ctx, gsb_ws *ws, const uint64_t *in, uint64_t *out, size_t batch, size_t L, void *stream)
+{
+    return guarded([&] {
+        check_batch(ctx, batch, L, 1);
+        require(in && out, GSB_E_INVALID_ARG, "null operand");
+        const SwitchKey &key = find_key(ctx, GSB_KEY_RELIN, 0);
+        gsb_ws *w = pick_ws(ctx, ws);
+        cudaStream_t st = static_cast<cudaStream_t>(stream);
+        const size_t N = ctx->N, LN = L * N, per = ks_words_per_ct(ctx, L), chunk = chunk_for(per, batch);
+        void *scratch = w->reserve((chunk * per + 1024) * sizeof(uint64_t));
+        for (size_t b0 = 0; b0 < batch; b0 += chunk)
+        {
+            const size_t B = std::min(chunk, batch - b0);
+            const uint64_t *i3 = in + b0 * 3 * LN;
+            const KsOutput o{ i3, 3 * LN, LN, out + b0 * 2 * LN, 2 * LN, LN, nullptr };
+            GSB_DISPATCH_LOGN(ctx->logn, switch_key_core<LOGN>(ctx, scratch, i3 + 2 * LN, 3 * LN, key, o, B, L, st));
+        }
+        GSB_CUDA_CHECK(cudaGetLastError());
+    });
+}
+
+int gsb_rescale_dev(gsb_ctx *ctx, gsb_ws *ws, const uint64_t *in, uint64_t *out, size_t batch, size_t size, size_t L, void *stream)
+{
+    return guarded([&] {
+        check_batch(ctx, batch, L, 2); // evaluator.cpp:845-848: needs a next level
+        require(in && out && size >= 1 && size <= 16, GSB_E_INVALID_ARG, "invalid ciphertext");
+        gsb_ws *w = pick_ws(ctx, ws);
+        const size_t n_polys = batch * size;
+        uint64_t *t = static_cast<uint64_t *>(w->reserve(n_polys * ctx->N * sizeof(uint64_t)));
+        GSB_DISPATCH_LOGN(ctx->logn, rescale_core<LOGN>(ctx, t, in, out, n_polys, L, static_cast<cudaStream_t>(stream)));
+        GSB_CUDA_CHECK(cudaGetLastError());
+    });
+}
+
+int gsb_apply_galois_dev(gsb_ctx *ctx, gsb_ws *ws, uint32_t galois_elt, const uint64_t *in, uint64_t *out, size_t batch, size_t L, void *stream)
+{
+    return guarded([&] {
+        check_batch(ctx, batch, L, 1);
+        require(in && out, GSB_E_INVALID_ARG, "null operand");
+        const uint32_t *table = ctx->galois_table(galois_elt);
+        const SwitchKey &key = find_key(ctx, GSB_KEY_GALOIS, galois_elt);
+        gsb_ws *w = pick_ws(ctx, ws);
+        cudaStream_t st = static_cast<cudaStream_t>(stream);
+        const size_t N = ctx->N, LN = L * N, per = ks_words_per_ct(ctx, L) + LN, chunk = chunk_for(per, batch);
+        char *scratch = static_cast<char *>(w->reserve((chunk * per + 1024) * sizeof(uint64_t)));
+        for (size_t b0 = 0; b0 < batch; b0 += chunk)
+        {
+            const size_t B = std::min(chunk, batch - b0);
+            const uint64_t *i2 = in + b0 * 2 * LN;
+            // temp = apply_galois_ntt(c1) (evaluator.cpp:1920); c0's permutation (:1913-1917) and the
+            // zeroed c1 (:1928) are folded into the mod-down epilogue.
+            uint64_t *tperm = reinterpret_cast<uint64_t *>(scratch);
+            gather_core(ctx, i2 + LN, 2 * LN, tperm, table, B, L, st);
+            const KsOutput o{ i2, 2 * LN, LN, out + b0 * 2 * LN, 2 * LN, LN, table };
+            GSB_DISPATCH_LOGN(ctx->logn, switch_key_core<LOGN>(ctx, scratch + B * LN * sizeof(uint64_t), tperm, LN, key, o, B, L, st));
+        }
+        GSB_CUDA_CHECK(cudaGetLastError());
+    });
+}
+
+int gsb_mul_relin_rescale_dev(
+    gsb_ctx *ctx, gsb_ws *ws, const uint64_t *a, const uint64_t *b, uint64_t *out, size_t batch, size_t L, void *stream)
+{
+    return guarded([&] {
+        check_batch(ctx, batch, L, 2);
+        require(a && b && out, GSB_E_INVALID_ARG, "null operand");
+        const SwitchKey &key = find_key(ctx, GSB_KEY_RELIN, 0);
+        gsb_ws *w = pick_ws(ctx, ws);
+        cudaStream_t st = static_cast<cudaStream_t>(stream);
+        const size_t N = ctx->N, LN = L * N;
+        const size_t per = ks_words_per_ct(ctx, L) + 3 * LN + 2 * LN + 2 * N, chunk = chunk_for(per, batch);
+        void *scratch = w->reserve((chunk * per + 2048) * sizeof(uint64_t));
+        for (size_t b0 = 0; b0 < batch; b0 += chunk)
+        {
+            const size_t B = std::min(chunk, batch - b0);
+            Arena ar(scratch);
+            uint64_t *c3 = ar.words(B * 3 * LN), *c2 = ar.words(B * 2 * LN), *t = ar.words(B * 2 * N);
+            ckks_multiply_core(ctx, a + b0 * 2 * LN, b + b0 * 2 * LN, c3, B, L, st);
+            const KsOutput o{ c3, 3 * LN, LN, c2, 2 * LN, LN, nullptr };
+            GSB_DISPATCH_LOGN(ctx->logn, switch_key_core<LOGN>(ctx, ar.base + ar.off, c3 + 2 * LN, 3 * LN, key, o, B, L, st));
+            GSB_DISPATCH_LOGN(ctx->logn, rescale_core<LOGN>(ctx, t, c2, out + b0 * 2 * (L - 1) * N, B * 2, L, st));
+        }
+        GSB_CUDA_CHECK(cudaGetLastError());
+    });
+}
+
+// ---- host-buffer forms -----------------------------------------------------------------------------
+static int host_call(
+    gsb_ctx *ctx, const uint64_t *in0, size_t in0_words, const uint64_t *in1, size_t in1_words, uint64_t *out, size_t out_words,
+    const std::function<int(gsb_ws *, uint64_t *, uint64_t *, uint64_t *)> &run)
+{
+    int rc = GSB_OK;
+    int g = guarded([&] {
+        require(ctx != nullptr, GSB_E_INVALID_ARG, "ctx is null");
+        require(in0 != nullptr && out != nullptr && (in1 != nullptr || in1_words == 0), GSB_E_INVALID_ARG, "null operand");
+        std::lock_guard<std::mutex> lock(ctx->host_mu);
+        GSB_CUDA_CHECK(cudaSetDevice(ctx->device));
+        uint64_t *d = static_cast<uint64_t *>(ctx->host_io.reserve((in0_words + in1_words + out_words) * sizeof(uint64_t)));
+        GSB_CUDA_CHECK(cudaMemcpyAsync(d, in0, in0_words * sizeof(uint64_t), cudaMemcpyHostToDevice, nullptr));
+        if (in1_words)
+            GSB_CUDA_CHECK(cudaMemcpyAsync(d + in0_words, in1, in1_words * sizeof(uint64_t), cudaMemcpyHostToDevice, nullptr));
+        rc = run(&ctx->default_ws, d, d + in0_words, d + in0_words + in1_words);
+        if (rc == GSB_OK)
+        {
+            GSB_CUDA_CHECK(cudaMemcpyAsync(out, d + in0_words + in1_words, out_words * sizeof(uint64_t), cudaMemcpyDeviceToHost, nullptr));
+            GSB_CUDA_CHECK(cudaStreamSynchronize(nullptr));
+        }
+    });
+    return g != GSB_OK ? g : rc;
+}
+
+int gsb_ckks_multiply_host(gsb_ctx *ctx, const uint64_t *a, const uint64_t *b, uint64_t *out, size_t batch, size_t L)
+{
+    const size_t w = ctx ? batch * L * ctx->N : 0;
+    return host_call(ctx, a, 2 * w, b, 2 * w, out, 3 * w, [&](gsb_ws *, uint64_t *da, uint64_t *db, uint64_t *dout) {
+        return gsb_ckks_multiply_dev(ctx, da, db, dout, batch, L, nullptr);
+    });
+}
+
+int gsb_relinearize_host(gsb_ctx *ctx, const uint64_t *in, uint64_t *out, size_t batch, size_t L)
+{
+    const size_t w = ctx ? batch * L * ctx->N : 0;
+    return host_call(ctx, in, 3 * w, nullptr, 0, out, 2 * w, [&](gsb_ws *ws, uint64_t *di, uint64_t *, uint64_t *dout) {
+        return gsb_relinearize_dev(ctx, ws, di, dout, batch, L, nullptr);
+    });
+}
+
+int gsb_rescale_host(gsb_ctx *ctx, const uint64_t *in, uint64_t *out, size_t batch, size_t size, size_t L)
+{
+    const size_t w = ctx ? batch * size * ctx->N : 0;
+    return host_call(ctx, in, w * L, nullptr, 0, out, L ? w * (L - 1) : 0, [&](gsb_ws *ws, uint64_t *di, uint64_t *, uint64_t *dout) {
+        return gsb_rescale_dev(ctx, ws, di, dout, batch, size, L, nullptr);
+    });
+}
+
+int gsb_apply_galois_host(gsb_ctx *ctx, uint32_t galois_elt, const uint64_t *in, uint64_t *out, size_t batch, size_t L)
+{
+    const size_t w = ctx ? batch * L * ctx->N : 0;
+    return host_call(ctx, in, 2 * w, nullptr, 0, out, 2 * w, [&](gsb_ws *ws, uint64_t *di, uint64_t *, uint64_t *dout) {
+        return gsb_apply_galois_dev(ctx, ws, galois_elt, di, dout, batch, L, nullptr);
+    });
+}
+
+int gsb_mul_relin_rescale_host(gsb_ctx *ctx, const uint64_t *a, const uint64_t *b, uint64_t *out, size_t batch, size_t L)
+{
+    const size_t w = ctx ? batch * ctx->N : 0;
+    return host_call(ctx, a, 2 * w * L, b, 2 * w * L, out, L ? 2 * w * (L - 1) : 0, [&](gsb_ws *ws, uint64_t *da, uint64_t *db, uint64_t *dout) {
+        return gsb_mul_relin_rescale_dev(ctx, ws, da, db, dout, batch, L, nullptr);
+    });
+}
+
+} // extern "C"

@@ -1,0 +1,492 @@
+// Device kernels and NTT prologue / epilogue functors of the CKKS evaluator path.
+// See gsb_evaluator.cuh for the pipeline that launches them.
+#pragma once
+#include "ntt_kernels.cuh"
+
+namespace gsb
+{
+    // Geometry + constants of one key switch at level L, passed to kernels by value.
+    // ext slot kap in [0, E): kap < L is ciphertext limb kap (modulus index kap), kap >= L is
+    // special prime kap-L (modulus index L0 + kap - L)  (evaluator.cpp:2316-2317).
+    struct KsDev
+    {
+        const LimbC *limb;       // [K]
+        const uint64_t *modup_a; // [beta][k][2]
+        const uint64_t *modup_b; // [beta][k][E]
+        const uint64_t *inv_hat; // [k][2]
+        const uint64_t *neg_hat; // [L][k]
+        const uint64_t *inv_p;   // [L][2]
+        uint32_t L, L0, k, E, beta, N;
+        GSB_DEV int ext_mod(int kap) const { return kap < static_cast<int>(L) ? kap : static_cast<int>(L0) + kap - static_cast<int>(L); }
+    };
+
+    // ---- combinator: any prologue with any epilogue -------------------------------------------------
+    // A functor type F provides `struct Args` (trivially copyable, with `bool skip(y, z) const` for
+    // prologues) and a constructor F(const Args&, y, z, mod, const LimbC&, N).
+    template <class ProF, class EpiF>
+    struct IoPair
+    {
+        typename ProF::Args pa;
+        typename EpiF::Args ea;
+        GSB_DEV bool skip(int y, int z) const { return pa.skip(y, z); }
+        struct Pro : ProF
+        {
+            GSB_DEV Pro(const IoPair &io, int y, int z, int mod, const LimbC &c, uint32_t N) : ProF(io.pa, y, z, mod, c, N) {}
+        };
+        struct Epi : EpiF
+        {
+            GSB_DEV Epi(const IoPair &io, int y, int z, int mod, const LimbC &c, uint32_t N) : EpiF(io.ea, y, z, mod, c, N) {}
+        };
+    };
+
+    struct PlainArgs
+    {
+        const uint64_t *base;
+        size_t zs;
+        GSB_DEV bool skip(int, int) const { return false; }
+    };
+    struct PlainLoad : PlainPro
+    {
+        typedef PlainArgs Args;
+        GSB_DEV PlainLoad(const Args &a, int y, int z, int, const LimbC &, uint32_t N) : PlainPro(a.base, a.zs, y, z, N) {}
+    };
+    struct PlainStoreArgs
+    {
+        uint64_t *base;
+        size_t zs;
+    };
+    template <int MODE>
+    struct PlainStore : PlainEpi<MODE>
+    {
+        typedef PlainStoreArgs Args;
+        GSB_DEV PlainStore(const Args &a, int y, int z, int, const LimbC &c, uint32_t N) : PlainEpi<MODE>(a.base, a.zs, y, z, c, N) {}
+    };
+
+    // ---- mod-up prologue (modup_to_single_rns, multi_special_primes.cpp:80-148) --------------------
+    // Source = coefficient-form bundle limbs coef[b][s0 .. s0+cnt); destination modulus = ext slot kap.
+    struct ModupCore
+    {
+        const uint64_t *src; // coef + (b*L + s0)*N
+        const uint64_t *a;   // modup_a + (j*k)*2
+        const uint64_t *bb;  // modup_b + (j*k)*E + kap
+        const LimbC *limb;   // limb + s0
+        uint64_t q, cr0, cr1;
+        uint32_t N, E;
+        int cnt;
+        bool reduce; // single-limb bundle with q_src > q_dst -> barrett_reduce_63 (:104-107)
+        GSB_DEV ModupCore(const KsDev &ks, const uint64_t *coef, int b, int j, int kap, const LimbC &c)
+        {
+            const int s0 = j * static_cast<int>(ks.k);
+            const int s1 = s0 + static_cast<int>(ks.k) < static_cast<int>(ks.L) ? s0 + static_cast<int>(ks.k) : static_cast<int>(ks.L);
+            N = ks.N;
+            E = ks.E;
+            cnt = s1 - s0;
+            src = coef + (static_cast<size_t>(b) * ks.L + s0) * N;
+            a = ks.modup_a + static_cast<size_t>(j) * ks.k * 2;
+            bb = ks.modup_b + static_cast<size_t>(j) * ks.k * E + kap;
+            limb = ks.limb + s0;
+            q = c.q;
+            cr0 = c.cr0;
+            cr1 = c.cr1;
+            reduce = cnt == 1 && limb[0].q > q;
+        }
+        GSB_DEV uint64_t convert(uint32_t d) const
+        {
+            if (cnt == 1)
+            {
+                const uint64_t v = src[d];
+                return reduce ? barrett63(v, q, cr1) : v;
+            }
+            uint64_t lo = 0, hi = 0;
+            for (int i = 0; i < cnt; i++)
+            {
+                const uint64_t t = mulmod_shoup(src[static_cast<size_t>(i) * N + d], __ldg(a + 2 * i), __ldg(a + 2 * i + 1), limb[i].q);
+                mac128(lo, hi, t, __ldg(bb + static_cast<size_t>(i) * E));
+            }
+            return barrett128(lo, hi, q, cr0, cr1);
+        }
+        GSB_DEV uint64_t load(uint32_t d) const { return convert(d); }
+        GSB_DEV void load2(uint32_t d, uint64_t &x, uint64_t &y) const
+        {
+            if (cnt == 1)
+            {
+                const ulonglong2 v = *reinterpret_cast<const ulonglong2 *>(src + d);
+                x = reduce ? barrett63(v.x, q, cr1) : v.x;
+                y = reduce ? barrett63(v.y, q, cr1) : v.y;
+            }
+            else
+            {
+                x = convert(d);
+                y = convert(d + 1);
+            }
+        }
+    };
+
+    // grid: y = ext slot kap, z = b*beta + j; slots inside the source bundle are skipped.
+    struct ModupArgs
+    {
+        KsDev ks;
+        const uint64_t *coef;
+        GSB_DEV bool skip(int y, int z) const
+        {
+            const int j = z % static_cast<int>(ks.beta);
+            const int s0 = j * static_cast<int>(ks.k);
+            return y >= s0 && y < s0 + static_cast<int>(ks.k) && y < static_cast<int>(ks.L);
+        }
+    };
+    struct ModupLoad : ModupCore
+    {
+        typedef ModupArgs Args;
+        GSB_DEV ModupLoad(const Args &a, int y, int z, int, const LimbC &c, uint32_t)
+            : ModupCore(a.ks, a.coef, z / static_cast<int>(a.ks.beta), z % static_cast<int>(a.ks.beta), y, c)
+        {}
+    };
+
+    // ---- mod-down prologue (rescale_special_rns_inplace steps 1-2, multi_special_primes.cpp:253-282)
+    // grid: y = ciphertext limb i, z = b*2 + l.  red = [B*2][E][N]; its special slots hold the lazy
+    // inverse NTT of the reduced accumulators (evaluator.cpp:2353-2357).
+    struct MdLoadArgs
+    {
+        KsDev ks;
+        const uint64_t *red;
+        GSB_DEV bool skip(int, int) const { return false; }
+    };
+    struct MdLoad
+    {
+        typedef MdLoadArgs Args;
+        const uint64_t *sp;  // red + (z*E + L)*N
+        const uint64_t *ih;  // inv_hat
+        const uint64_t *nh;  // neg_hat + i*k
+        const LimbC *plimb;  // limb + L0
+        uint64_t q, cr0, cr1;
+        uint32_t N;
+        int k;
+        GSB_DEV MdLoad(const Args &a, int y, int z, int, const LimbC &c, uint32_t N_)
+        {
+            sp = a.red + (static_cast<size_t>(z) * a.ks.E + a.ks.L) * N_;
+            ih = a.ks.inv_hat;
+            nh = a.ks.neg_hat + static_cast<size_t>(y) * a.ks.k;
+            plimb = a.ks.limb + a.ks.L0;
+            q = c.q;
+            cr0 = c.cr0;
+            cr1 = c.cr1;
+            N = N_;
+            k = static_cast<int>(a.ks.k);
+        }
+        GSB_DEV uint64_t load(uint32_t d) const
+        {
+            if (k == 1)
+            {
+                // :268-275: negate(barrett_reduce_63(c_p)) then barrett_reduce_128 of (v, 0)
+                const uint64_t p = plimb[0].q;
+                const uint64_t v = neg_mod(barrett63(sp[d], p, plimb[0].cr1), p);
+                return barrett128(v, 0, q, cr0, cr1);
+            }
+            uint64_t lo = 0, hi = 0;
+            for (int j = 0; j < k; j++)
+            {
+                const uint64_t t = mulmod_shoup(sp[static_cast<size_t>(j) * N + d], __ldg(ih + 2 * j), __ldg(ih + 2 * j + 1), plimb[j].q);
+                mac128(lo, hi, t, __ldg(nh + j));
+            }
+            return barrett128(lo, hi, q, cr0, cr1);
+        }
+        GSB_DEV void load2(uint32_t d, uint64_t &x, uint64_t &y) const
+        {
+            x = load(d);
+            y = load(d + 1);
+        }
+    };
+
+    // ---- mod-down epilogue (multi_special_primes.cpp:291-302 + evaluator.cpp:2363-2366) -------------
+    // val = MulModShoup_{q_i}(red[z][i][d] + corr_ntt[d]; P^-1);  dst = add_mod(val, addend).
+    // addend: add_src[b][l][i][d]; with a Galois table, component 0 is gathered through it and
+    // component 1 is zero (apply_galois_inplace, evaluator.cpp:1913-1928).
+    struct MdStoreArgs
+    {
+        KsDev ks;
+        const uint64_t *red;
+        const uint64_t *add_src;
+        size_t add_bs, add_ls; // word strides: ciphertext, component
+        uint64_t *dst;
+        size_t dst_bs, dst_ls;
+        const uint32_t *table; // nullptr unless Galois
+    };
+    struct MdStore
+    {
+        typedef MdStoreArgs Args;
+        const uint64_t *r;
+        const uint64_t *s; // nullptr -> addend 0
+        uint64_t *o;
+        const uint32_t *table;
+        uint64_t q, ip, ips;
+        GSB_DEV MdStore(const Args &a, int y, int z, int, const LimbC &c, uint32_t N)
+        {
+            const int b = z >> 1, l = z & 1;
+            r = a.red + (static_cast<size_t>(z) * a.ks.E + y) * N;
+            o = a.dst + static_cast<size_t>(b) * a.dst_bs + static_cast<size_t>(l) * a.dst_ls + static_cast<size_t>(y) * N;
+            table = a.table;
+            s = (a.table && l == 1) ? nullptr
+                                    : a.add_src + static_cast<size_t>(b) * a.add_bs + static_cast<size_t>(l) * a.add_ls + static_cast<size_t>(y) * N;
+            q = c.q;
+            ip = a.ks.inv_p[2 * y];
+            ips = a.ks.inv_p[2 * y + 1];
+        }
+        GSB_DEV uint64_t one(uint32_t d, uint64_t v) const
+        {
+            const uint64_t val = mulmod_shoup(r[d] + v, ip, ips, q);
+            const uint64_t addend = s ? (table ? s[__ldg(table + d)] : s[d]) : 0;
+            return add_mod(val, addend, q);
+        }
+        GSB_DEV void store(uint32_t d, uint64_t v, int) const { o[d] = one(d, v); }
+        GSB_DEV void store2(uint32_t d, uint64_t a, uint64_t b, int) const
+        {
+            *reinterpret_cast<ulonglong2 *>(o + d) = make_ulonglong2(one(d, a), one(d + 1, b));
+        }
+    };
+
+    // ---- rescale (RNSTool::divide_and_round_q_last_ntt_inplace, util/rns.cpp:777-851) --------------
+    // Stage 1 epilogue: strict inverse NTT of the last limb, then barrett_reduce_63(x + q_last/2)
+    // (:798-806).  t = [n_polys][N].
+    struct RsLastStore
+    {
+        typedef PlainStoreArgs Args;
+        uint64_t *p;
+        uint64_t q, cr1, half;
+        GSB_DEV RsLastStore(const Args &a, int y, int z, int, const LimbC &c, uint32_t N)
+            : p(a.base + static_cast<size_t>(z) * a.zs + static_cast<size_t>(y) * N), q(c.q), cr1(c.cr1), half(c.q >> 1)
+        {}
+        GSB_DEV uint64_t one(uint64_t v) const
+        {
+            v -= (v >= q) ? q : 0; // util/ntt.h:328-333
+            return barrett63(v + half, q, cr1);
+        }
+        GSB_DEV void store(uint32_t d, uint64_t v, int) const { p[d] = one(v); }
+        GSB_DEV void store2(uint32_t d, uint64_t a, uint64_t b, int) const
+        {
+            *reinterpret_cast<ulonglong2 *>(p + d) = make_ulonglong2(one(a), one(b));
+        }
+    };
+
+    // Stage 2 prologue (:811-827): (t mod q_i if q_i < q_last) + (q_i - half mod q_i).
+    // grid: y = limb i in [0, L-1), z = polynomial.
+    struct RsLoadArgs
+    {
+        const uint64_t *t;        // [n_polys][N]
+        const uint64_t *neg_half; // [L-1]
+        uint64_t q_last;
+        GSB_DEV bool skip(int, int) const { return false; }
+    };
+    struct RsLoad
+    {
+        typedef RsLoadArgs Args;
+        const uint64_t *t;
+        uint64_t q, cr1, nh;
+        bool reduce;
+        GSB_DEV RsLoad(const Args &a, int y, int z, int, const LimbC &c, uint32_t N)
+            : t(a.t + static_cast<size_t>(z) * N), q(c.q), cr1(c.cr1), nh(a.neg_half[y]), reduce(c.q < a.q_last)
+        {}
+        GSB_DEV uint64_t one(uint64_t v) const { return (reduce ? barrett63(v, q, cr1) : v) + nh; }
+        GSB_DEV uint64_t load(uint32_t d) const { return one(t[d]); }
+        GSB_DEV void load2(uint32_t d, uint64_t &x, uint64_t &y) const
+        {
+            const ulonglong2 v = *reinterpret_cast<const ulonglong2 *>(t + d);
+            x = one(v.x);
+            y = one(v.y);
+        }
+    };
+
+    // Stage 2 epilogue (:836-848): out = multiply_uint_mod(in + 4q - ntt_lazy, q_last^-1 mod q_i).
+    struct RsStoreArgs
+    {
+        const uint64_t *in; // [n_polys][L][N]
+        uint64_t *out;      // [n_polys][L-1][N]
+        const uint64_t *inv_qlast;
+        uint32_t L;
+    };
+    struct RsStore
+    {
+        typedef RsStoreArgs Args;
+        const uint64_t *in;
+        uint64_t *out;
+        uint64_t q, cr0, cr1, four_q, inv;
+        GSB_DEV RsStore(const Args &a, int y, int z, int, const LimbC &c, uint32_t N)
+            : in(a.in + (static_cast<size_t>(z) * a.L + y) * N), out(a.out + (static_cast<size_t>(z) * (a.L - 1) + y) * N),
+              q(c.q), cr0(c.cr0), cr1(c.cr1), four_q(c.q << 2), inv(a.inv_qlast[y])
+        {}
+        GSB_DEV uint64_t one(uint64_t u, uint64_t v) const { return mul_mod(u + four_q - v, inv, q, cr0, cr1); }
+        GSB_DEV void store(uint32_t d, uint64_t v, int) const { out[d] = one(in[d], v); }
+        GSB_DEV void store2(uint32_t d, uint64_t a, uint64_t b, int) const
+        {
+            const ulonglong2 u = *reinterpret_cast<const ulonglong2 *>(in + d);
+            *reinterpret_cast<ulonglong2 *>(out + d) = make_ulonglong2(one(u.x, a), one(u.y, b));
+        }
+    };
+
+    // ---- epilogue that leaves the transform in registers (used by the fused inner product) --------
+    struct KeepInRegs
+    {
+        GSB_DEV void store(uint32_t, uint64_t, int) const {}
+        GSB_DEV void store2(uint32_t, uint64_t, uint64_t, int) const {}
+    };
+
+    // ---- fused (last NTT pass + key inner product + lazy reduction) --------------------------------
+    // evaluator.cpp:2315-2335 (step 3) and :2341-2350 (step 4, Barrett part).  One CTA owns a tile of
+    // ext slot kap of ciphertext b and loops over the bundles: the lazy forward NTT of the mod-up'd
+    // bundle (its last pass when N >= 2^13, the whole transform otherwise) finishes in registers and
+    // is multiplied straight into two 128-bit accumulators per coefficient (FMAU128), so neither the
+    // transformed operand nor the accumulators ever touch HBM.  Bundles that contain kap use the
+    // original NTT-form target limb (:2319-2320).  grid = (B, tiles per limb, E): ciphertexts of a
+    // batch run side by side on the same key tile, so a key word is fetched from HBM once per batch.
+    struct KsMacArgs
+    {
+        KsDev ks;
+        const uint64_t *target; // ciphertext b at target + b*target_stride, [L][N], NTT form
+        size_t target_stride;
+        const uint64_t *coef; // [B][L][N] coefficient form (single-pass prologue)
+        const uint64_t *ext1; // [B][beta][E][N] column-pass output (two-pass)
+        const uint64_t *key;  // [beta0][2][K][N]
+        uint64_t *red;        // [B][2][E][N]
+        uint32_t K;
+    };
+
+    template <int LOGN>
+    struct MacPlan
+    {
+        static constexpr bool two_pass = Split<LOGN>::two_pass;
+        static constexpr int T = two_pass ? 8 : Split<LOGN>::T1;
+        static constexpr int G_HI = two_pass ? LOGN - Split<LOGN>::A - 1 : LOGN - 1;
+    };
+
+    template <int LOGN>
+    __global__ void __launch_bounds__(1 << MacPlan<LOGN>::T) ks_mac_kernel(KsMacArgs p, NttTables tab)
+    {
+        typedef MacPlan<LOGN> MP;
+        constexpr int T = MP::T;
+        const KsDev &ks = p.ks;
+        const int b = blockIdx.x, tile = blockIdx.y, kap = blockIdx.z;
+        const uint32_t tid = threadIdx.x, N = tab.N;
+        const int mod = ks.ext_mod(kap);
+        const LimbC c = tab.limb[mod];
+        const Twiddle *WW = tab.WW + static_cast<size_t>(mod) * N;
+        const ContigMap<T> map{ N };
+        const uint32_t d0 = map.coeff(tile, tid * 8);
+        uint64_t lo[2][8], hi[2][8];
+#pragma unroll
+        for (int r = 0; r < 8; r++)
+            lo[0][r] = hi[0][r] = lo[1][r] = hi[1][r] = 0;
+        int parity = 0;
+        const KeepInRegs keep;
+        for (int j = 0; j < static_cast<int>(ks.beta); j++)
+        {
+            const int s0 = j * static_cast<int>(ks.k);
+            uint64_t x[8];
+            if (kap >= s0 && kap < s0 + static_cast<int>(ks.k) && kap < static_cast<int>(ks.L))
+            {
+                const uint64_t *t = p.target + static_cast<size_t>(b) * p.target_stride + static_cast<size_t>(kap) * N + d0;
+#pragma unroll
+                for (int r = 0; r < 8; r += 2)
+                {
+                    const ulonglong2 v = *reinterpret_cast<const ulonglong2 *>(t + r);
+                    x[r] = v.x;
+                    x[r + 1] = v.y;
+                }
+            }
+            else
+            {
+                if constexpr (MP::two_pass)
+                {
+                    const PlainPro pro(p.ext1, static_cast<size_t>(ks.E) * N, kap, b * static_cast<int>(ks.beta) + j, N);
+                    fwd_rounds<T, MP::G_HI, 0, true, 0>(x, dyn_smem(), tid, tile, map, pro, keep, WW, c, parity);
+                }
+                else
+                {
+                    const ModupCore pro(ks, p.coef, b, j, kap, c);
+                    fwd_rounds<T, MP::G_HI, 0, true, 0>(x, dyn_smem(), tid, tile, map, pro, keep, WW, c, parity);
+                }
+                __syncthreads(); // the exchange buffers are reused by the next bundle
+            }
+            const uint64_t *k0 = p.key + (static_cast<size_t>(j * 2) * p.K + mod) * N + d0;
+            const uint64_t *k1 = k0 + static_cast<size_t>(p.K) * N;
+#pragma unroll
+            for (int r = 0; r < 8; r += 2)
+            {
+                const ulonglong2 u = __ldg(reinterpret_cast<const ulonglong2 *>(k0 + r));
+                const ulonglong2 v = __ldg(reinterpret_cast<const ulonglong2 *>(k1 + r));
+                mac128(lo[0][r], hi[0][r], x[r], u.x);
+                mac128(lo[0][r + 1], hi[0][r + 1], x[r + 1], u.y);
+                mac128(lo[1][r], hi[1][r], x[r], v.x);
+                mac128(lo[1][r + 1], hi[1][r + 1], x[r + 1], v.y);
+            }
+        }
+#pragma unroll
+        for (int l = 0; l < 2; l++)
+        {
+            uint64_t *o = p.red + ((static_cast<size_t>(b) * 2 + l) * ks.E + kap) * N + d0;
+#pragma unroll
+            for (int r = 0; r < 8; r += 2)
+                *reinterpret_cast<ulonglong2 *>(o + r) = make_ulonglong2(
+                    barrett128(lo[l][r], hi[l][r], c.q, c.cr0, c.cr1), barrett128(lo[l][r + 1], hi[l][r + 1], c.q, c.cr0, c.cr1));
+        }
+    }
+
+    // ---- CKKS tensor product of two size-2 ciphertexts (evaluator.cpp:493-520) ---------------------
+    // a, b = [B][2][L][N] -> out = [B][3][L][N]: c0 = a0*b0, c1 = a0*b1 + a1*b0, c2 = a1*b1.
+    struct CkksMulArgs
+    {
+        const uint64_t *a, *b;
+        uint64_t *out;
+        const LimbC *limb;
+        uint32_t N, L;
+        size_t pairs; // B*L*N/2
+    };
+
+    __global__ void __launch_bounds__(256) ckks_multiply_kernel(CkksMulArgs p)
+    {
+        const size_t LN = static_cast<size_t>(p.L) * p.N;
+        for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < p.pairs;
+             i += static_cast<size_t>(gridDim.x) * blockDim.x)
+        {
+            const size_t w = i << 1;
+            const size_t ct = w / LN, rem = w - ct * LN;
+            const LimbC c = p.limb[rem / p.N];
+            const uint64_t *pa = p.a + ct * 2 * LN + rem, *pb = p.b + ct * 2 * LN + rem;
+            uint64_t *po = p.out + ct * 3 * LN + rem;
+            const ulonglong2 a0 = *reinterpret_cast<const ulonglong2 *>(pa), a1 = *reinterpret_cast<const ulonglong2 *>(pa + LN);
+            const ulonglong2 b0 = *reinterpret_cast<const ulonglong2 *>(pb), b1 = *reinterpret_cast<const ulonglong2 *>(pb + LN);
+            ulonglong2 c0, c1, c2;
+            c0.x = mul_mod(a0.x, b0.x, c.q, c.cr0, c.cr1);
+            c0.y = mul_mod(a0.y, b0.y, c.q, c.cr0, c.cr1);
+            c1.x = add_mod(mul_mod(a1.x, b0.x, c.q, c.cr0, c.cr1), mul_mod(a0.x, b1.x, c.q, c.cr0, c.cr1), c.q);
+            c1.y = add_mod(mul_mod(a1.y, b0.y, c.q, c.cr0, c.cr1), mul_mod(a0.y, b1.y, c.q, c.cr0, c.cr1), c.q);
+            c2.x = mul_mod(a1.x, b1.x, c.q, c.cr0, c.cr1);
+            c2.y = mul_mod(a1.y, b1.y, c.q, c.cr0, c.cr1);
+            *reinterpret_cast<ulonglong2 *>(po) = c0;
+            *reinterpret_cast<ulonglong2 *>(po + LN) = c1;
+            *reinterpret_cast<ulonglong2 *>(po + 2 * LN) = c2;
+        }
+    }
+
+    // ---- NTT-form Galois gather (GaloisTool::apply_galois_ntt, util/galois.cpp:188-214) ------------
+    // out[z][i][d] = in[z*in_zs + i*N + table[d]] for z < n, i < L.
+    struct GatherArgs
+    {
+        const uint64_t *in;
+        size_t in_zs;
+        uint64_t *out; // [n][L][N]
+        const uint32_t *table;
+        uint32_t N, L;
+        size_t total; // n*L*N
+    };
+
+    __global__ void __launch_bounds__(256) galois_gather_kernel(GatherArgs p)
+    {
+        const size_t LN = static_cast<size_t>(p.L) * p.N;
+        for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < p.total;
+             i += static_cast<size_t>(gridDim.x) * blockDim.x)
+        {
+            const size_t z = i / LN, rem = i - z * LN;
+            const uint32_t d = static_cast<uint32_t>(rem & (p.N - 1));
+            p.out[i] = p.in[z * p.in_zs + (rem - d) + __ldg(p.table + d)];
+        }
+    }
+} // namespace gsb

@@ -304,13 +304,13 @@ namespace gsb
                     {
 #pragma unroll
                         for (int i = 0; i < 8; i += 2)
-                            epi.store2(map.coeff(tile, base + i), x[i], x[i + 1]);
+                            epi.store2(map.coeff(tile, base + i), x[i], x[i + 1], i);
                     }
                     else
                     {
 #pragma unroll
                         for (int i = 0; i < (1 << R); i++)
-                            epi.store(map.coeff(tile, base + (static_cast<uint32_t>(i) << low)), x[sub * (1 << R) + i]);
+                            epi.store(map.coeff(tile, base + (static_cast<uint32_t>(i) << low)), x[sub * (1 << R) + i], sub * (1 << R) + i);
                     }
                 }
             }
@@ -375,13 +375,13 @@ namespace gsb
                     {
 #pragma unroll
                         for (int i = 0; i < 8; i += 2)
-                            epi.store2(map.coeff(tile, base + i), x[i], x[i + 1]);
+                            epi.store2(map.coeff(tile, base + i), x[i], x[i + 1], i);
                     }
                     else
                     {
 #pragma unroll
                         for (int i = 0; i < (1 << R); i++)
-                            epi.store(map.coeff(tile, base + (static_cast<uint32_t>(i) << BOT)), x[sub * (1 << R) + i]);
+                            epi.store(map.coeff(tile, base + (static_cast<uint32_t>(i) << BOT)), x[sub * (1 << R) + i], sub * (1 << R) + i);
                     }
                 }
             }

@@ -32,38 +32,56 @@ namespace gsb
         return v;
     }
 
-    // Plain limb-major IO: element (z, y, d) at base[(z*ny + y)*N + d].
+    // Plain limb-major IO: element (z, y, d) at base[z*zs + y*N + d] (zs = word stride between
+    // polynomials; separate strides for source and destination allow out-of-place transforms).
+    struct PlainPro
+    {
+        const uint64_t *p;
+        GSB_DEV PlainPro(const uint64_t *base, size_t zs, int y, int z, uint32_t N)
+            : p(base + static_cast<size_t>(z) * zs + static_cast<size_t>(y) * N)
+        {}
+        GSB_DEV uint64_t load(uint32_t d) const { return p[d]; }
+        GSB_DEV void load2(uint32_t d, uint64_t &a, uint64_t &b) const
+        {
+            ulonglong2 v = *reinterpret_cast<const ulonglong2 *>(p + d);
+            a = v.x;
+            b = v.y;
+        }
+    };
+
+    template <int MODE>
+    struct PlainEpi
+    {
+        uint64_t *p;
+        const LimbC &c;
+        GSB_DEV PlainEpi(uint64_t *base, size_t zs, int y, int z, const LimbC &c_, uint32_t N)
+            : p(base + static_cast<size_t>(z) * zs + static_cast<size_t>(y) * N), c(c_)
+        {}
+        GSB_DEV void store(uint32_t d, uint64_t v, int) const { p[d] = finish<MODE>(v, c); }
+        GSB_DEV void store2(uint32_t d, uint64_t a, uint64_t b, int) const
+        {
+            *reinterpret_cast<ulonglong2 *>(p + d) = make_ulonglong2(finish<MODE>(a, c), finish<MODE>(b, c));
+        }
+    };
+
     template <int MODE>
     struct IoPlain
     {
         const uint64_t *src;
         uint64_t *dst;
-        struct Pro
+        size_t src_zs, dst_zs;
+        GSB_DEV bool skip(int, int) const { return false; }
+        struct Pro : PlainPro
         {
-            const uint64_t *p;
             GSB_DEV Pro(const IoPlain &io, int y, int z, int, const LimbC &, uint32_t N)
-                : p(io.src + (static_cast<size_t>(z) * gridDim.y + y) * N)
+                : PlainPro(io.src, io.src_zs, y, z, N)
             {}
-            GSB_DEV uint64_t load(uint32_t d) const { return p[d]; }
-            GSB_DEV void load2(uint32_t d, uint64_t &a, uint64_t &b) const
-            {
-                ulonglong2 v = *reinterpret_cast<const ulonglong2 *>(p + d);
-                a = v.x;
-                b = v.y;
-            }
         };
-        struct Epi
+        struct Epi : PlainEpi<MODE>
         {
-            uint64_t *p;
-            const LimbC &c;
             GSB_DEV Epi(const IoPlain &io, int y, int z, int, const LimbC &c_, uint32_t N)
-                : p(io.dst + (static_cast<size_t>(z) * gridDim.y + y) * N), c(c_)
+                : PlainEpi<MODE>(io.dst, io.dst_zs, y, z, c_, N)
             {}
-            GSB_DEV void store(uint32_t d, uint64_t v) const { p[d] = finish<MODE>(v, c); }
-            GSB_DEV void store2(uint32_t d, uint64_t a, uint64_t b) const
-            {
-                *reinterpret_cast<ulonglong2 *>(p + d) = make_ulonglong2(finish<MODE>(a, c), finish<MODE>(b, c));
-            }
         };
     };
 
@@ -71,6 +89,8 @@ namespace gsb
     __global__ void __launch_bounds__(1 << T_LOG) ntt_fwd_kernel(IO io, NttTables tab, ModMap mm, Map map)
     {
         const int y = blockIdx.y, z = blockIdx.z, mod = mm.mod(y);
+        if (io.skip(y, z))
+            return;
         const LimbC c = tab.limb[mod];
         typename IO::Pro pro(io, y, z, mod, c, tab.N);
         typename IO::Epi epi(io, y, z, mod, c, tab.N);
@@ -84,6 +104,8 @@ namespace gsb
     __global__ void __launch_bounds__(1 << T_LOG) ntt_inv_kernel(IO io, NttTables tab, ModMap mm, Map map)
     {
         const int y = blockIdx.y, z = blockIdx.z, mod = mm.mod(y);
+        if (io.skip(y, z))
+            return;
         const LimbC c = tab.limb[mod];
         typename IO::Pro pro(io, y, z, mod, c, tab.N);
         typename IO::Epi epi(io, y, z, mod, c, tab.N);
@@ -121,7 +143,8 @@ namespace gsb
 
     // Forward pass 1 (columns) with arbitrary IO.  grid.x = N / 2^C column groups.
     template <int LOGN, class IO>
-    inline void launch_fwd_cols(const IO &io, const NttTables &tab, const ModMap &mm, int ny, int nz, cudaStream_t st)
+    inline void launch_fwd_cols(
+        const IO &io, const NttTables &tab, const ModMap &mm, int ny, int nz, cudaStream_t st, const char *tag = "plain")
     {
         using SP = Split<LOGN>;
         constexpr int A = SP::A, TC = SP::TC, C = TC + 3 - A;
@@ -129,12 +152,13 @@ namespace gsb
         auto kfn = ntt_fwd_kernel<TC, A + C - 1, C, false, ColMap<TC, A>, IO>;
         allow_smem(kfn, tile_smem_bytes<TC>());
         dim3 grid((1u << (LOGN - A)) >> C, ny, nz);
-        GSB_LAUNCH(kfn, grid, dim3(1 << TC), tile_smem_bytes<TC>(), st, io, tab, mm, map);
+        GSB_LAUNCH("fwd_cols", tag, kfn, grid, dim3(1 << TC), tile_smem_bytes<TC>(), st, io, tab, mm, map);
     }
 
     // Forward pass 2 (contiguous blocks of N >> A) -- or the whole transform when !two_pass.
     template <int LOGN, class IO>
-    inline void launch_fwd_contig(const IO &io, const NttTables &tab, const ModMap &mm, int ny, int nz, cudaStream_t st)
+    inline void launch_fwd_contig(
+        const IO &io, const NttTables &tab, const ModMap &mm, int ny, int nz, cudaStream_t st, const char *tag = "plain")
     {
         using SP = Split<LOGN>;
         if constexpr (SP::two_pass)
@@ -144,7 +168,7 @@ namespace gsb
             auto kfn = ntt_fwd_kernel<T, LOGN - SP::A - 1, 0, true, ContigMap<T>, IO>;
             allow_smem(kfn, tile_smem_bytes<T>());
             dim3 grid(1u << (LOGN - T - 3), ny, nz);
-            GSB_LAUNCH(kfn, grid, dim3(1 << T), tile_smem_bytes<T>(), st, io, tab, mm, map);
+            GSB_LAUNCH("fwd_contig", tag, kfn, grid, dim3(1 << T), tile_smem_bytes<T>(), st, io, tab, mm, map);
         }
         else
         {
@@ -152,13 +176,14 @@ namespace gsb
             ContigMap<T> map{ tab.N };
             auto kfn = ntt_fwd_kernel<T, LOGN - 1, 0, true, ContigMap<T>, IO>;
             allow_smem(kfn, tile_smem_bytes<T>());
-            GSB_LAUNCH(kfn, dim3(1, ny, nz), dim3(1 << T), tile_smem_bytes<T>(), st, io, tab, mm, map);
+            GSB_LAUNCH("fwd_contig", tag, kfn, dim3(1, ny, nz), dim3(1 << T), tile_smem_bytes<T>(), st, io, tab, mm, map);
         }
     }
 
     // Inverse pass 1 (contiguous) -- or the whole transform when !two_pass.
     template <int LOGN, class IO>
-    inline void launch_inv_contig(const IO &io, const NttTables &tab, const ModMap &mm, int ny, int nz, cudaStream_t st)
+    inline void launch_inv_contig(
+        const IO &io, const NttTables &tab, const ModMap &mm, int ny, int nz, cudaStream_t st, const char *tag = "plain")
     {
         using SP = Split<LOGN>;
         if constexpr (SP::two_pass)
@@ -168,7 +193,7 @@ namespace gsb
             auto kfn = ntt_inv_kernel<T, LOGN - SP::A - 1, 0, false, ContigMap<T>, IO>;
             allow_smem(kfn, tile_smem_bytes<T>());
             dim3 grid(1u << (LOGN - T - 3), ny, nz);
-            GSB_LAUNCH(kfn, grid, dim3(1 << T), tile_smem_bytes<T>(), st, io, tab, mm, map);
+            GSB_LAUNCH("inv_contig", tag, kfn, grid, dim3(1 << T), tile_smem_bytes<T>(), st, io, tab, mm, map);
         }
         else
         {
@@ -176,13 +201,14 @@ namespace gsb
             ContigMap<T> map{ tab.N };
             auto kfn = ntt_inv_kernel<T, LOGN - 1, 0, true, ContigMap<T>, IO>;
             allow_smem(kfn, tile_smem_bytes<T>());
-            GSB_LAUNCH(kfn, dim3(1, ny, nz), dim3(1 << T), tile_smem_bytes<T>(), st, io, tab, mm, map);
+            GSB_LAUNCH("inv_contig", tag, kfn, dim3(1, ny, nz), dim3(1 << T), tile_smem_bytes<T>(), st, io, tab, mm, map);
         }
     }
 
     // Inverse pass 2 (columns; carries the global last stage with n^-1).
     template <int LOGN, class IO>
-    inline void launch_inv_cols(const IO &io, const NttTables &tab, const ModMap &mm, int ny, int nz, cudaStream_t st)
+    inline void launch_inv_cols(
+        const IO &io, const NttTables &tab, const ModMap &mm, int ny, int nz, cudaStream_t st, const char *tag = "plain")
     {
         using SP = Split<LOGN>;
         constexpr int A = SP::A, TC = SP::TC, C = TC + 3 - A;
@@ -190,45 +216,47 @@ namespace gsb
         auto kfn = ntt_inv_kernel<TC, A + C - 1, C, true, ColMap<TC, A>, IO>;
         allow_smem(kfn, tile_smem_bytes<TC>());
         dim3 grid((1u << (LOGN - A)) >> C, ny, nz);
-        GSB_LAUNCH(kfn, grid, dim3(1 << TC), tile_smem_bytes<TC>(), st, io, tab, mm, map);
+        GSB_LAUNCH("inv_cols", tag, kfn, grid, dim3(1 << TC), tile_smem_bytes<TC>(), st, io, tab, mm, map);
     }
 
-    // Plain batched transforms: src/dst are [nz][ny][N]; in-place allowed (src == dst).
+    // Plain batched transforms: element (z, y, d) of src/dst at base + z*zs + y*N + d; in place
+    // allowed (src == dst with equal strides).
     template <int LOGN>
     inline void ntt_forward_plain(
-        const NttTables &tab, const ModMap &mm, const uint64_t *src, uint64_t *dst, int ny, int nz, bool lazy,
-        cudaStream_t st)
+        const NttTables &tab, const ModMap &mm, const uint64_t *src, size_t src_zs, uint64_t *dst, size_t dst_zs, int ny,
+        int nz, bool lazy, cudaStream_t st, const char *tag = "plain")
     {
         if constexpr (Split<LOGN>::two_pass)
         {
-            launch_fwd_cols<LOGN>(IoPlain<OUT_RAW>{ src, dst }, tab, mm, ny, nz, st);
+            launch_fwd_cols<LOGN>(IoPlain<OUT_RAW>{ src, dst, src_zs, dst_zs }, tab, mm, ny, nz, st, tag);
             src = dst;
+            src_zs = dst_zs;
         }
         if (lazy)
-            launch_fwd_contig<LOGN>(IoPlain<OUT_RAW>{ src, dst }, tab, mm, ny, nz, st);
+            launch_fwd_contig<LOGN>(IoPlain<OUT_RAW>{ src, dst, src_zs, dst_zs }, tab, mm, ny, nz, st, tag);
         else
-            launch_fwd_contig<LOGN>(IoPlain<OUT_FWD_STRICT>{ src, dst }, tab, mm, ny, nz, st);
+            launch_fwd_contig<LOGN>(IoPlain<OUT_FWD_STRICT>{ src, dst, src_zs, dst_zs }, tab, mm, ny, nz, st, tag);
     }
 
     template <int LOGN>
     inline void ntt_inverse_plain(
-        const NttTables &tab, const ModMap &mm, const uint64_t *src, uint64_t *dst, int ny, int nz, bool lazy,
-        cudaStream_t st)
+        const NttTables &tab, const ModMap &mm, const uint64_t *src, size_t src_zs, uint64_t *dst, size_t dst_zs, int ny,
+        int nz, bool lazy, cudaStream_t st, const char *tag = "plain")
     {
         if constexpr (Split<LOGN>::two_pass)
         {
-            launch_inv_contig<LOGN>(IoPlain<OUT_RAW>{ src, dst }, tab, mm, ny, nz, st);
+            launch_inv_contig<LOGN>(IoPlain<OUT_RAW>{ src, dst, src_zs, dst_zs }, tab, mm, ny, nz, st, tag);
             if (lazy)
-                launch_inv_cols<LOGN>(IoPlain<OUT_RAW>{ dst, dst }, tab, mm, ny, nz, st);
+                launch_inv_cols<LOGN>(IoPlain<OUT_RAW>{ dst, dst, dst_zs, dst_zs }, tab, mm, ny, nz, st, tag);
             else
-                launch_inv_cols<LOGN>(IoPlain<OUT_INV_STRICT>{ dst, dst }, tab, mm, ny, nz, st);
+                launch_inv_cols<LOGN>(IoPlain<OUT_INV_STRICT>{ dst, dst, dst_zs, dst_zs }, tab, mm, ny, nz, st, tag);
         }
         else
         {
             if (lazy)
-                launch_inv_contig<LOGN>(IoPlain<OUT_RAW>{ src, dst }, tab, mm, ny, nz, st);
+                launch_inv_contig<LOGN>(IoPlain<OUT_RAW>{ src, dst, src_zs, dst_zs }, tab, mm, ny, nz, st, tag);
             else
-                launch_inv_contig<LOGN>(IoPlain<OUT_INV_STRICT>{ src, dst }, tab, mm, ny, nz, st);
+                launch_inv_contig<LOGN>(IoPlain<OUT_INV_STRICT>{ src, dst, src_zs, dst_zs }, tab, mm, ny, nz, st, tag);
         }
     }
 

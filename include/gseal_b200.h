@@ -57,6 +57,13 @@ const char *gsb_last_error(void);
 int gsb_version(void);
 /* number of kernel launches this library has issued in this process (bench.py "gpu_launches") */
 unsigned long long gsb_launch_count(void);
+/* Optional per-launch timing for bench.py's roofline: while enabled, every kernel launch is
+ * bracketed by CUDA events on its own stream.  gsb_prof_enable(1) clears earlier records.
+ * gsb_prof_report synchronises the device and writes a JSON object
+ * {"<kernel label>": {"launches": n, "ms": total}, ...} (launch order) into buf; returns the bytes
+ * needed including the terminator (call with buf = NULL to size), or -1 on a CUDA error. */
+int gsb_prof_enable(int on);
+long gsb_prof_report(char *buf, size_t cap);
 
 /* ---- context: replaces SEALContext::ContextData tables (context.cpp:135-420) --------------------
  * moduli[0..K) is the key-level coeff_modulus; its last k_special entries are the special primes
@@ -100,6 +107,62 @@ int gsb_ntt_inverse_host(gsb_ctx *ctx, uint64_t *data, size_t n_polys, size_t n_
 int gsb_poly_op_dev(
     gsb_ctx *ctx, int op, const uint64_t *a, const uint64_t *b, const uint64_t *scalars, uint64_t *out,
     size_t n_polys, size_t n_limbs, size_t limb_offset, void *stream);
+
+int gsb_poly_op_host(
+    gsb_ctx *ctx, int op, const uint64_t *a, const uint64_t *b, const uint64_t *scalars, uint64_t *out,
+    size_t n_polys, size_t n_limbs, size_t limb_offset);
+
+/* ---- switching keys: KSwitchKeys / RelinKeys / GaloisKeys (kswitchkeys.h:343, relinkeys.h:61,
+ * galoiskeys.h:52-66, keygenerator.cpp:325-369) --------------------------------------------------
+ * key_host = [n_bundles][2][K][N]: bundle j is `keys.data()[index][j].data()` of the reference (a
+ * size-2 ciphertext over all K key-level limbs, NTT form).  n_bundles must be ceil((K-k)/k).
+ * kind GSB_KEY_RELIN ignores galois_elt.  The context keeps a device copy until gsb_key_drop /
+ * gsb_ctx_destroy.  Uploading also builds the Galois permutation table (util/galois.cpp:18-47). */
+int gsb_key_upload(gsb_ctx *ctx, int kind, uint32_t galois_elt, const uint64_t *key_host, size_t n_bundles);
+int gsb_key_drop(gsb_ctx *ctx, int kind, uint32_t galois_elt);
+/* GaloisTool::get_elt_from_step (util/galois.cpp:49-91); GSB_E_INVALID_ARG for |step| >= N/2 */
+int gsb_galois_elt_from_step(const gsb_ctx *ctx, int step, uint32_t *elt);
+/* GaloisTool::generate_table_ntt (util/galois.cpp:18-47): table_out[0..N) (host) */
+int gsb_galois_table(const gsb_ctx *ctx, uint32_t galois_elt, uint32_t *table_out);
+
+/* ---- Evaluator hot path, batched: every pointer is a batch of `batch` ciphertexts stored back to
+ * back; L = number of limbs of the ciphertexts' level (2 <= L <= K-k for rescale, 1 <= L otherwise).
+ * All ciphertexts are CKKS, NTT form.  ws = NULL uses the context's default workspace. ----------- */
+
+/* Evaluator::multiply_inplace -> ckks_multiply (evaluator.cpp:235-272,447-527) for two size-2
+ * operands: a, b = [batch][2][L][N] -> out = [batch][3][L][N]. */
+int gsb_ckks_multiply_dev(gsb_ctx *ctx, const uint64_t *a, const uint64_t *b, uint64_t *out, size_t batch, size_t L, void *stream);
+
+/* Evaluator::switch_key_inplace (evaluator.cpp:2259-2368): enc = [batch][enc_size][L][N], its
+ * components 0 and 1 are updated in place; target = one polynomial [L][N] per ciphertext, the b-th
+ * at target + b*target_stride words (may point inside enc, e.g. component 2). */
+int gsb_switch_key_dev(
+    gsb_ctx *ctx, gsb_ws *ws, uint64_t *enc, size_t enc_size, const uint64_t *target, size_t target_stride,
+    int key_kind, uint32_t galois_elt, size_t batch, size_t L, void *stream);
+
+/* Evaluator::relinearize_inplace (evaluator.h:344, evaluator.cpp:772-827) of size-3 ciphertexts:
+ * in = [batch][3][L][N] -> out = [batch][2][L][N]  (out must not overlap in). */
+int gsb_relinearize_dev(gsb_ctx *ctx, gsb_ws *ws, const uint64_t *in, uint64_t *out, size_t batch, size_t L, void *stream);
+
+/* Evaluator::rescale_to_next (evaluator.cpp:1090-1126,829-892; util/rns.cpp:777-851):
+ * in = [batch][size][L][N] -> out = [batch][size][L-1][N]  (the caller divides `scale` by q_{L-1}). */
+int gsb_rescale_dev(gsb_ctx *ctx, gsb_ws *ws, const uint64_t *in, uint64_t *out, size_t batch, size_t size, size_t L, void *stream);
+
+/* Evaluator::apply_galois_inplace (evaluator.cpp:1841-1943; rotate_vector = elt from step,
+ * complex_conjugate = elt 2N-1): in, out = [batch][2][L][N]  (out must not overlap in). */
+int gsb_apply_galois_dev(gsb_ctx *ctx, gsb_ws *ws, uint32_t galois_elt, const uint64_t *in, uint64_t *out, size_t batch, size_t L, void *stream);
+
+/* multiply_inplace + relinearize_inplace + rescale_to_next_inplace in one call (the unit of work of
+ * the headline metric): a, b = [batch][2][L][N] -> out = [batch][2][L-1][N]. */
+int gsb_mul_relin_rescale_dev(gsb_ctx *ctx, gsb_ws *ws, const uint64_t *a, const uint64_t *b, uint64_t *out, size_t batch, size_t L, void *stream);
+
+/* Host-buffer forms (what the C++ shim calls with seal::Ciphertext::data()): copy in, run, copy out,
+ * synchronise.  Shapes as above. */
+int gsb_ckks_multiply_host(gsb_ctx *ctx, const uint64_t *a, const uint64_t *b, uint64_t *out, size_t batch, size_t L);
+int gsb_relinearize_host(gsb_ctx *ctx, const uint64_t *in, uint64_t *out, size_t batch, size_t L);
+int gsb_rescale_host(gsb_ctx *ctx, const uint64_t *in, uint64_t *out, size_t batch, size_t size, size_t L);
+int gsb_apply_galois_host(gsb_ctx *ctx, uint32_t galois_elt, const uint64_t *in, uint64_t *out, size_t batch, size_t L);
+int gsb_mul_relin_rescale_host(gsb_ctx *ctx, const uint64_t *a, const uint64_t *b, uint64_t *out, size_t batch, size_t L);
 
 #ifdef __cplusplus
 }

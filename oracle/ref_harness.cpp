@@ -251,6 +251,50 @@ extern "C"
         });
     }
 
+    // Synthetic switching keys without the (slow, non-reproducible) KeyGenerator: build KSwitchKeys of
+    // the shape generate_kswitch_keys produces (keygenerator.cpp:325-369: one PublicKey per bundle, each
+    // a size-2 NTT-form ciphertext at key level) and fill every limb with uniform residues from
+    // mt19937_64(seed).  The same limbs are read back with ref_get_key and uploaded to the GPU.
+    int ref_make_synthetic_keys(void *h, const uint32_t *galois_elts, size_t n_elts, uint64_t seed)
+    {
+        auto *c = static_cast<RefCtx *>(h);
+        return guarded([&] {
+            auto key_cd = c->context->key_context_data();
+            auto &mods = key_cd->parms().coeff_modulus();
+            size_t n_bundles = (c->L0 + c->k - 1) / c->k;
+            std::mt19937_64 rng(seed);
+            auto fill = [&](std::vector<PublicKey> &v) {
+                v.resize(n_bundles);
+                for (auto &pk : v)
+                {
+                    Ciphertext &ct = pk.data();
+                    ct.resize(c->context, key_cd->parms_id(), 2);
+                    ct.is_ntt_form() = true;
+                    ct.scale() = 1.0;
+                    for (size_t p = 0; p < 2; p++)
+                        for (size_t i = 0; i < c->K; i++)
+                            for (size_t d = 0; d < c->N; d++)
+                                ct.data(p)[i * c->N + d] = rng() % mods[i].value();
+                }
+            };
+            c->relin = RelinKeys();
+            c->relin.data().resize(1);
+            fill(c->relin.data()[0]);
+            c->relin.parms_id() = key_cd->parms_id();
+            c->have_relin = true;
+            c->galois = GaloisKeys();
+            for (size_t e = 0; e < n_elts; e++)
+            {
+                size_t idx = GaloisKeys::get_index(galois_elts[e]);
+                if (c->galois.data().size() <= idx)
+                    c->galois.data().resize(idx + 1);
+                fill(c->galois.data()[idx]);
+            }
+            c->galois.parms_id() = key_cd->parms_id();
+            c->have_galois = n_elts > 0;
+        });
+    }
+
     // Synthetic keys: allocate KSwitchKeys of the right shape by running keygen once, then
     // (optionally) the caller overwrites the limbs with ref_set_key.
     // which: 0 = relin (index 0), 1 = galois for element `elt`.

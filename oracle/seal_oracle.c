@@ -355,7 +355,9 @@ void so_ntt_inv(uint64_t *a, const so_tables *t)
 int so_ntt(int logn, uint64_t q, uint64_t *data, size_t n_polys, int kind)
 {
     so_tables t;
-    if (logn < 3 || so_tables_init(&t, logn, q))
+    /* the forward loops are generic (the reference's N = 2 KAT, tests/seal/util/ntt.cpp:98-102,
+     * runs through them); the inverse restatement mirrors the three fixed loops, n >= 8 */
+    if (logn < 1 || (kind >= 2 && logn < 3) || so_tables_init(&t, logn, q))
         return -1;
     size_t n = (size_t)1 << logn;
     for (size_t p = 0; p < n_polys; p++)

@@ -1,0 +1,221 @@
+"""Named, seeded parity cases shared by the golden-fixture generator (tests/golden/make_golden.py,
+run against the unmodified reference), the oracle pin test and the GPU / simulator parity tests.
+
+A case is fully determined by its name: parameters + seed -> input limbs and synthetic keys.
+`run_case(name, backend)` returns {output name: sha256 of the output limbs}.  Backends expose the
+same six operations over single ciphertexts [size][L][N] (device backends batch them internally).
+"""
+import numpy as np
+
+from common import digest, mixed_moduli, ntt_primes, rand_key, rand_poly
+
+# CoeffModulus::BFVDefault(N) of the reference (util/globals.cpp:22-160), as returned by
+# oracle/_ref (ref_default_moduli) -- what native/examples/7_performance.cpp runs on.
+BFV_DEFAULT = {
+    4096: [68719403009, 68719230977, 137438822401],
+    8192: [8796092858369, 8796092792833, 17592186028033, 17592185438209, 17592184717313],
+    16384: [281474976546817, 281474976317441, 281474975662081, 562949952798721, 562949952700417,
+            562949952274433, 562949951979521, 562949951881217, 562949951619073],
+    32768: [36028797017456641, 36028797014704129, 36028797014573057, 36028797014376449,
+            36028797013327873, 36028797013000193, 36028797012606977, 36028797010444289,
+            36028797009985537, 36028797005856769, 36028797005529089, 36028797005135873,
+            36028797003694081, 36028797003563009, 36028797001138177, 72057594037338113],
+}
+
+# name -> (logn, moduli spec, k special, level L, batch, rotation step)
+EVAL = {
+    "c1_n4096_default": (12, BFV_DEFAULT[4096], 1, 2, 2, 1),
+    "n1024_k1_L3": (10, [40, 40, 40, 41], 1, 3, 2, 1),
+    "n2048_k2_L4": (11, [50, 40, 45, 45, 50, 51], 2, 4, 2, -1),
+    "n2048_k2_L3_ragged": (11, [50, 40, 45, 45, 50, 51], 2, 3, 1, 3),
+    "n1024_k3_L5": (10, [45, 45, 45, 45, 45, 46, 46, 46], 3, 5, 1, 7),
+    "n1024_k3_L4_ragged": (10, [45, 45, 45, 45, 45, 46, 46, 46], 3, 4, 1, 2),
+    "n8192_default_k1_L4": (13, BFV_DEFAULT[8192], 1, 4, 1, 1),
+    "n8192_k2_L3": (13, BFV_DEFAULT[8192], 2, 3, 1, -2),
+    "c3_n16384_default": (14, BFV_DEFAULT[16384], 1, 8, 1, 1),
+    "c4_n32768_default": (15, BFV_DEFAULT[32768], 1, 15, 1, 1),
+    "n32768_k4_L12": (15, BFV_DEFAULT[32768], 4, 12, 1, 1),
+    "n65536_k1_L2": (16, [59, 59, 59], 1, 2, 1, 1),
+}
+# (logn, bits): 3 polys x 3 limbs, all four transforms
+NTT = {"ntt_n%d_b%d" % (ln, b): (ln, b) for ln in (10, 11, 12, 13, 14, 15, 16) for b in (30, 59)}
+NTT["ntt_n12_b60_wrap"] = (12, 60)  # lazy forward transform wraps mod 2^64
+NTT["ntt_n15_b60_wrap"] = (15, 60)
+
+SMALL = [n for n, c in EVAL.items() if c[0] <= 12] + [n for n, c in NTT.items() if c[0] <= 13]
+
+
+def case_seed(name):
+    return int.from_bytes(name.encode(), "little") % (1 << 31)
+
+
+def eval_inputs(name):
+    logn, spec, k, L, batch, step = EVAL[name]
+    N = 1 << logn
+    mods = list(spec) if spec[0] > 64 else mixed_moduli(logn, spec)
+    rng = np.random.default_rng(case_seed(name))
+    K = len(mods)
+    nb = (K - k + k - 1) // k
+    return dict(
+        logn=logn, N=N, mods=mods, k=k, L=L, batch=batch, step=step,
+        a=rand_poly(rng, mods[:L], (batch, 2), N), b=rand_poly(rng, mods[:L], (batch, 2), N),
+        relin=rand_key(rng, mods, nb, N), galois=rand_key(rng, mods, nb, N))
+
+
+def ntt_inputs(name):
+    logn, bits = NTT[name]
+    mods = ntt_primes(logn, bits, 3)
+    rng = np.random.default_rng(case_seed(name))
+    return dict(logn=logn, mods=mods, x=rand_poly(rng, mods, (3,), 1 << logn))
+
+
+def run_case(name, be):
+    out = {}
+    if name in NTT:
+        c = ntt_inputs(name)
+        for kind in range(4):
+            out["kind%d" % kind] = digest(be.ntt(c["logn"], c["mods"], c["x"], kind))
+        return out
+    c = eval_inputs(name)
+    be.setup(c["logn"], c["mods"], c["k"])
+    elt = be.elt_from_step(c["logn"], c["step"])
+    be.set_keys(c["relin"], elt, c["galois"])
+    c3 = be.multiply(c["a"], c["b"])
+    c2 = be.relinearize(c3)
+    out["multiply"] = digest(c3)
+    out["relinearize"] = digest(c2)
+    if c["L"] >= 2:
+        out["rescale"] = digest(be.rescale(c2))
+        out["mul_relin_rescale"] = digest(be.mul_relin_rescale(c["a"], c["b"]))
+    out["rotate"] = digest(be.apply_galois(c["a"], elt))
+    return out
+
+
+class _PerCt:
+    """Maps batched [B][size][L][N] arrays over a per-ciphertext function."""
+    @staticmethod
+    def each(fn, *arrs):
+        return np.ascontiguousarray(np.stack([fn(*[np.ascontiguousarray(a[i]) for a in arrs]) for i in range(arrs[0].shape[0])]))
+
+
+class OracleBackend(_PerCt):
+    def __init__(self, oracle):
+        self.o = oracle
+
+    def ntt(self, logn, mods, x, kind):
+        return self.o.ntt_rns(logn, mods, x, kind)
+
+    def setup(self, logn, mods, k):
+        self.logn = logn
+        self.c = self.o.context(logn, mods, k)
+
+    def elt_from_step(self, logn, step):
+        return self.o.elt_from_step(logn, step)
+
+    def set_keys(self, relin, elt, galois):
+        self.relin, self.elt, self.gal = relin, elt, galois
+
+    def multiply(self, a, b):
+        return self.each(self.c.multiply, a, b)
+
+    def relinearize(self, c3):
+        return self.each(lambda x: self.c.relinearize(x, self.relin), c3)
+
+    def rescale(self, c):
+        return self.each(self.c.rescale, c)
+
+    def mul_relin_rescale(self, a, b):
+        return self.each(lambda x, y: self.c.mul_relin_rescale(x, y, self.relin), a, b)
+
+    def apply_galois(self, c, elt):
+        return self.each(lambda x: self.c.apply_galois(x, elt, self.gal), c)
+
+
+class RefBackend(_PerCt):
+    """The unmodified reference (oracle/_ref); used by make_golden.py only."""
+
+    def __init__(self, reflib):
+        self.r = reflib
+
+    def ntt(self, logn, mods, x, kind):
+        out = x.copy()
+        for y, q in enumerate(mods):
+            out[:, y, :] = self.r.ntt(logn, q, np.ascontiguousarray(x[:, y, :]), kind)
+        return out
+
+    def setup(self, logn, mods, k):
+        self.c = self.r.context(1 << logn, mods, k)
+
+    def elt_from_step(self, logn, step):
+        return self.c.elt_from_step(step)
+
+    def set_keys(self, relin, elt, galois):
+        self.c.keygen([elt])
+        self.c.set_key(0, 0, relin)
+        self.c.set_key(1, elt, galois)
+
+    def multiply(self, a, b):
+        return self.each(self.c.multiply, a, b)
+
+    def relinearize(self, c3):
+        return self.each(self.c.relinearize, c3)
+
+    def rescale(self, c):
+        return self.each(self.c.rescale, c)
+
+    def mul_relin_rescale(self, a, b):
+        return self.each(self.c.mul_relin_rescale, a, b)
+
+    def apply_galois(self, c, elt):
+        return self.each(lambda x: self.c.apply_galois(x, elt), c)
+
+
+class DeviceBackend:
+    """The product path through the C ABI (host-buffer entry points); `lib` is the CUDA library on
+    the GPU box or the test-only simulator build on CPU."""
+
+    def __init__(self, lib):
+        self.lib = lib
+        self.ctx = None
+
+    def _ctx(self, logn, mods, k):
+        from gemini_seal_b200 import Context
+        return Context(1 << logn, mods, k, lib=self.lib)
+
+    def ntt(self, logn, mods, x, kind):
+        import gemini_seal_b200 as g
+        ctx = self._ctx(logn, mods, 1)
+        fn = [g.ntt_negacyclic_harvey_lazy, g.ntt_negacyclic_harvey, g.inverse_ntt_negacyclic_harvey_lazy,
+              g.inverse_ntt_negacyclic_harvey][kind]
+        out = fn(x.copy(), ctx)
+        ctx.close()
+        return out
+
+    def setup(self, logn, mods, k):
+        from gemini_seal_b200 import Evaluator
+        if self.ctx is not None:
+            self.ctx.close()
+        self.ctx = self._ctx(logn, mods, k)
+        self.ev = Evaluator(self.ctx)
+
+    def elt_from_step(self, logn, step):
+        return self.ctx.galois_elt_from_step(step)
+
+    def set_keys(self, relin, elt, galois):
+        self.ctx.set_relin_keys(relin)
+        self.ctx.set_galois_key(elt, galois)
+
+    def multiply(self, a, b):
+        return self.ev.multiply(a, b)
+
+    def relinearize(self, c3):
+        return self.ev.relinearize(c3)
+
+    def rescale(self, c):
+        return self.ev.rescale_to_next(c)
+
+    def mul_relin_rescale(self, a, b):
+        return self.ev.mul_relin_rescale(a, b)
+
+    def apply_galois(self, c, elt):
+        return self.ev.apply_galois(c, elt)

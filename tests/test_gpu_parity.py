@@ -1,0 +1,145 @@
+"""Parity tests proper (-m gpu): the CUDA library through the C ABI against
+  * the golden digests produced by the unmodified reference (tests/golden/evaluator_digests.json),
+  * the CPU oracle on the same seeded inputs (bit-exact, integer work),
+  * size-independent properties at BASELINE.json's full sizes (round trips, batch independence,
+    host-buffer vs device-buffer entry points)."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+import golden_cases
+from common import ntt_primes, rand_key, rand_poly
+
+pytestmark = pytest.mark.gpu
+
+with open(os.path.join(os.path.dirname(__file__), "golden", "evaluator_digests.json")) as f:
+    GOLDEN = json.load(f)["cases"]
+
+
+@pytest.mark.parametrize("name", list(golden_cases.NTT) + list(golden_cases.EVAL))
+def test_matches_reference_digests(cudalib, name):
+    got = golden_cases.run_case(name, golden_cases.DeviceBackend(cudalib))
+    assert got == GOLDEN[name]
+
+
+@pytest.mark.parametrize("name", ["n2048_k2_L4", "n8192_k2_L3", "c3_n16384_default"])
+def test_matches_oracle_arrays(cudalib, oracle, name):
+    """Array-level comparison with the oracle (locates a mismatch, unlike a digest)."""
+    c = golden_cases.eval_inputs(name)
+    dev, orc = golden_cases.DeviceBackend(cudalib), golden_cases.OracleBackend(oracle)
+    for be in (dev, orc):
+        be.setup(c["logn"], c["mods"], c["k"])
+        be.set_keys(c["relin"], be.elt_from_step(c["logn"], c["step"]), c["galois"])
+    elt = orc.elt_from_step(c["logn"], c["step"])
+    c3 = orc.multiply(c["a"], c["b"])
+    assert np.array_equal(dev.multiply(c["a"], c["b"]), c3)
+    assert np.array_equal(dev.relinearize(c3), orc.relinearize(c3))
+    assert np.array_equal(dev.rescale(c3), orc.rescale(c3))
+    assert np.array_equal(dev.apply_galois(c["a"], elt), orc.apply_galois(c["a"], elt))
+    assert np.array_equal(dev.mul_relin_rescale(c["a"], c["b"]), orc.mul_relin_rescale(c["a"], c["b"]))
+
+
+def test_ntt_sweep_limbs_vs_oracle(cudalib, oracle):
+    """BASELINE config #2: N = 2^12..2^16 x up to 48 limbs of 59-bit primes, strict + lazy."""
+    import gemini_seal_b200 as g
+    for logn, n_limbs in [(12, 48), (13, 7), (14, 1), (15, 16), (16, 3)]:
+        mods = ntt_primes(logn, 59, n_limbs)
+        ctx = g.Context(1 << logn, mods + ntt_primes(logn, 58, 1), 1, lib=cudalib)
+        rng = np.random.default_rng(logn)
+        x = rand_poly(rng, mods, (2,), 1 << logn)
+        fns = [g.ntt_negacyclic_harvey_lazy, g.ntt_negacyclic_harvey, g.inverse_ntt_negacyclic_harvey_lazy,
+               g.inverse_ntt_negacyclic_harvey]
+        for kind, fn in enumerate(fns):
+            assert np.array_equal(fn(x.copy(), ctx), oracle.ntt_rns(logn, mods, x, kind)), (logn, kind)
+        # limb_offset: transform limbs 1.. only
+        if n_limbs > 2:
+            y = np.ascontiguousarray(x[:, 1:, :])
+            assert np.array_equal(g.ntt_negacyclic_harvey(y.copy(), ctx, limb_offset=1), oracle.ntt_rns(logn, mods, y, 1, limb_offset=1))
+        ctx.close()
+
+
+def test_poly_ops_vs_oracle(cudalib, oracle):
+    import gemini_seal_b200 as g
+    logn = 12
+    mods = ntt_primes(logn, 59, 2) + ntt_primes(logn, 36, 1)
+    ctx = g.Context(1 << logn, mods, 1, lib=cudalib)
+    rng = np.random.default_rng(3)
+    a, b = rand_poly(rng, mods, (3,), 1 << logn), rand_poly(rng, mods, (3,), 1 << logn)
+    a[0, :, 0], b[0, :, 0] = 0, 0
+    scal = [int(rng.integers(0, q)) for q in mods]
+    for name, op in g.evaluator.OPS.items():
+        got = g.poly_op(ctx, name, a, b if op < 3 else None, scal if op == 4 else None)
+        for i, q in enumerate(mods):
+            want = oracle.poly_op(op, q, a[:, i, :], b[:, i, :], scal[i])
+            assert np.array_equal(got[:, i, :], want), (name, i)
+
+
+def test_full_size_properties(cudalib):
+    """N = 2^15, K = 16 (BASELINE config #4/#5) on device buffers, batch 8: forward/inverse round trip,
+    batch independence (each ciphertext of a batch equals the same ciphertext run alone), and
+    device-pointer entry points == host-buffer entry points."""
+    import torch
+    import gemini_seal_b200 as g
+    mods = golden_cases.BFV_DEFAULT[32768]
+    N, L, B = 32768, 15, 8
+    ctx = g.Context(N, mods, 1, lib=cudalib)
+    ev = g.Evaluator(ctx)
+    rng = np.random.default_rng(11)
+    ctx.set_relin_keys(rand_key(rng, mods, 15, N))
+    elt = ctx.galois_elt_from_step(1)
+    ctx.set_galois_key(elt, rand_key(rng, mods, 15, N))
+    a, b = rand_poly(rng, mods[:L], (B, 2), N), rand_poly(rng, mods[:L], (B, 2), N)
+    da = torch.from_numpy(a.view(np.int64)).cuda()
+    db = torch.from_numpy(b.view(np.int64)).cuda()
+    # round trip on the device
+    w = da.clone()
+    g.ntt_negacyclic_harvey(g.inverse_ntt_negacyclic_harvey(w, ctx), ctx)
+    assert torch.equal(w, da)
+    # batched device call vs single-ciphertext host calls
+    out = ev.mul_relin_rescale(da, db)
+    rot = ev.rotate_vector(da, 1)
+    torch.cuda.synchronize()
+    out, rot = out.cpu().numpy().view(np.uint64), rot.cpu().numpy().view(np.uint64)
+    for i in (0, B - 1):
+        assert np.array_equal(ev.mul_relin_rescale(a[i:i + 1], b[i:i + 1])[0], out[i])
+        assert np.array_equal(ev.apply_galois(a[i:i + 1], elt)[0], rot[i])
+    # composition: fused pipeline == multiply -> relinearize -> rescale
+    c2 = ev.rescale_to_next(ev.relinearize(ev.multiply(da, db)))
+    assert np.array_equal(c2.cpu().numpy().view(np.uint64), out)
+    # rotate by +1 then -1 is NOT the identity on raw limbs with synthetic keys, but conjugating
+    # twice permutes back: check the permutation part (component-wise gather) is an involution
+    t = ctx.galois_table(2 * N - 1)
+    assert np.array_equal(t[t], np.arange(N, dtype=np.uint32))
+    ctx.close()
+
+
+def test_error_convention(cudalib):
+    """Argument errors -> ValueError (std::invalid_argument), evaluator.cpp:238-249,781-796,1872-1887."""
+    import gemini_seal_b200 as g
+    mods = ntt_primes(10, 40, 4)
+    ctx = g.Context(1024, mods, 1, lib=cudalib)
+    ev = g.Evaluator(ctx)
+    rng = np.random.default_rng(0)
+    a = rand_poly(rng, mods[:3], (1, 2), 1024)
+    c3 = rand_poly(rng, mods[:3], (1, 3), 1024)
+    with pytest.raises(ValueError):
+        ev.relinearize(c3)  # no relin keys uploaded
+    with pytest.raises(ValueError):
+        ev.apply_galois(a, 3)  # no Galois key
+    with pytest.raises(ValueError):
+        ev.apply_galois(a, 4)  # even element
+    with pytest.raises(ValueError):
+        ctx.galois_elt_from_step(512)
+    with pytest.raises(ValueError):
+        ctx.set_relin_keys(np.zeros((2, 2, 4, 1024), dtype=np.uint64))  # wrong bundle count
+    with pytest.raises(ValueError):
+        ev.rescale_to_next(rand_poly(rng, mods[:1], (1, 2), 1024))  # last level
+    with pytest.raises(ValueError):
+        ev.multiply(a, rand_poly(rng, mods[:2], (1, 2), 1024))
+    with pytest.raises(ValueError):
+        g.Context(1024, [mods[0], mods[0]], 1, lib=cudalib)
+    with pytest.raises(ValueError):
+        g.Context(1024, [97, 193], 1, lib=cudalib)  # 97 is not 1 mod 2N
+    ctx.close()
