@@ -57,12 +57,17 @@ PROTOTYPES = {
     "gsb_rescale_host": (i32, [vp, vp, vp, sz, sz, sz]),
     "gsb_apply_galois_host": (i32, [vp, u32, vp, vp, sz, sz]),
     "gsb_mul_relin_rescale_host": (i32, [vp, vp, vp, vp, sz, sz]),
+    "gsb_int_peak": (i32, [vp, i32, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double)]),
 }
+# measurement aids that the test-only simulator build does not provide
+CUDA_ONLY = {"gsb_int_peak"}
 
 
 def bind(lib):
     """Attach prototypes; raises AttributeError if a declared symbol is not exported."""
     for name, (res, args) in PROTOTYPES.items():
+        if name in CUDA_ONLY and not hasattr(lib, name):
+            continue
         fn = getattr(lib, name)
         fn.restype = res
         fn.argtypes = args

@@ -49,3 +49,55 @@ namespace gsb
 #endif
     }
 } // namespace gsb
+
+// ---- TMA 1-D bulk copy (cp.async.bulk) + mbarrier helpers -------------------------------------------
+// Used to stage the twiddle segments of a tile into shared memory asynchronously.  One thread arms
+// the barrier with the byte count and issues the copies; every thread waits on phase parity 0.
+// Under the test-only simulator the copy is a plain memcpy and the wait is a __syncthreads().
+namespace gsb
+{
+#ifdef GSB_CUSIM
+    GSB_DEV void mbar_init(uint64_t *) {}
+    GSB_DEV void mbar_expect(uint64_t *, uint32_t) {}
+    GSB_DEV void bulk_g2s(void *dst, const void *src, uint32_t bytes, uint64_t *)
+    {
+        memcpy(dst, src, bytes);
+    }
+    GSB_DEV void mbar_wait(uint64_t *, uint32_t)
+    {
+        __syncthreads();
+    }
+#else
+    GSB_DEV uint32_t smem_u32(const void *p)
+    {
+        return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+    }
+    GSB_DEV void mbar_init(uint64_t *bar)
+    {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(bar)));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    GSB_DEV void mbar_expect(uint64_t *bar, uint32_t bytes)
+    {
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+    }
+    GSB_DEV void bulk_g2s(void *dst, const void *src, uint32_t bytes, uint64_t *bar)
+    {
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
+                     "l"(src), "r"(bytes), "r"(smem_u32(bar))
+                     : "memory");
+    }
+    GSB_DEV void mbar_wait(uint64_t *bar, uint32_t parity)
+    {
+        asm volatile(
+            "{\n"
+            ".reg .pred p;\n"
+            "WAIT_LOOP:\n"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+            "@!p bra WAIT_LOOP;\n"
+            "}\n" ::"r"(smem_u32(bar)),
+            "r"(parity)
+            : "memory");
+    }
+#endif
+} // namespace gsb

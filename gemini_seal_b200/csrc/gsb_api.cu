@@ -486,3 +486,6 @@ int gsb_poly_op_dev(
 } // extern "C"
 
 #include "gsb_evaluator.cuh"
+#ifndef GSB_CUSIM
+#include "int_peak.cuh"
+#endif

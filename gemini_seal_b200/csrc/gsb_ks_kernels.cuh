@@ -92,11 +92,6 @@ namespace gsb
         }
         GSB_DEV uint64_t convert(uint32_t d) const
         {
-            if (cnt == 1)
-            {
-                const uint64_t v = src[d];
-                return reduce ? barrett63(v, q, cr1) : v;
-            }
             uint64_t lo = 0, hi = 0;
             for (int i = 0; i < cnt; i++)
             {
@@ -105,14 +100,16 @@ namespace gsb
             }
             return barrett128(lo, hi, q, cr0, cr1);
         }
-        GSB_DEV uint64_t load(uint32_t d) const { return convert(d); }
-        GSB_DEV void load2(uint32_t d, uint64_t &x, uint64_t &y) const
+        // single-limb bundle: raw = the load, xform = the optional Barrett-63; multi-limb bundle: the
+        // whole conversion happens in raw (several source limbs per word)
+        GSB_DEV uint64_t raw(uint32_t d) const { return cnt == 1 ? src[d] : convert(d); }
+        GSB_DEV void raw2(uint32_t d, uint64_t &x, uint64_t &y) const
         {
             if (cnt == 1)
             {
                 const ulonglong2 v = *reinterpret_cast<const ulonglong2 *>(src + d);
-                x = reduce ? barrett63(v.x, q, cr1) : v.x;
-                y = reduce ? barrett63(v.y, q, cr1) : v.y;
+                x = v.x;
+                y = v.y;
             }
             else
             {
@@ -120,6 +117,7 @@ namespace gsb
                 y = convert(d + 1);
             }
         }
+        GSB_DEV uint64_t xform(uint64_t v) const { return reduce ? barrett63(v, q, cr1) : v; }
     };
 
     // grid: y = ext slot kap, z = b*beta + j; slots inside the source bundle are skipped.
@@ -158,7 +156,7 @@ namespace gsb
         const uint64_t *ih;  // inv_hat
         const uint64_t *nh;  // neg_hat + i*k
         const LimbC *plimb;  // limb + L0
-        uint64_t q, cr0, cr1;
+        uint64_t q, cr0, cr1, p0, p0cr1;
         uint32_t N;
         int k;
         GSB_DEV MdLoad(const Args &a, int y, int z, int, const LimbC &c, uint32_t N_)
@@ -172,16 +170,11 @@ namespace gsb
             cr1 = c.cr1;
             N = N_;
             k = static_cast<int>(a.ks.k);
+            p0 = plimb[0].q;
+            p0cr1 = plimb[0].cr1;
         }
-        GSB_DEV uint64_t load(uint32_t d) const
+        GSB_DEV uint64_t convert(uint32_t d) const
         {
-            if (k == 1)
-            {
-                // :268-275: negate(barrett_reduce_63(c_p)) then barrett_reduce_128 of (v, 0)
-                const uint64_t p = plimb[0].q;
-                const uint64_t v = neg_mod(barrett63(sp[d], p, plimb[0].cr1), p);
-                return barrett128(v, 0, q, cr0, cr1);
-            }
             uint64_t lo = 0, hi = 0;
             for (int j = 0; j < k; j++)
             {
@@ -190,10 +183,19 @@ namespace gsb
             }
             return barrett128(lo, hi, q, cr0, cr1);
         }
-        GSB_DEV void load2(uint32_t d, uint64_t &x, uint64_t &y) const
+        GSB_DEV uint64_t raw(uint32_t d) const { return k == 1 ? sp[d] : convert(d); }
+        GSB_DEV void raw2(uint32_t d, uint64_t &x, uint64_t &y) const
         {
-            x = load(d);
-            y = load(d + 1);
+            x = raw(d);
+            y = raw(d + 1);
+        }
+        GSB_DEV uint64_t xform(uint64_t v) const
+        {
+            if (k != 1)
+                return v;
+            // :268-275: negate(barrett_reduce_63(c_p)) then barrett_reduce_128 of (v, 0)
+            const uint64_t t = neg_mod(barrett63(v, p0, p0cr1), p0);
+            return barrett128(t, 0, q, cr0, cr1);
         }
     };
 
@@ -285,13 +287,13 @@ namespace gsb
         GSB_DEV RsLoad(const Args &a, int y, int z, int, const LimbC &c, uint32_t N)
             : t(a.t + static_cast<size_t>(z) * N), q(c.q), cr1(c.cr1), nh(a.neg_half[y]), reduce(c.q < a.q_last)
         {}
-        GSB_DEV uint64_t one(uint64_t v) const { return (reduce ? barrett63(v, q, cr1) : v) + nh; }
-        GSB_DEV uint64_t load(uint32_t d) const { return one(t[d]); }
-        GSB_DEV void load2(uint32_t d, uint64_t &x, uint64_t &y) const
+        GSB_DEV uint64_t xform(uint64_t v) const { return (reduce ? barrett63(v, q, cr1) : v) + nh; }
+        GSB_DEV uint64_t raw(uint32_t d) const { return t[d]; }
+        GSB_DEV void raw2(uint32_t d, uint64_t &x, uint64_t &y) const
         {
             const ulonglong2 v = *reinterpret_cast<const ulonglong2 *>(t + d);
-            x = one(v.x);
-            y = one(v.y);
+            x = v.x;
+            y = v.y;
         }
     };
 
@@ -355,12 +357,14 @@ namespace gsb
         static constexpr bool two_pass = Split<LOGN>::two_pass;
         static constexpr int T = two_pass ? 8 : Split<LOGN>::T1;
         static constexpr int G_HI = two_pass ? LOGN - Split<LOGN>::A - 1 : LOGN - 1;
+        typedef TilePlan<T, G_HI, 0> TP;
     };
 
     template <int LOGN>
-    __global__ void __launch_bounds__(1 << MacPlan<LOGN>::T) ks_mac_kernel(KsMacArgs p, NttTables tab)
+    __global__ void __launch_bounds__(1 << MacPlan<LOGN>::T, MacPlan<LOGN>::T <= 8 ? 2 : 1) ks_mac_kernel(KsMacArgs p, NttTables tab)
     {
         typedef MacPlan<LOGN> MP;
+        typedef typename MP::TP TP;
         constexpr int T = MP::T;
         const KsDev &ks = p.ks;
         const int b = blockIdx.x, tile = blockIdx.y, kap = blockIdx.z;
@@ -370,52 +374,87 @@ namespace gsb
         const Twiddle *WW = tab.WW + static_cast<size_t>(mod) * N;
         const ContigMap<T> map{ N };
         const uint32_t d0 = map.coeff(tile, tid * 8);
-        uint64_t lo[2][8], hi[2][8];
-#pragma unroll
-        for (int r = 0; r < 8; r++)
-            lo[0][r] = hi[0][r] = lo[1][r] = hi[1][r] = 0;
-        int parity = 0;
-        const KeepInRegs keep;
-        for (int j = 0; j < static_cast<int>(ks.beta); j++)
-        {
-            const int s0 = j * static_cast<int>(ks.k);
-            uint64_t x[8];
-            if (kap >= s0 && kap < s0 + static_cast<int>(ks.k) && kap < static_cast<int>(ks.L))
+        uint64_t *smem = dyn_smem();
+        Twiddle *tws = reinterpret_cast<Twiddle *>(smem + TP::exch_words);
+        uint64_t *bar = reinterpret_cast<uint64_t *>(tws + TP::PAIRS);
+        if (tid == 0)
+            mbar_init(bar);
+        __syncthreads();
+        if (tid == 0)
+            TP::TwC::stage(tws, WW, N, map.off(tile), false, bar);
+        const typename TP::TwC tw{ tws, TwGlobal{ WW, N, map.off(tile), N } };
+        const int nb = static_cast<int>(ks.beta), k = static_cast<int>(ks.k), L = static_cast<int>(ks.L);
+        auto in_bundle = [&](int j) { return kap >= j * k && kap < j * k + k && kap < L; };
+        // raw loads of bundle j's operand tile into xn (first-round register layout, or the final
+        // layout for the in-bundle limb that needs no transform)
+        auto load_bundle = [&](int j, uint64_t (&xn)[8]) {
+            if (in_bundle(j))
             {
                 const uint64_t *t = p.target + static_cast<size_t>(b) * p.target_stride + static_cast<size_t>(kap) * N + d0;
 #pragma unroll
                 for (int r = 0; r < 8; r += 2)
                 {
                     const ulonglong2 v = *reinterpret_cast<const ulonglong2 *>(t + r);
-                    x[r] = v.x;
-                    x[r + 1] = v.y;
+                    xn[r] = v.x;
+                    xn[r + 1] = v.y;
                 }
+            }
+            else if constexpr (MP::two_pass)
+            {
+                const PlainPro pro(p.ext1, static_cast<size_t>(ks.E) * N, kap, b * nb + j, N);
+                xf_load_raw<T, MP::G_HI, 0, false>(xn, tid, tile, map, pro);
             }
             else
             {
-                if constexpr (MP::two_pass)
-                {
-                    const PlainPro pro(p.ext1, static_cast<size_t>(ks.E) * N, kap, b * static_cast<int>(ks.beta) + j, N);
-                    fwd_rounds<T, MP::G_HI, 0, true, 0>(x, dyn_smem(), tid, tile, map, pro, keep, WW, c, parity);
-                }
-                else
-                {
-                    const ModupCore pro(ks, p.coef, b, j, kap, c);
-                    fwd_rounds<T, MP::G_HI, 0, true, 0>(x, dyn_smem(), tid, tile, map, pro, keep, WW, c, parity);
-                }
-                __syncthreads(); // the exchange buffers are reused by the next bundle
+                const ModupCore pro(ks, p.coef, b, j, kap, c);
+                xf_load_raw<T, MP::G_HI, 0, false>(xn, tid, tile, map, pro);
             }
+        };
+        uint64_t lo[2][8], hi[2][8], xn[8];
+#pragma unroll
+        for (int r = 0; r < 8; r++)
+            lo[0][r] = hi[0][r] = lo[1][r] = hi[1][r] = 0;
+        load_bundle(0, xn);
+        mbar_wait(bar, 0);
+        int parity = 0;
+        for (int j = 0; j < nb; j++)
+        {
+            uint64_t x[8];
+            const bool direct = in_bundle(j);
+            if (!MP::two_pass && !direct)
+            {
+                const ModupCore pro(ks, p.coef, b, j, kap, c);
+#pragma unroll
+                for (int r = 0; r < 8; r++)
+                    x[r] = pro.xform(xn[r]);
+            }
+            else
+            {
+#pragma unroll
+                for (int r = 0; r < 8; r++)
+                    x[r] = xn[r];
+            }
+            // key words of this bundle and the next bundle's operand: in flight during the butterflies
             const uint64_t *k0 = p.key + (static_cast<size_t>(j * 2) * p.K + mod) * N + d0;
             const uint64_t *k1 = k0 + static_cast<size_t>(p.K) * N;
+            ulonglong2 u[4], v[4];
 #pragma unroll
-            for (int r = 0; r < 8; r += 2)
+            for (int r = 0; r < 4; r++)
             {
-                const ulonglong2 u = __ldg(reinterpret_cast<const ulonglong2 *>(k0 + r));
-                const ulonglong2 v = __ldg(reinterpret_cast<const ulonglong2 *>(k1 + r));
-                mac128(lo[0][r], hi[0][r], x[r], u.x);
-                mac128(lo[0][r + 1], hi[0][r + 1], x[r + 1], u.y);
-                mac128(lo[1][r], hi[1][r], x[r], v.x);
-                mac128(lo[1][r + 1], hi[1][r + 1], x[r + 1], v.y);
+                u[r] = __ldg(reinterpret_cast<const ulonglong2 *>(k0) + r);
+                v[r] = __ldg(reinterpret_cast<const ulonglong2 *>(k1) + r);
+            }
+            if (j + 1 < nb)
+                load_bundle(j + 1, xn);
+            if (!direct)
+                fwd_compute<T, MP::G_HI, 0, true, 0>(x, smem, tid, tw, c, parity);
+#pragma unroll
+            for (int r = 0; r < 4; r++)
+            {
+                mac128(lo[0][2 * r], hi[0][2 * r], x[2 * r], u[r].x);
+                mac128(lo[0][2 * r + 1], hi[0][2 * r + 1], x[2 * r + 1], u[r].y);
+                mac128(lo[1][2 * r], hi[1][2 * r], x[2 * r], v[r].x);
+                mac128(lo[1][2 * r + 1], hi[1][2 * r + 1], x[2 * r + 1], v[r].y);
             }
         }
 #pragma unroll

@@ -27,19 +27,20 @@ namespace gsb
     // SlothfulNTT::mulmodLazy (util/ntt.cpp:230-234): x*y - hi64(x*y')*q  (mod 2^64), in [0,2q).
     GSB_DEV uint64_t mulmod_lazy(uint64_t x, uint64_t y, uint64_t ys, uint64_t q)
     {
-        return x * y - mulhi(x, ys) * q;
+        // x*y - h*q == x*y + h*(2^64 - q) (mod 2^64): one multiply-add chain, no negate
+        return x * y + mulhi(x, ys) * (0 - q);
     }
 
     // SlothfulNTT::reduceBarrettLazy (util/ntt.cpp:237-241)
     GSB_DEV uint64_t reduce_barrett_lazy(uint64_t x, uint64_t rdp, uint64_t q)
     {
-        return x - mulhi(x, rdp) * q;
+        return x + mulhi(x, rdp) * (0 - q);
     }
 
     // MulModShoup::operator() (multi_special_primes.cpp:13-19) / FastMulMod (uintarithsmallmod.h:312-322)
     GSB_DEV uint64_t mulmod_shoup(uint64_t x, uint64_t c, uint64_t cs, uint64_t p)
     {
-        uint64_t t = x * c - mulhi(x, cs) * p;
+        uint64_t t = x * c + mulhi(x, cs) * (0 - p);
         return t - (t >= p ? p : 0);
     }
 
@@ -55,14 +56,14 @@ namespace gsb
         uint64_t s = tmp1 + lo;
         carry = hi + (s < tmp1 ? 1 : 0);
         uint64_t quot = z1 * cr1 + tmp3 + carry;
-        uint64_t r = z0 - quot * q;
+        uint64_t r = z0 + quot * (0 - q);
         return r - (r >= q ? q : 0);
     }
 
     // barrett_reduce_63 (util/uintarithsmallmod.h:181-207)
     GSB_DEV uint64_t barrett63(uint64_t x, uint64_t q, uint64_t cr1)
     {
-        uint64_t r = x - mulhi(x, cr1) * q;
+        uint64_t r = x + mulhi(x, cr1) * (0 - q);
         return r - (r >= q ? q : 0);
     }
 

@@ -127,27 +127,102 @@ namespace gsb
         }
     }
 
+    // ---- twiddle sources ------------------------------------------------------------------------
+    // fwd(g, local, grp) / inv(g, local, grp): the Shoup twiddle of the stage with tile gap 2^g for the
+    // butterfly group that contains tile-local index `local`, plus `grp` groups.  (Indexing rules at
+    // the top of this file.)
+    //
+    // TwGlobal reads the tables straight from global memory (L2 / L1).
+    struct TwGlobal
+    {
+        const Twiddle *tab; // WW (forward) or VV (inverse) of the limb's modulus
+        uint32_t S, off, N;
+        GSB_DEV Twiddle fwd(int g, uint32_t local, int grp) const
+        {
+            return __ldg(tab + (S >> (g + 1)) + ((off + local) >> (g + 1)) + grp);
+        }
+        GSB_DEV Twiddle inv(int g, uint32_t local, int grp) const
+        {
+            return __ldg(tab + N - 2u * (S >> (g + 1)) + 1u + ((off + local) >> (g + 1)) + grp);
+        }
+    };
+
+    // TwContigSmem: contiguous tile of 2^TILE_LOG words at coefficient offset `off`.  The stage with
+    // gap 2^g uses the 2^TILE_LOG >> (g+1) consecutive table entries starting at
+    //   forward: W[(N >> (g+1)) + (off >> (g+1))]      inverse: V[N - 2(N >> (g+1)) + 1 + (off >> (g+1))]
+    // which a single thread stages into shared memory with one TMA bulk copy per stage
+    // (segment g at pair offset TILE - (TILE >> g)); stages g > G_SM stay on the global path.
+    template <int TILE_LOG, int G_SM>
+    struct TwContigSmem
+    {
+        static constexpr uint32_t TILE = 1u << TILE_LOG;
+        static constexpr uint32_t PAIRS = TILE - (TILE >> (G_SM + 1)); // pairs staged for g = 0..G_SM
+        const Twiddle *sm;
+        TwGlobal gl;
+        GSB_DEV static uint32_t seg(int g) { return TILE - (TILE >> g); }
+        GSB_DEV Twiddle fwd(int g, uint32_t local, int grp) const
+        {
+            return g <= G_SM ? sm[seg(g) + (local >> (g + 1)) + grp] : gl.fwd(g, local, grp);
+        }
+        GSB_DEV Twiddle inv(int g, uint32_t local, int grp) const
+        {
+            return g <= G_SM ? sm[seg(g) + (local >> (g + 1)) + grp] : gl.inv(g, local, grp);
+        }
+        // issued by ONE thread after mbar_init + a CTA barrier
+        GSB_DEV static void stage(Twiddle *sm, const Twiddle *tab, uint32_t N, uint32_t off, bool inverse, uint64_t *bar)
+        {
+            mbar_expect(bar, PAIRS * static_cast<uint32_t>(sizeof(Twiddle)));
+#pragma unroll
+            for (int g = 0; g <= G_SM; g++)
+            {
+                const uint32_t m = N >> (g + 1);
+                const Twiddle *src = tab + (inverse ? N - 2u * m + 1u : m) + (off >> (g + 1));
+                bulk_g2s(sm + seg(g), src, (TILE >> (g + 1)) * static_cast<uint32_t>(sizeof(Twiddle)), bar);
+            }
+        }
+    };
+
+    // TwColsSmem: column tile (2^A rows): every stage indexes the first 2^A forward entries, or the
+    // last 2^A inverse entries, of the table -- 2^A pairs staged with one bulk copy.
+    template <int A, int C>
+    struct TwColsSmem
+    {
+        static constexpr uint32_t PAIRS = 1u << A;
+        const Twiddle *sm;
+        GSB_DEV Twiddle fwd(int g, uint32_t local, int grp) const
+        {
+            return sm[((1u << (A + C)) >> (g + 1)) + (local >> (g + 1)) + grp];
+        }
+        GSB_DEV Twiddle inv(int g, uint32_t local, int grp) const
+        {
+            return sm[PAIRS - 2u * ((1u << (A + C)) >> (g + 1)) + 1u + (local >> (g + 1)) + grp];
+        }
+        GSB_DEV static void stage(Twiddle *sm, const Twiddle *tab, uint32_t N, bool inverse, uint64_t *bar)
+        {
+            mbar_expect(bar, PAIRS * static_cast<uint32_t>(sizeof(Twiddle)));
+            bulk_g2s(sm, inverse ? tab + N - PAIRS : tab, PAIRS * static_cast<uint32_t>(sizeof(Twiddle)), bar);
+        }
+    };
+
     // ---- forward round: ForwardLazy / ForwardLazyLast (util/ntt.cpp:245-261) -------------------
     // LAST: this transform's gap-2^0 stage is the global last stage (h = 1), where x0 is first
     // reduced with reduceBarrettLazy.
-    template <int TOP, int R, int T_LOG, bool LAST>
-    GSB_DEV void fwd_round(
-        uint64_t (&x)[8], uint32_t tid, uint32_t off, uint32_t S, const Twiddle *__restrict__ WW, const LimbC &c)
+    template <int TOP, int R, int T_LOG, bool LAST, class TW>
+    GSB_DEV void fwd_round(uint64_t (&x)[8], uint32_t tid, const TW &tw, const LimbC &c)
     {
 #pragma unroll
         for (int sub = 0; sub < (8 >> R); sub++)
         {
-            const uint32_t base = off + group_base<TOP, R, T_LOG>(tid, sub);
+            const uint32_t base = group_base<TOP, R, T_LOG>(tid, sub);
 #pragma unroll
             for (int s = 0; s < R; s++)
             {
                 const int g = TOP - s;
                 const int half = 1 << (R - 1 - s);
-                const uint32_t tw0 = (S >> (g + 1)) + (base >> (g + 1));
 #pragma unroll
                 for (int grp = 0; grp < (1 << s); grp++)
                 {
-                    const Twiddle w = __ldg(WW + tw0 + grp);
+                    const Twiddle w = tw.fwd(g, base, grp);
 #pragma unroll
                     for (int i = 0; i < half; i++)
                     {
@@ -167,26 +242,22 @@ namespace gsb
     // ---- inverse round: BackwardLazy / BackwardLazyLast (util/ntt.cpp:265-281) -----------------
     // Round covers gaps 2^BOT ... 2^(BOT+R-1), smallest first.  LAST: the gap-2^(BOT+R-1) stage is
     // the global last stage (m = 1), where n^-1 is folded in (util/ntt.cpp:391-402).
-    template <int BOT, int R, int T_LOG, bool LAST>
-    GSB_DEV void inv_round(
-        uint64_t (&x)[8], uint32_t tid, uint32_t off, uint32_t S, uint32_t N, const Twiddle *__restrict__ VV,
-        const LimbC &c)
+    template <int BOT, int R, int T_LOG, bool LAST, class TW>
+    GSB_DEV void inv_round(uint64_t (&x)[8], uint32_t tid, const TW &tw, const LimbC &c)
     {
         constexpr int TOP = BOT + R - 1;
 #pragma unroll
         for (int sub = 0; sub < (8 >> R); sub++)
         {
-            const uint32_t base = off + group_base<TOP, R, T_LOG>(tid, sub);
+            const uint32_t base = group_base<TOP, R, T_LOG>(tid, sub);
 #pragma unroll
             for (int s = 0; s < R; s++)
             {
                 const int g = BOT + s;
-                const uint32_t m = S >> (g + 1);
-                const uint32_t tw0 = N - 2u * m + 1u + (base >> (g + 1));
 #pragma unroll
                 for (int grp = 0; grp < (1 << (R - 1 - s)); grp++)
                 {
-                    const Twiddle w = __ldg(VV + tw0 + grp);
+                    const Twiddle w = tw.inv(g, base, grp);
 #pragma unroll
                     for (int i = 0; i < (1 << s); i++)
                     {
@@ -252,12 +323,93 @@ namespace gsb
     };
 
     // ---- generic forward / inverse tile transforms ----------------------------------------------
-    // Runs the stages with tile gaps 2^G_HI ... 2^G_LO.  First round loads through `pro`, last
-    // round stores through `epi`; both see coefficient indices, never tile indices.
-    template <int T_LOG, int G_HI, int G_LO, bool LAST, int IDX, class Map, class Pro, class Epi>
-    GSB_DEV void fwd_rounds(
-        uint64_t (&x)[8], uint64_t *smem, uint32_t tid, uint32_t tile, const Map &map, const Pro &pro, const Epi &epi,
-        const Twiddle *__restrict__ WW, const LimbC &c, int &parity)
+    // A transform over tile gaps 2^G_HI ... 2^G_LO is: tile_load (raw global loads in the register
+    // layout of the first round) -> tile_xform (the prologue's arithmetic) -> *_compute (all rounds,
+    // exchanging through shared memory) -> tile_store (epilogue, register layout of the last round).
+    // Loads are split from the prologue arithmetic so a kernel can issue the NEXT tile's loads before
+    // it computes on the current one.  Pro/Epi see coefficient indices, never tile indices.
+    template <int NS, bool INVERSE>
+    struct RoundPlan
+    {
+        static constexpr int NR = plan_count(NS);
+        // plan index of the first / last round EXECUTED (the inverse walks the plan backwards)
+        static constexpr int first = INVERSE ? NR - 1 : 0;
+        static constexpr int last = INVERSE ? 0 : NR - 1;
+    };
+
+    template <int TOP, int R, int T_LOG, class Map, class Pro>
+    GSB_DEV void tile_load_raw(uint64_t (&x)[8], uint32_t tid, uint32_t tile, const Map &map, const Pro &pro)
+    {
+        constexpr int low = TOP - R + 1;
+#pragma unroll
+        for (int sub = 0; sub < (8 >> R); sub++)
+        {
+            const uint32_t base = group_base<TOP, R, T_LOG>(tid, sub);
+            if (low == 0 && R == 3)
+            {
+#pragma unroll
+                for (int i = 0; i < 8; i += 2)
+                    pro.raw2(map.coeff(tile, base + i), x[i], x[i + 1]);
+            }
+            else
+            {
+#pragma unroll
+                for (int i = 0; i < (1 << R); i++)
+                    x[sub * (1 << R) + i] = pro.raw(map.coeff(tile, base + (static_cast<uint32_t>(i) << low)));
+            }
+        }
+    }
+
+    template <class Pro>
+    GSB_DEV void tile_xform(uint64_t (&x)[8], const Pro &pro)
+    {
+#pragma unroll
+        for (int i = 0; i < 8; i++)
+            x[i] = pro.xform(x[i]);
+    }
+
+    template <int TOP, int R, int T_LOG, class Map, class Epi>
+    GSB_DEV void tile_store_global(const uint64_t (&x)[8], uint32_t tid, uint32_t tile, const Map &map, const Epi &epi)
+    {
+        constexpr int low = TOP - R + 1;
+#pragma unroll
+        for (int sub = 0; sub < (8 >> R); sub++)
+        {
+            const uint32_t base = group_base<TOP, R, T_LOG>(tid, sub);
+            if (low == 0 && R == 3)
+            {
+#pragma unroll
+                for (int i = 0; i < 8; i += 2)
+                    epi.store2(map.coeff(tile, base + i), x[i], x[i + 1], i);
+            }
+            else
+            {
+#pragma unroll
+                for (int i = 0; i < (1 << R); i++)
+                    epi.store(map.coeff(tile, base + (static_cast<uint32_t>(i) << low)), x[sub * (1 << R) + i], sub * (1 << R) + i);
+            }
+        }
+    }
+
+    // Loads / stores of a whole transform (first / last executed round's layout).
+    template <int T_LOG, int G_HI, int G_LO, bool INVERSE, class Map, class Pro>
+    GSB_DEV void xf_load_raw(uint64_t (&x)[8], uint32_t tid, uint32_t tile, const Map &map, const Pro &pro)
+    {
+        constexpr int NS = G_HI - G_LO + 1;
+        constexpr int PI = RoundPlan<NS, INVERSE>::first;
+        tile_load_raw<G_HI - plan_before(NS, PI), plan_size(NS, PI), T_LOG>(x, tid, tile, map, pro);
+    }
+    template <int T_LOG, int G_HI, int G_LO, bool INVERSE, class Map, class Epi>
+    GSB_DEV void xf_store(const uint64_t (&x)[8], uint32_t tid, uint32_t tile, const Map &map, const Epi &epi)
+    {
+        constexpr int NS = G_HI - G_LO + 1;
+        constexpr int PI = RoundPlan<NS, INVERSE>::last;
+        tile_store_global<G_HI - plan_before(NS, PI), plan_size(NS, PI), T_LOG>(x, tid, tile, map, epi);
+    }
+
+    // All rounds of a forward transform; x enters in the first round's layout, leaves in the last's.
+    template <int T_LOG, int G_HI, int G_LO, bool LAST, int IDX, class TW>
+    GSB_DEV void fwd_compute(uint64_t (&x)[8], uint64_t *smem, uint32_t tid, const TW &tw, const LimbC &c, int &parity)
     {
         constexpr int NS = G_HI - G_LO + 1;
         constexpr int NR = plan_count(NS);
@@ -265,69 +417,26 @@ namespace gsb
         {
             constexpr int R = plan_size(NS, IDX);
             constexpr int TOP = G_HI - plan_before(NS, IDX);
-            constexpr int low = TOP - R + 1;
-            if constexpr (IDX == 0)
-            {
-#pragma unroll
-                for (int sub = 0; sub < (8 >> R); sub++)
-                {
-                    uint32_t base = group_base<TOP, R, T_LOG>(tid, sub);
-                    if (low == 0 && R == 3)
-                    {
-#pragma unroll
-                        for (int i = 0; i < 8; i += 2)
-                            pro.load2(map.coeff(tile, base + i), x[i], x[i + 1]);
-                    }
-                    else
-                    {
-#pragma unroll
-                        for (int i = 0; i < (1 << R); i++)
-                            x[sub * (1 << R) + i] = pro.load(map.coeff(tile, base + (static_cast<uint32_t>(i) << low)));
-                    }
-                }
-            }
-            else
+            if constexpr (IDX > 0)
             {
                 uint64_t *buf = smem + (static_cast<size_t>(parity) << (T_LOG + 3));
                 parity ^= 1;
                 __syncthreads();
                 tile_load<TOP, R, T_LOG>(buf, x, tid);
             }
-            fwd_round<TOP, R, T_LOG, LAST>(x, tid, map.off(tile), map.S(), WW, c);
-            if constexpr (IDX == NR - 1)
-            {
-#pragma unroll
-                for (int sub = 0; sub < (8 >> R); sub++)
-                {
-                    uint32_t base = group_base<TOP, R, T_LOG>(tid, sub);
-                    if (low == 0 && R == 3)
-                    {
-#pragma unroll
-                        for (int i = 0; i < 8; i += 2)
-                            epi.store2(map.coeff(tile, base + i), x[i], x[i + 1], i);
-                    }
-                    else
-                    {
-#pragma unroll
-                        for (int i = 0; i < (1 << R); i++)
-                            epi.store(map.coeff(tile, base + (static_cast<uint32_t>(i) << low)), x[sub * (1 << R) + i], sub * (1 << R) + i);
-                    }
-                }
-            }
-            else
+            fwd_round<TOP, R, T_LOG, LAST>(x, tid, tw, c);
+            if constexpr (IDX < NR - 1)
             {
                 uint64_t *buf = smem + (static_cast<size_t>(parity) << (T_LOG + 3));
                 tile_store<TOP, R, T_LOG>(buf, x, tid);
-                fwd_rounds<T_LOG, G_HI, G_LO, LAST, IDX + 1>(x, smem, tid, tile, map, pro, epi, WW, c, parity);
+                fwd_compute<T_LOG, G_HI, G_LO, LAST, IDX + 1>(x, smem, tid, tw, c, parity);
             }
         }
     }
 
     // Inverse: rounds run in the reverse order of the forward plan (smallest gaps first).
-    template <int T_LOG, int G_HI, int G_LO, bool LAST, int IDX, class Map, class Pro, class Epi>
-    GSB_DEV void inv_rounds(
-        uint64_t (&x)[8], uint64_t *smem, uint32_t tid, uint32_t tile, const Map &map, const Pro &pro, const Epi &epi,
-        const Twiddle *__restrict__ VV, uint32_t N, const LimbC &c, int &parity)
+    template <int T_LOG, int G_HI, int G_LO, bool LAST, int IDX, class TW>
+    GSB_DEV void inv_compute(uint64_t (&x)[8], uint64_t *smem, uint32_t tid, const TW &tw, const LimbC &c, int &parity)
     {
         constexpr int NS = G_HI - G_LO + 1;
         constexpr int NR = plan_count(NS);
@@ -337,59 +446,19 @@ namespace gsb
             constexpr int R = plan_size(NS, PI);
             constexpr int TOP = G_HI - plan_before(NS, PI);
             constexpr int BOT = TOP - R + 1;
-            if constexpr (IDX == 0)
-            {
-#pragma unroll
-                for (int sub = 0; sub < (8 >> R); sub++)
-                {
-                    uint32_t base = group_base<TOP, R, T_LOG>(tid, sub);
-                    if (BOT == 0 && R == 3)
-                    {
-#pragma unroll
-                        for (int i = 0; i < 8; i += 2)
-                            pro.load2(map.coeff(tile, base + i), x[i], x[i + 1]);
-                    }
-                    else
-                    {
-#pragma unroll
-                        for (int i = 0; i < (1 << R); i++)
-                            x[sub * (1 << R) + i] = pro.load(map.coeff(tile, base + (static_cast<uint32_t>(i) << BOT)));
-                    }
-                }
-            }
-            else
+            if constexpr (IDX > 0)
             {
                 uint64_t *buf = smem + (static_cast<size_t>(parity) << (T_LOG + 3));
                 parity ^= 1;
                 __syncthreads();
                 tile_load<TOP, R, T_LOG>(buf, x, tid);
             }
-            inv_round<BOT, R, T_LOG, (LAST && IDX == NR - 1)>(x, tid, map.off(tile), map.S(), N, VV, c);
-            if constexpr (IDX == NR - 1)
-            {
-#pragma unroll
-                for (int sub = 0; sub < (8 >> R); sub++)
-                {
-                    uint32_t base = group_base<TOP, R, T_LOG>(tid, sub);
-                    if (BOT == 0 && R == 3)
-                    {
-#pragma unroll
-                        for (int i = 0; i < 8; i += 2)
-                            epi.store2(map.coeff(tile, base + i), x[i], x[i + 1], i);
-                    }
-                    else
-                    {
-#pragma unroll
-                        for (int i = 0; i < (1 << R); i++)
-                            epi.store(map.coeff(tile, base + (static_cast<uint32_t>(i) << BOT)), x[sub * (1 << R) + i], sub * (1 << R) + i);
-                    }
-                }
-            }
-            else
+            inv_round<BOT, R, T_LOG, (LAST && IDX == NR - 1)>(x, tid, tw, c);
+            if constexpr (IDX < NR - 1)
             {
                 uint64_t *buf = smem + (static_cast<size_t>(parity) << (T_LOG + 3));
                 tile_store<TOP, R, T_LOG>(buf, x, tid);
-                inv_rounds<T_LOG, G_HI, G_LO, LAST, IDX + 1>(x, smem, tid, tile, map, pro, epi, VV, N, c, parity);
+                inv_compute<T_LOG, G_HI, G_LO, LAST, IDX + 1>(x, smem, tid, tw, c, parity);
             }
         }
     }

@@ -40,13 +40,15 @@ namespace gsb
         GSB_DEV PlainPro(const uint64_t *base, size_t zs, int y, int z, uint32_t N)
             : p(base + static_cast<size_t>(z) * zs + static_cast<size_t>(y) * N)
         {}
-        GSB_DEV uint64_t load(uint32_t d) const { return p[d]; }
-        GSB_DEV void load2(uint32_t d, uint64_t &a, uint64_t &b) const
+        // raw / raw2: the memory loads only; xform: the prologue arithmetic on a loaded word
+        GSB_DEV uint64_t raw(uint32_t d) const { return p[d]; }
+        GSB_DEV void raw2(uint32_t d, uint64_t &a, uint64_t &b) const
         {
             ulonglong2 v = *reinterpret_cast<const ulonglong2 *>(p + d);
             a = v.x;
             b = v.y;
         }
+        GSB_DEV uint64_t xform(uint64_t v) const { return v; }
     };
 
     template <int MODE>
@@ -85,44 +87,98 @@ namespace gsb
         };
     };
 
-    template <int T_LOG, int G_HI, int G_LO, bool LAST, class Map, class IO>
-    __global__ void __launch_bounds__(1 << T_LOG) ntt_fwd_kernel(IO io, NttTables tab, ModMap mm, Map map)
+    // ---- the tile kernel ----------------------------------------------------------------------
+    // One CTA owns tile blockIdx.x of limb slot y = blockIdx.y and walks `zb` consecutive polynomials
+    // z (same modulus, same twiddles):
+    //   * the tile's twiddles are staged ONCE into shared memory by TMA bulk copies (one per stage
+    //     for a contiguous tile, one for a column tile) and reused for every z;
+    //   * the global loads of polynomial z+1 are issued before the butterflies of polynomial z run,
+    //     so HBM/L2 latency hides behind integer work.
+    // A = 0: contiguous tile (ContigMap);  A > 0: column tile with 2^A rows (ColMap).
+    template <int T_LOG, int G_HI, int A>
+    struct TilePlan
     {
-        const int y = blockIdx.y, z = blockIdx.z, mod = mm.mod(y);
-        if (io.skip(y, z))
-            return;
-        const LimbC c = tab.limb[mod];
-        typename IO::Pro pro(io, y, z, mod, c, tab.N);
-        typename IO::Epi epi(io, y, z, mod, c, tab.N);
-        uint64_t x[8];
-        int parity = 0;
-        fwd_rounds<T_LOG, G_HI, G_LO, LAST, 0>(
-            x, dyn_smem(), threadIdx.x, blockIdx.x, map, pro, epi, tab.WW + static_cast<size_t>(mod) * tab.N, c, parity);
-    }
+        static constexpr int TILE_LOG = T_LOG + 3;
+        static constexpr bool COLS = A > 0;
+        typedef TwContigSmem<TILE_LOG, G_HI> TwC; // every stage of the tile staged
+        typedef TwColsSmem<(A > 0 ? A : 1), TILE_LOG - (A > 0 ? A : 1)> TwR;
+        static constexpr uint32_t PAIRS = COLS ? TwR::PAIRS : TwC::PAIRS;
+        static constexpr size_t exch_words = size_t(2) << TILE_LOG;
+        static constexpr size_t smem_bytes = exch_words * sizeof(uint64_t) + PAIRS * sizeof(Twiddle) + 16;
+    };
 
-    template <int T_LOG, int G_HI, int G_LO, bool LAST, class Map, class IO>
-    __global__ void __launch_bounds__(1 << T_LOG) ntt_inv_kernel(IO io, NttTables tab, ModMap mm, Map map)
+    template <bool INVERSE, int T_LOG, int G_HI, int G_LO, bool LAST, int A, class IO>
+    __global__ void __launch_bounds__(1 << T_LOG) ntt_tile_kernel(IO io, NttTables tab, ModMap mm, int nz, int zb)
     {
-        const int y = blockIdx.y, z = blockIdx.z, mod = mm.mod(y);
-        if (io.skip(y, z))
-            return;
+        typedef TilePlan<T_LOG, G_HI, A> TP;
+        const int y = blockIdx.y, mod = mm.mod(y);
+        const uint32_t tid = threadIdx.x, tile = blockIdx.x, N = tab.N;
+        const int z0 = blockIdx.z * zb, z1 = z0 + zb < nz ? z0 + zb : nz;
+        uint64_t *smem = dyn_smem();
+        Twiddle *tws = reinterpret_cast<Twiddle *>(smem + TP::exch_words);
+        uint64_t *bar = reinterpret_cast<uint64_t *>(tws + TP::PAIRS);
+        const Twiddle *table = (INVERSE ? tab.VV : tab.WW) + static_cast<size_t>(mod) * N;
         const LimbC c = tab.limb[mod];
-        typename IO::Pro pro(io, y, z, mod, c, tab.N);
-        typename IO::Epi epi(io, y, z, mod, c, tab.N);
-        uint64_t x[8];
-        int parity = 0;
-        inv_rounds<T_LOG, G_HI, G_LO, LAST, 0>(
-            x, dyn_smem(), threadIdx.x, blockIdx.x, map, pro, epi, tab.VV + static_cast<size_t>(mod) * tab.N, tab.N, c,
-            parity);
+        if (tid == 0)
+            mbar_init(bar);
+        __syncthreads();
+        uint64_t xn[8];
+        int z = z0;
+        while (z < z1 && io.skip(y, z))
+            z++;
+        auto body = [&](const auto &map, const auto &tw) {
+            if (z < z1)
+            {
+                const typename IO::Pro pro(io, y, z, mod, c, N);
+                xf_load_raw<T_LOG, G_HI, G_LO, INVERSE>(xn, tid, tile, map, pro);
+            }
+            mbar_wait(bar, 0); // twiddles have landed (every thread waits, also before an early exit)
+            int parity = 0;
+            while (z < z1)
+            {
+                uint64_t x[8];
+                {
+                    const typename IO::Pro pro(io, y, z, mod, c, N);
+#pragma unroll
+                    for (int i = 0; i < 8; i++)
+                        x[i] = pro.xform(xn[i]);
+                }
+                int zn = z + 1;
+                while (zn < z1 && io.skip(y, zn))
+                    zn++;
+                if (zn < z1)
+                {
+                    const typename IO::Pro pro(io, y, zn, mod, c, N);
+                    xf_load_raw<T_LOG, G_HI, G_LO, INVERSE>(xn, tid, tile, map, pro);
+                }
+                if constexpr (INVERSE)
+                    inv_compute<T_LOG, G_HI, G_LO, LAST, 0>(x, smem, tid, tw, c, parity);
+                else
+                    fwd_compute<T_LOG, G_HI, G_LO, LAST, 0>(x, smem, tid, tw, c, parity);
+                const typename IO::Epi epi(io, y, z, mod, c, N);
+                xf_store<T_LOG, G_HI, G_LO, INVERSE>(x, tid, tile, map, epi);
+                z = zn;
+            }
+        };
+        if constexpr (TP::COLS)
+        {
+            if (tid == 0)
+                TP::TwR::stage(tws, table, N, INVERSE, bar);
+            const ColMap<T_LOG, A> map{ N, tab.logn };
+            const typename TP::TwR tw{ tws };
+            body(map, tw);
+        }
+        else
+        {
+            const ContigMap<T_LOG> map{ N };
+            if (tid == 0)
+                TP::TwC::stage(tws, table, N, map.off(tile), INVERSE, bar);
+            const typename TP::TwC tw{ tws, TwGlobal{ table, N, map.off(tile), N } };
+            body(map, tw);
+        }
     }
 
     // ---- launch plans ------------------------------------------------------------------------
-    template <int T_LOG>
-    constexpr size_t tile_smem_bytes()
-    {
-        return size_t(2) * (size_t(8) << T_LOG) * sizeof(uint64_t);
-    }
-
     template <class K>
     inline void allow_smem(K kfn, size_t bytes)
     {
@@ -131,28 +187,47 @@ namespace gsb
     }
 
     // Two-pass split for a given log2(N): A = log2(rows) of the column pass, TC = T_LOG of the
-    // column pass.  The contiguous pass always uses 2048-word tiles (T_LOG = 8).
+    // column pass.  The contiguous pass always uses 2048-word tiles (T_LOG = 8).  A is chosen so the
+    // two passes need as few register rounds (<= 3 stages each) as possible.
     template <int LOGN>
     struct Split
     {
         static constexpr bool two_pass = LOGN >= 13;
-        static constexpr int A = LOGN == 13 ? 6 : LOGN == 14 ? 7 : LOGN == 15 ? 7 : 8;
+        static constexpr int A = LOGN == 13 ? 6 : LOGN == 14 ? 6 : LOGN == 15 ? 6 : 8;
         static constexpr int TC = LOGN == 16 ? 9 : 8;
         static constexpr int T1 = LOGN - 3; // single-pass T_LOG
     };
 
-    // Forward pass 1 (columns) with arbitrary IO.  grid.x = N / 2^C column groups.
+    // polynomials per CTA: enough CTAs left for ~8 waves of 148 SMs x 3 resident CTAs
+    inline int pick_zb(size_t ctas_per_z, int nz)
+    {
+        const size_t want = size_t(148) * 3 * 8;
+        size_t zb = (ctas_per_z * static_cast<size_t>(nz)) / want;
+        zb = zb < 1 ? 1 : zb > 8 ? 8 : zb;
+        return static_cast<int>(zb);
+    }
+
+    template <bool INVERSE, int T_LOG, int G_HI, int G_LO, bool LAST, int A, class IO>
+    inline void launch_tile(
+        const char *pass, const char *tag, const IO &io, const NttTables &tab, const ModMap &mm, unsigned tiles, int ny, int nz,
+        cudaStream_t st)
+    {
+        typedef TilePlan<T_LOG, G_HI, A> TP;
+        auto kfn = ntt_tile_kernel<INVERSE, T_LOG, G_HI, G_LO, LAST, A, IO>;
+        allow_smem(kfn, TP::smem_bytes);
+        const int zb = pick_zb(static_cast<size_t>(tiles) * ny, nz);
+        dim3 grid(tiles, ny, (nz + zb - 1) / zb);
+        GSB_LAUNCH(pass, tag, kfn, grid, dim3(1 << T_LOG), TP::smem_bytes, st, io, tab, mm, nz, zb);
+    }
+
+    // Forward pass 1 (columns) with arbitrary IO.  tiles = N / 2^C column groups.
     template <int LOGN, class IO>
     inline void launch_fwd_cols(
         const IO &io, const NttTables &tab, const ModMap &mm, int ny, int nz, cudaStream_t st, const char *tag = "plain")
     {
         using SP = Split<LOGN>;
         constexpr int A = SP::A, TC = SP::TC, C = TC + 3 - A;
-        ColMap<TC, A> map{ tab.N, tab.logn };
-        auto kfn = ntt_fwd_kernel<TC, A + C - 1, C, false, ColMap<TC, A>, IO>;
-        allow_smem(kfn, tile_smem_bytes<TC>());
-        dim3 grid((1u << (LOGN - A)) >> C, ny, nz);
-        GSB_LAUNCH("fwd_cols", tag, kfn, grid, dim3(1 << TC), tile_smem_bytes<TC>(), st, io, tab, mm, map);
+        launch_tile<false, TC, A + C - 1, C, false, A>("fwd_cols", tag, io, tab, mm, (1u << (LOGN - A)) >> C, ny, nz, st);
     }
 
     // Forward pass 2 (contiguous blocks of N >> A) -- or the whole transform when !two_pass.
@@ -162,22 +237,9 @@ namespace gsb
     {
         using SP = Split<LOGN>;
         if constexpr (SP::two_pass)
-        {
-            constexpr int T = 8;
-            ContigMap<T> map{ tab.N };
-            auto kfn = ntt_fwd_kernel<T, LOGN - SP::A - 1, 0, true, ContigMap<T>, IO>;
-            allow_smem(kfn, tile_smem_bytes<T>());
-            dim3 grid(1u << (LOGN - T - 3), ny, nz);
-            GSB_LAUNCH("fwd_contig", tag, kfn, grid, dim3(1 << T), tile_smem_bytes<T>(), st, io, tab, mm, map);
-        }
+            launch_tile<false, 8, LOGN - SP::A - 1, 0, true, 0>("fwd_contig", tag, io, tab, mm, 1u << (LOGN - 11), ny, nz, st);
         else
-        {
-            constexpr int T = SP::T1;
-            ContigMap<T> map{ tab.N };
-            auto kfn = ntt_fwd_kernel<T, LOGN - 1, 0, true, ContigMap<T>, IO>;
-            allow_smem(kfn, tile_smem_bytes<T>());
-            GSB_LAUNCH("fwd_contig", tag, kfn, dim3(1, ny, nz), dim3(1 << T), tile_smem_bytes<T>(), st, io, tab, mm, map);
-        }
+            launch_tile<false, SP::T1, LOGN - 1, 0, true, 0>("fwd_contig", tag, io, tab, mm, 1u, ny, nz, st);
     }
 
     // Inverse pass 1 (contiguous) -- or the whole transform when !two_pass.
@@ -187,22 +249,9 @@ namespace gsb
     {
         using SP = Split<LOGN>;
         if constexpr (SP::two_pass)
-        {
-            constexpr int T = 8;
-            ContigMap<T> map{ tab.N };
-            auto kfn = ntt_inv_kernel<T, LOGN - SP::A - 1, 0, false, ContigMap<T>, IO>;
-            allow_smem(kfn, tile_smem_bytes<T>());
-            dim3 grid(1u << (LOGN - T - 3), ny, nz);
-            GSB_LAUNCH("inv_contig", tag, kfn, grid, dim3(1 << T), tile_smem_bytes<T>(), st, io, tab, mm, map);
-        }
+            launch_tile<true, 8, LOGN - SP::A - 1, 0, false, 0>("inv_contig", tag, io, tab, mm, 1u << (LOGN - 11), ny, nz, st);
         else
-        {
-            constexpr int T = SP::T1;
-            ContigMap<T> map{ tab.N };
-            auto kfn = ntt_inv_kernel<T, LOGN - 1, 0, true, ContigMap<T>, IO>;
-            allow_smem(kfn, tile_smem_bytes<T>());
-            GSB_LAUNCH("inv_contig", tag, kfn, dim3(1, ny, nz), dim3(1 << T), tile_smem_bytes<T>(), st, io, tab, mm, map);
-        }
+            launch_tile<true, SP::T1, LOGN - 1, 0, true, 0>("inv_contig", tag, io, tab, mm, 1u, ny, nz, st);
     }
 
     // Inverse pass 2 (columns; carries the global last stage with n^-1).
@@ -212,11 +261,7 @@ namespace gsb
     {
         using SP = Split<LOGN>;
         constexpr int A = SP::A, TC = SP::TC, C = TC + 3 - A;
-        ColMap<TC, A> map{ tab.N, tab.logn };
-        auto kfn = ntt_inv_kernel<TC, A + C - 1, C, true, ColMap<TC, A>, IO>;
-        allow_smem(kfn, tile_smem_bytes<TC>());
-        dim3 grid((1u << (LOGN - A)) >> C, ny, nz);
-        GSB_LAUNCH("inv_cols", tag, kfn, grid, dim3(1 << TC), tile_smem_bytes<TC>(), st, io, tab, mm, map);
+        launch_tile<true, TC, A + C - 1, C, true, A>("inv_cols", tag, io, tab, mm, (1u << (LOGN - A)) >> C, ny, nz, st);
     }
 
     // Plain batched transforms: element (z, y, d) of src/dst at base + z*zs + y*N + d; in place

@@ -164,6 +164,12 @@ int gsb_rescale_host(gsb_ctx *ctx, const uint64_t *in, uint64_t *out, size_t bat
 int gsb_apply_galois_host(gsb_ctx *ctx, uint32_t galois_elt, const uint64_t *in, uint64_t *out, size_t batch, size_t L);
 int gsb_mul_relin_rescale_host(gsb_ctx *ctx, const uint64_t *a, const uint64_t *b, uint64_t *out, size_t batch, size_t L);
 
+/* ---- integer-pipe roofline (measurement aid, not part of the reference's interface) -------------
+ * Register-resident microbenchmarks on ctx's device with `ctas_per_sm` x 256 threads per SM:
+ * 32-bit IMAD/s, IMAD.WIDE.U32/s and forward lazy Harvey butterflies/s (the exact butterfly of the
+ * NTT kernels, twiddles in registers, no memory traffic).  Any output pointer may be NULL. */
+int gsb_int_peak(gsb_ctx *ctx, int ctas_per_sm, double *imad_per_s, double *imad_wide_per_s, double *butterflies_per_s);
+
 #ifdef __cplusplus
 }
 #endif

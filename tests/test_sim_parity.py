@@ -25,4 +25,4 @@ def test_sim_matches_reference_digests(simlib, oracle, name):
 def test_sim_exports_every_declared_symbol(simlib):
     from gemini_seal_b200 import _lib
     for sym in _lib.PROTOTYPES:
-        assert hasattr(simlib, sym)
+        assert hasattr(simlib, sym) or sym in _lib.CUDA_ONLY
