@@ -268,6 +268,13 @@ void gsb_ctx_destroy(gsb_ctx *ctx)
         cudaFree(kv.second);
     cudaFree(ctx->default_ws.buf);
     cudaFree(ctx->host_io.buf);
+    if (ctx->pipe_ready)
+    {
+        for (int i = 0; i < 3; i++)
+            cudaStreamDestroy(ctx->pipe_stream[i]);
+        for (int i = 0; i < 6; i++)
+            cudaEventDestroy(ctx->pipe_event[i]);
+    }
     if (ctx->default_ws.pinned)
         cudaFreeHost(ctx->default_ws.pinned);
     delete ctx;

@@ -87,6 +87,9 @@ struct gsb_ctx
     std::mutex host_mu; // serialises the *_host entry points (they share host_io / default_ws)
     gsb_ws default_ws;  // compute scratch for callers that pass ws = NULL
     gsb_ws host_io;     // device staging of the *_host entry points
+    bool pipe_ready = false; // copy-in / run / copy-out streams and events of the *_host pipeline
+    cudaStream_t pipe_stream[3] = {};
+    cudaEvent_t pipe_event[6] = {};
 
     gsb::NttTables ntt_tables() const
     {

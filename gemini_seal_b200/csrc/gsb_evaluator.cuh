@@ -579,68 +579,103 @@ int gsb_mul_relin_rescale_dev(
 }
 
 // ---- host-buffer forms -----------------------------------------------------------------------------
+// Copy in, run, copy out -- pipelined: the batch is cut into chunks of a few ciphertexts and chunk
+// i+1's host->device copy, chunk i's kernels and chunk i-1's device->host copy run concurrently on
+// three streams over two staging sets (PCIe is full duplex; with pinned host buffers the copies
+// are real DMA).  w0/w1/wo = words per ciphertext of the two inputs and the output.
 static int host_call(
-    gsb_ctx *ctx, const uint64_t *in0, size_t in0_words, const uint64_t *in1, size_t in1_words, uint64_t *out, size_t out_words,
-    const std::function<int(gsb_ws *, uint64_t *, uint64_t *, uint64_t *)> &run)
+    gsb_ctx *ctx, const uint64_t *in0, size_t w0, const uint64_t *in1, size_t w1, uint64_t *out, size_t wo, size_t batch,
+    const std::function<int(gsb_ws *, uint64_t *, uint64_t *, uint64_t *, size_t, void *)> &run)
 {
     int rc = GSB_OK;
     int g = guarded([&] {
         require(ctx != nullptr, GSB_E_INVALID_ARG, "ctx is null");
-        require(in0 != nullptr && out != nullptr && (in1 != nullptr || in1_words == 0), GSB_E_INVALID_ARG, "null operand");
+        require(in0 != nullptr && out != nullptr && (in1 != nullptr || w1 == 0), GSB_E_INVALID_ARG, "null operand");
+        require(batch >= 1 && batch <= (size_t(1) << 20), GSB_E_INVALID_ARG, "batch out of range");
         std::lock_guard<std::mutex> lock(ctx->host_mu);
         GSB_CUDA_CHECK(cudaSetDevice(ctx->device));
-        uint64_t *d = static_cast<uint64_t *>(ctx->host_io.reserve((in0_words + in1_words + out_words) * sizeof(uint64_t)));
-        GSB_CUDA_CHECK(cudaMemcpyAsync(d, in0, in0_words * sizeof(uint64_t), cudaMemcpyHostToDevice, nullptr));
-        if (in1_words)
-            GSB_CUDA_CHECK(cudaMemcpyAsync(d + in0_words, in1, in1_words * sizeof(uint64_t), cudaMemcpyHostToDevice, nullptr));
-        rc = run(&ctx->default_ws, d, d + in0_words, d + in0_words + in1_words);
-        if (rc == GSB_OK)
+        if (!ctx->pipe_ready)
         {
-            GSB_CUDA_CHECK(cudaMemcpyAsync(out, d + in0_words + in1_words, out_words * sizeof(uint64_t), cudaMemcpyDeviceToHost, nullptr));
-            GSB_CUDA_CHECK(cudaStreamSynchronize(nullptr));
+            for (int i = 0; i < 3; i++)
+                GSB_CUDA_CHECK(cudaStreamCreateWithFlags(&ctx->pipe_stream[i], cudaStreamNonBlocking));
+            for (int i = 0; i < 6; i++)
+                GSB_CUDA_CHECK(cudaEventCreateWithFlags(&ctx->pipe_event[i], cudaEventDisableTiming));
+            ctx->pipe_ready = true;
         }
+        cudaStream_t s_in = ctx->pipe_stream[0], s_run = ctx->pipe_stream[1], s_out = ctx->pipe_stream[2];
+        // chunk: ~128 MiB of input per chunk, at least 1 ciphertext, at most the batch
+        size_t chunk = (size_t(128) << 20) / ((w0 + w1) * sizeof(uint64_t));
+        chunk = chunk < 1 ? 1 : chunk > batch ? batch : chunk;
+        const size_t per_set = chunk * (w0 + w1 + wo);
+        uint64_t *stage = static_cast<uint64_t *>(ctx->host_io.reserve(2 * per_set * sizeof(uint64_t)));
+        cudaEvent_t *in_done = ctx->pipe_event, *run_done = ctx->pipe_event + 2, *out_done = ctx->pipe_event + 4;
+        size_t n = 0;
+        for (size_t b0 = 0; b0 < batch && rc == GSB_OK; b0 += chunk, n++)
+        {
+            const size_t B = std::min(chunk, batch - b0);
+            const int set = static_cast<int>(n & 1);
+            uint64_t *d0 = stage + set * per_set, *d1 = d0 + chunk * w0, *dout = d1 + chunk * w1;
+            if (n >= 2) // the set's inputs are free once its previous kernels ran, its output once copied out
+            {
+                GSB_CUDA_CHECK(cudaStreamWaitEvent(s_in, run_done[set], 0));
+                GSB_CUDA_CHECK(cudaStreamWaitEvent(s_run, out_done[set], 0));
+            }
+            GSB_CUDA_CHECK(cudaMemcpyAsync(d0, in0 + b0 * w0, B * w0 * sizeof(uint64_t), cudaMemcpyHostToDevice, s_in));
+            if (w1)
+                GSB_CUDA_CHECK(cudaMemcpyAsync(d1, in1 + b0 * w1, B * w1 * sizeof(uint64_t), cudaMemcpyHostToDevice, s_in));
+            GSB_CUDA_CHECK(cudaEventRecord(in_done[set], s_in));
+            GSB_CUDA_CHECK(cudaStreamWaitEvent(s_run, in_done[set], 0));
+            rc = run(&ctx->default_ws, d0, d1, dout, B, s_run);
+            GSB_CUDA_CHECK(cudaEventRecord(run_done[set], s_run));
+            GSB_CUDA_CHECK(cudaStreamWaitEvent(s_out, run_done[set], 0));
+            GSB_CUDA_CHECK(cudaMemcpyAsync(out + b0 * wo, dout, B * wo * sizeof(uint64_t), cudaMemcpyDeviceToHost, s_out));
+            GSB_CUDA_CHECK(cudaEventRecord(out_done[set], s_out));
+        }
+        for (int i = 0; i < 3; i++)
+            GSB_CUDA_CHECK(cudaStreamSynchronize(ctx->pipe_stream[i]));
     });
     return g != GSB_OK ? g : rc;
 }
 
 int gsb_ckks_multiply_host(gsb_ctx *ctx, const uint64_t *a, const uint64_t *b, uint64_t *out, size_t batch, size_t L)
 {
-    const size_t w = ctx ? batch * L * ctx->N : 0;
-    return host_call(ctx, a, 2 * w, b, 2 * w, out, 3 * w, [&](gsb_ws *, uint64_t *da, uint64_t *db, uint64_t *dout) {
-        return gsb_ckks_multiply_dev(ctx, da, db, dout, batch, L, nullptr);
+    const size_t w = ctx ? L * ctx->N : 0;
+    return host_call(ctx, a, 2 * w, b, 2 * w, out, 3 * w, batch, [&](gsb_ws *, uint64_t *da, uint64_t *db, uint64_t *dout, size_t B, void *st) {
+        return gsb_ckks_multiply_dev(ctx, da, db, dout, B, L, st);
     });
 }
 
 int gsb_relinearize_host(gsb_ctx *ctx, const uint64_t *in, uint64_t *out, size_t batch, size_t L)
 {
-    const size_t w = ctx ? batch * L * ctx->N : 0;
-    return host_call(ctx, in, 3 * w, nullptr, 0, out, 2 * w, [&](gsb_ws *ws, uint64_t *di, uint64_t *, uint64_t *dout) {
-        return gsb_relinearize_dev(ctx, ws, di, dout, batch, L, nullptr);
+    const size_t w = ctx ? L * ctx->N : 0;
+    return host_call(ctx, in, 3 * w, nullptr, 0, out, 2 * w, batch, [&](gsb_ws *ws, uint64_t *di, uint64_t *, uint64_t *dout, size_t B, void *st) {
+        return gsb_relinearize_dev(ctx, ws, di, dout, B, L, st);
     });
 }
 
 int gsb_rescale_host(gsb_ctx *ctx, const uint64_t *in, uint64_t *out, size_t batch, size_t size, size_t L)
 {
-    const size_t w = ctx ? batch * size * ctx->N : 0;
-    return host_call(ctx, in, w * L, nullptr, 0, out, L ? w * (L - 1) : 0, [&](gsb_ws *ws, uint64_t *di, uint64_t *, uint64_t *dout) {
-        return gsb_rescale_dev(ctx, ws, di, dout, batch, size, L, nullptr);
+    const size_t w = ctx ? size * ctx->N : 0;
+    return host_call(ctx, in, w * L, nullptr, 0, out, L ? w * (L - 1) : 0, batch, [&](gsb_ws *ws, uint64_t *di, uint64_t *, uint64_t *dout, size_t B, void *st) {
+        return gsb_rescale_dev(ctx, ws, di, dout, B, size, L, st);
     });
 }
 
 int gsb_apply_galois_host(gsb_ctx *ctx, uint32_t galois_elt, const uint64_t *in, uint64_t *out, size_t batch, size_t L)
 {
-    const size_t w = ctx ? batch * L * ctx->N : 0;
-    return host_call(ctx, in, 2 * w, nullptr, 0, out, 2 * w, [&](gsb_ws *ws, uint64_t *di, uint64_t *, uint64_t *dout) {
-        return gsb_apply_galois_dev(ctx, ws, galois_elt, di, dout, batch, L, nullptr);
+    const size_t w = ctx ? L * ctx->N : 0;
+    return host_call(ctx, in, 2 * w, nullptr, 0, out, 2 * w, batch, [&](gsb_ws *ws, uint64_t *di, uint64_t *, uint64_t *dout, size_t B, void *st) {
+        return gsb_apply_galois_dev(ctx, ws, galois_elt, di, dout, B, L, st);
     });
 }
 
 int gsb_mul_relin_rescale_host(gsb_ctx *ctx, const uint64_t *a, const uint64_t *b, uint64_t *out, size_t batch, size_t L)
 {
-    const size_t w = ctx ? batch * ctx->N : 0;
-    return host_call(ctx, a, 2 * w * L, b, 2 * w * L, out, L ? 2 * w * (L - 1) : 0, [&](gsb_ws *ws, uint64_t *da, uint64_t *db, uint64_t *dout) {
-        return gsb_mul_relin_rescale_dev(ctx, ws, da, db, dout, batch, L, nullptr);
-    });
+    const size_t w = ctx ? ctx->N : 0;
+    return host_call(ctx, a, 2 * w * L, b, 2 * w * L, out, L ? 2 * w * (L - 1) : 0, batch,
+                     [&](gsb_ws *ws, uint64_t *da, uint64_t *db, uint64_t *dout, size_t B, void *st) {
+                         return gsb_mul_relin_rescale_dev(ctx, ws, da, db, dout, B, L, st);
+                     });
 }
 
 } // extern "C"

@@ -245,6 +245,29 @@ static inline cudaError_t cudaEventCreate(cudaEvent_t *e)
     *e = nullptr;
     return 0;
 }
+enum
+{
+    cudaStreamNonBlocking = 1,
+    cudaEventDisableTiming = 2
+};
+static inline cudaError_t cudaStreamCreateWithFlags(cudaStream_t *s, unsigned)
+{
+    *s = nullptr;
+    return 0;
+}
+static inline cudaError_t cudaStreamDestroy(cudaStream_t)
+{
+    return 0;
+}
+static inline cudaError_t cudaStreamWaitEvent(cudaStream_t, cudaEvent_t, unsigned)
+{
+    return 0;
+}
+static inline cudaError_t cudaEventCreateWithFlags(cudaEvent_t *e, unsigned)
+{
+    *e = nullptr;
+    return 0;
+}
 static inline cudaError_t cudaEventDestroy(cudaEvent_t)
 {
     return 0;
