@@ -217,18 +217,14 @@ def run_ours(args):
     ctx.set_galois_key(elt, uniform_residues(torch, mods, (L, 2), gen).cpu().numpy().view(np.uint64))
     del relin
     # inputs: rank 0 draws the whole job and scatters the shards over NCCL (untimed plumbing)
+    from gemini_seal_b200 import shard
     if world > 1:
-        a = torch.empty((B, 2, L, N), dtype=torch.int64, device="cuda")
-        b = torch.empty_like(a)
-        if rank == 0:
-            ga = list(uniform_residues(torch, mods[:L], (world * B, 2), gen).chunk(world))
-            gb = list(uniform_residues(torch, mods[:L], (world * B, 2), gen).chunk(world))
-            ga, gb = [x.contiguous() for x in ga], [x.contiguous() for x in gb]
-        else:
-            ga = gb = None
-        dist.scatter(a, ga, src=0)
-        dist.scatter(b, gb, src=0)
-        del ga, gb
+        ga = uniform_residues(torch, mods[:L], (world * B, 2), gen) if rank == 0 else None
+        a = shard.scatter_batch(ga, (B, 2, L, N), torch.int64, "cuda")
+        del ga
+        gb = uniform_residues(torch, mods[:L], (world * B, 2), gen) if rank == 0 else None
+        b = shard.scatter_batch(gb, (B, 2, L, N), torch.int64, "cuda")
+        del gb
     else:
         a = uniform_residues(torch, mods[:L], (B, 2), gen)
         b = uniform_residues(torch, mods[:L], (B, 2), gen)
@@ -338,10 +334,12 @@ def run_ours(args):
                "sample": "%d mul+relin+rescale ops on %d host threads (shared Evaluator, disjoint ciphertexts), %.1f s" % (ops * 2, threads, secs)}
 
     if world > 1:
-        # gather a checksum of every shard's result on rank 0 (NCCL plumbing, untimed)
-        chk = out.sum().reshape(1)
-        gathered = [torch.empty_like(chk) for _ in range(world)] if rank == 0 else None
-        dist.gather(chk, gathered, dst=0)
+        # gather every shard's result on rank 0 (NCCL plumbing, untimed) and spot-check one of them
+        step()
+        allout = shard.gather_batch(out)
+        if rank == 0:
+            assert allout.shape[0] == world * B and torch.equal(allout[:B], out)
+        del allout
     if rank == 0:
         line = {
             "metric": METRIC, "value": value, "unit": "ops/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),

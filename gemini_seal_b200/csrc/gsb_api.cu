@@ -261,7 +261,8 @@ void gsb_ctx_destroy(gsb_ctx *ctx)
         cudaFree(kv.second.d_inv_qlast);
         cudaFree(kv.second.d_neg_half);
     }
-    cudaFree(ctx->relin.d);
+    for (auto &kv : ctx->relin)
+        cudaFree(kv.second.d);
     for (auto &kv : ctx->galois)
         cudaFree(kv.second.d);
     for (auto &kv : ctx->galois_tables)

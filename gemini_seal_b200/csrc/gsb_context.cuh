@@ -80,7 +80,7 @@ struct gsb_ctx
     gsb::Twiddle *d_WW = nullptr, *d_VV = nullptr;
     gsb::LimbC *d_limb = nullptr;
     std::map<size_t, gsb::KsLevelConsts> level_consts;
-    gsb::SwitchKey relin;
+    std::map<uint32_t, gsb::SwitchKey> relin; // RelinKeys::get_index(key_power) -> key
     std::map<uint32_t, gsb::SwitchKey> galois;
     std::map<uint32_t, uint32_t *> galois_tables; // device permutation tables per element
     std::mutex mu;      // guards the lazily built maps below

@@ -331,8 +331,9 @@ namespace gsb
         std::lock_guard<std::mutex> lock(ctx->mu);
         if (kind == GSB_KEY_RELIN)
         {
-            require(ctx->relin.d != nullptr, GSB_E_INVALID_ARG, "Not enough relinearization keys");
-            return ctx->relin;
+            auto it = ctx->relin.find(elt);
+            require(it != ctx->relin.end(), GSB_E_INVALID_ARG, "not enough relinearization keys");
+            return it->second;
         }
         require(kind == GSB_KEY_GALOIS, GSB_E_INVALID_ARG, "key kind");
         auto it = ctx->galois.find(elt);
@@ -410,7 +411,7 @@ int gsb_key_upload(gsb_ctx *ctx, int kind, uint32_t galois_elt, const uint64_t *
         GSB_CUDA_CHECK(cudaMalloc(reinterpret_cast<void **>(&d), words * sizeof(uint64_t)));
         GSB_CUDA_CHECK(cudaMemcpy(d, key_host, words * sizeof(uint64_t), cudaMemcpyHostToDevice));
         std::lock_guard<std::mutex> lock(ctx->mu);
-        SwitchKey &slot = kind == GSB_KEY_RELIN ? ctx->relin : ctx->galois[galois_elt];
+        SwitchKey &slot = kind == GSB_KEY_RELIN ? ctx->relin[galois_elt] : ctx->galois[galois_elt];
         if (slot.d)
             cudaFree(slot.d);
         slot.d = d;
@@ -425,8 +426,10 @@ int gsb_key_drop(gsb_ctx *ctx, int kind, uint32_t galois_elt)
         std::lock_guard<std::mutex> lock(ctx->mu);
         if (kind == GSB_KEY_RELIN)
         {
-            cudaFree(ctx->relin.d);
-            ctx->relin = SwitchKey();
+            auto it = ctx->relin.find(galois_elt);
+            require(it != ctx->relin.end(), GSB_E_INVALID_ARG, "relinearization key not present");
+            cudaFree(it->second.d);
+            ctx->relin.erase(it);
         }
         else
         {

@@ -116,7 +116,8 @@ int gsb_poly_op_host(
  * galoiskeys.h:52-66, keygenerator.cpp:325-369) --------------------------------------------------
  * key_host = [n_bundles][2][K][N]: bundle j is `keys.data()[index][j].data()` of the reference (a
  * size-2 ciphertext over all K key-level limbs, NTT form).  n_bundles must be ceil((K-k)/k).
- * kind GSB_KEY_RELIN ignores galois_elt.  The context keeps a device copy until gsb_key_drop /
+ * For kind GSB_KEY_RELIN, `galois_elt` is RelinKeys::get_index(key_power) (0 = the s^2 key that
+ * relinearizes size 3 -> 2; relinkeys.h:61).  The context keeps a device copy until gsb_key_drop /
  * gsb_ctx_destroy.  Uploading also builds the Galois permutation table (util/galois.cpp:18-47). */
 int gsb_key_upload(gsb_ctx *ctx, int kind, uint32_t galois_elt, const uint64_t *key_host, size_t n_bundles);
 int gsb_key_drop(gsb_ctx *ctx, int kind, uint32_t galois_elt);

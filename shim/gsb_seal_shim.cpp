@@ -1,0 +1,447 @@
+// See gsb_seal_shim.h.  Host C++ only: validation + metadata exactly as native/src/seal/evaluator.cpp,
+// polynomial arithmetic through the C ABI of the B200 library.  No CPU arithmetic fallback.
+#include "gsb_seal_shim.h"
+#include "seal/util/numth.h"
+#include "seal/valcheck.h"
+#include <cmath>
+#include <cstring>
+#include <stdexcept>
+#include <utility>
+
+using namespace seal;
+using namespace std;
+
+namespace gsb_seal
+{
+    namespace
+    {
+        [[noreturn]] void raise(int rc)
+        {
+            const string msg = gsb_last_error();
+            switch (rc)
+            {
+            case GSB_E_INVALID_ARG: throw invalid_argument(msg);
+            case GSB_E_LOGIC: throw logic_error(msg);
+            case GSB_E_RANGE: throw out_of_range(msg);
+            default: throw runtime_error("gseal_b200: " + msg);
+            }
+        }
+        inline void check(int rc)
+        {
+            if (rc != GSB_OK)
+                raise(rc);
+        }
+    } // namespace
+
+    void Evaluator::fail(int rc) const
+    {
+        raise(rc);
+    }
+
+    Evaluator::Evaluator(shared_ptr<SEALContext> context, int device) : context_(move(context))
+    {
+        // evaluator.cpp:24-36
+        if (!context_)
+            throw invalid_argument("invalid context");
+        if (!context_->parameters_set())
+            throw invalid_argument("encryption parameters are not set correctly");
+        auto &key_parms = context_->key_context_data()->parms();
+        if (key_parms.scheme() != scheme_type::CKKS)
+            throw logic_error("gsb_seal::Evaluator serves the CKKS path only");
+        N_ = key_parms.poly_modulus_degree();
+        K_ = key_parms.coeff_modulus().size();
+        k_ = K_ - context_->first_context_data()->parms().coeff_modulus().size(); // evaluator.cpp:2273-2276
+        if (K_ == 1)
+            k_ = 1;
+        vector<uint64_t> moduli;
+        for (auto &m : key_parms.coeff_modulus())
+            moduli.push_back(m.value());
+        int logn = 0;
+        while ((size_t(1) << logn) < N_)
+            logn++;
+        check(gsb_ctx_create(device, logn, moduli.data(), K_, k_, &ctx_));
+    }
+
+    Evaluator::~Evaluator()
+    {
+        gsb_ctx_destroy(ctx_);
+    }
+
+    void Evaluator::validate(const Ciphertext &ct, const char *what) const
+    {
+        if (!is_metadata_valid_for(ct, context_) || !is_buffer_valid(ct))
+            throw invalid_argument(string(what) + " is not valid for encryption parameters");
+    }
+
+    size_t Evaluator::level_limbs(const Ciphertext &ct) const
+    {
+        return context_->get_context_data(ct.parms_id())->parms().coeff_modulus().size();
+    }
+
+    // ---- multiply (evaluator.cpp:235-272, 447-527) ------------------------------------------------
+    void Evaluator::multiply_inplace(Ciphertext &encrypted1, const Ciphertext &encrypted2, MemoryPoolHandle)
+    {
+        validate(encrypted1, "encrypted1");
+        validate(encrypted2, "encrypted2");
+        if (encrypted1.parms_id() != encrypted2.parms_id())
+            throw invalid_argument("encrypted1 and encrypted2 parameter mismatch");
+        if (!(encrypted1.is_ntt_form() && encrypted2.is_ntt_form()))
+            throw invalid_argument("encrypted1 or encrypted2 must be in NTT form");
+        auto &context_data = *context_->get_context_data(encrypted1.parms_id());
+        const double new_scale = encrypted1.scale() * encrypted2.scale();
+        if (new_scale <= 0 || (static_cast<int>(log2(new_scale)) >= context_data.total_coeff_modulus_bit_count()))
+            throw invalid_argument("scale out of bounds");
+        if (encrypted1.size() != 2 || encrypted2.size() != 2)
+            throw logic_error("device multiply serves size-2 operands (relinearize first)");
+        const size_t L = level_limbs(encrypted1);
+        vector<uint64_t> b;
+        const uint64_t *pb = encrypted2.data();
+        if (&encrypted1 == &encrypted2) // square: keep a copy, the destination is resized below
+        {
+            b.assign(encrypted2.data(), encrypted2.data() + 2 * L * N_);
+            pb = b.data();
+        }
+        encrypted1.resize(context_, context_data.parms_id(), 3);
+        check(gsb_ckks_multiply_host(ctx_, encrypted1.data(), pb, encrypted1.data(), 1, L));
+        encrypted1.scale() = new_scale;
+#ifdef SEAL_THROW_ON_TRANSPARENT_CIPHERTEXT
+        if (encrypted1.is_transparent())
+            throw logic_error("result ciphertext is transparent");
+#endif
+    }
+
+    void Evaluator::multiply(const Ciphertext &encrypted1, const Ciphertext &encrypted2, Ciphertext &destination, MemoryPoolHandle pool)
+    {
+        if (&encrypted2 == &destination) // evaluator.h:262-276
+        {
+            multiply_inplace(destination, encrypted1, move(pool));
+        }
+        else
+        {
+            destination = encrypted1;
+            multiply_inplace(destination, encrypted2, move(pool));
+        }
+    }
+
+    // ---- key upload ---------------------------------------------------------------------------------
+    void Evaluator::upload_key(int kind, uint32_t slot, const vector<PublicKey> &bundles)
+    {
+        const size_t per = 2 * K_ * N_;
+        vector<uint64_t> flat(bundles.size() * per);
+        for (size_t j = 0; j < bundles.size(); j++)
+        {
+            // evaluator.cpp:2283-2290: only the used component is validated
+            if (!is_metadata_valid_for(bundles[j], context_) || !is_buffer_valid(bundles[j]) || bundles[j].data().size() != 2)
+                throw invalid_argument("kswitch_keys is not valid for encryption parameters");
+            memcpy(flat.data() + j * per, bundles[j].data().data(), per * sizeof(uint64_t));
+        }
+        check(gsb_key_upload(ctx_, kind, slot, flat.data(), bundles.size()));
+    }
+
+    void Evaluator::ensure_relin(const RelinKeys &keys, size_t index)
+    {
+        lock_guard<mutex> lock(mu_);
+        const auto &bundles = keys.data()[index];
+        const void *id = bundles.empty() ? nullptr : static_cast<const void *>(bundles[0].data().data());
+        auto it = relin_loaded_.find(static_cast<uint32_t>(index));
+        if (it != relin_loaded_.end() && it->second == id)
+            return;
+        upload_key(GSB_KEY_RELIN, static_cast<uint32_t>(index), bundles);
+        relin_loaded_[static_cast<uint32_t>(index)] = id;
+    }
+
+    void Evaluator::ensure_galois(const GaloisKeys &keys, uint32_t elt)
+    {
+        lock_guard<mutex> lock(mu_);
+        const auto &bundles = keys.data()[GaloisKeys::get_index(elt)];
+        const void *id = bundles.empty() ? nullptr : static_cast<const void *>(bundles[0].data().data());
+        auto it = galois_loaded_.find(elt);
+        if (it != galois_loaded_.end() && it->second == id)
+            return;
+        upload_key(GSB_KEY_GALOIS, elt, bundles);
+        galois_loaded_[elt] = id;
+    }
+
+    // ---- relinearize (evaluator.cpp:772-827) -----------------------------------------------------------
+    void Evaluator::relinearize_inplace(Ciphertext &encrypted, const RelinKeys &relin_keys, MemoryPoolHandle)
+    {
+        validate(encrypted, "encrypted"); // evaluator.h:344-348 (checked by the public wrapper)
+        auto context_data_ptr = context_->get_context_data(encrypted.parms_id());
+        if (!context_data_ptr)
+            throw invalid_argument("encrypted is not valid for encryption parameters");
+        if (relin_keys.parms_id() != context_->key_parms_id())
+            throw invalid_argument("relin_keys is not valid for encryption parameters");
+        const size_t size = encrypted.size();
+        if (relin_keys.size() < (size >= 2 ? size - 2 : 0))
+            throw invalid_argument("not enough relinearization keys");
+        if (size <= 2)
+            return;
+        if (!encrypted.is_ntt_form())
+            throw logic_error("device key switching serves CKKS (NTT-form) ciphertexts");
+        const size_t L = level_limbs(encrypted), LN = L * N_;
+        if (size == 3)
+        {
+            ensure_relin(relin_keys, RelinKeys::get_index(2));
+            vector<uint64_t> out(2 * LN);
+            check(gsb_relinearize_host(ctx_, encrypted.data(), out.data(), 1, L));
+            encrypted.resize(context_, context_data_ptr->parms_id(), 2);
+            memcpy(encrypted.data(), out.data(), 2 * LN * sizeof(uint64_t));
+        }
+        else
+        {
+            // one key switch per extra component, last component first (evaluator.cpp:811-815), device resident
+            void *d = nullptr;
+            check(gsb_malloc(ctx_, size * LN * sizeof(uint64_t), &d));
+            int rc = gsb_memcpy_h2d(ctx_, d, encrypted.data(), size * LN * sizeof(uint64_t), nullptr);
+            for (size_t i = 0; rc == GSB_OK && i < size - 2; i++)
+            {
+                const size_t comp = size - 1 - i;
+                ensure_relin(relin_keys, RelinKeys::get_index(comp));
+                rc = gsb_switch_key_dev(
+                    ctx_, nullptr, static_cast<uint64_t *>(d), size, static_cast<uint64_t *>(d) + comp * LN, 0, GSB_KEY_RELIN,
+                    static_cast<uint32_t>(RelinKeys::get_index(comp)), 1, L, nullptr);
+            }
+            encrypted.resize(context_, context_data_ptr->parms_id(), 2);
+            if (rc == GSB_OK)
+                rc = gsb_memcpy_d2h(ctx_, encrypted.data(), d, 2 * LN * sizeof(uint64_t), nullptr);
+            if (rc == GSB_OK)
+                rc = gsb_stream_sync(ctx_, nullptr);
+            gsb_free(ctx_, d);
+            check(rc);
+        }
+#ifdef SEAL_THROW_ON_TRANSPARENT_CIPHERTEXT
+        if (encrypted.is_transparent())
+            throw logic_error("result ciphertext is transparent");
+#endif
+    }
+
+    void Evaluator::relinearize(const Ciphertext &encrypted, const RelinKeys &relin_keys, Ciphertext &destination, MemoryPoolHandle pool)
+    {
+        destination = encrypted;
+        relinearize_inplace(destination, relin_keys, move(pool));
+    }
+
+    // ---- rescale (evaluator.cpp:1090-1126, 829-892) ---------------------------------------------------
+    void Evaluator::rescale_to_next(const Ciphertext &encrypted, Ciphertext &destination, MemoryPoolHandle pool)
+    {
+        validate(encrypted, "encrypted");
+        if (context_->last_parms_id() == encrypted.parms_id())
+            throw invalid_argument("end of modulus switching chain reached");
+        if (!pool)
+            throw invalid_argument("pool is uninitialized");
+        if (!encrypted.is_ntt_form())
+            throw invalid_argument("CKKS encrypted must be in NTT form");
+        auto &context_data = *context_->get_context_data(encrypted.parms_id());
+        auto &next_context_data = *context_data.next_context_data();
+        const size_t L = context_data.parms().coeff_modulus().size(), size = encrypted.size();
+        vector<uint64_t> out(size * (L - 1) * N_);
+        check(gsb_rescale_host(ctx_, encrypted.data(), out.data(), 1, size, L));
+        const double new_scale = encrypted.scale() / static_cast<double>(context_data.parms().coeff_modulus().back().value());
+        const bool ntt = encrypted.is_ntt_form();
+        destination.resize(context_, next_context_data.parms_id(), size);
+        memcpy(destination.data(), out.data(), out.size() * sizeof(uint64_t));
+        destination.is_ntt_form() = ntt;
+        destination.scale() = new_scale;
+#ifdef SEAL_THROW_ON_TRANSPARENT_CIPHERTEXT
+        if (destination.is_transparent())
+            throw logic_error("result ciphertext is transparent");
+#endif
+    }
+
+    void Evaluator::rescale_to_next_inplace(Ciphertext &encrypted, MemoryPoolHandle pool)
+    {
+        rescale_to_next(encrypted, encrypted, move(pool));
+    }
+
+    // ---- Galois (evaluator.cpp:1841-1943) -----------------------------------------------------------
+    void Evaluator::apply_galois_inplace(Ciphertext &encrypted, uint32_t galois_elt, const GaloisKeys &galois_keys, MemoryPoolHandle)
+    {
+        validate(encrypted, "encrypted");
+        if (galois_keys.parms_id() != context_->key_parms_id())
+            throw invalid_argument("galois_keys is not valid for encryption parameters");
+        if (!galois_keys.has_key(galois_elt))
+            throw invalid_argument("Galois key not present");
+        if (!(galois_elt & 1) || galois_elt >= 2 * N_)
+            throw invalid_argument("Galois element is not valid");
+        if (encrypted.size() > 2)
+            throw invalid_argument("encrypted size must be 2");
+        if (!encrypted.is_ntt_form())
+            throw logic_error("device key switching serves CKKS (NTT-form) ciphertexts");
+        ensure_galois(galois_keys, galois_elt);
+        const size_t L = level_limbs(encrypted);
+        vector<uint64_t> out(2 * L * N_);
+        check(gsb_apply_galois_host(ctx_, galois_elt, encrypted.data(), out.data(), 1, L));
+        memcpy(encrypted.data(), out.data(), out.size() * sizeof(uint64_t));
+#ifdef SEAL_THROW_ON_TRANSPARENT_CIPHERTEXT
+        if (encrypted.is_transparent())
+            throw logic_error("result ciphertext is transparent");
+#endif
+    }
+
+    void Evaluator::apply_galois(
+        const Ciphertext &encrypted, uint32_t galois_elt, const GaloisKeys &galois_keys, Ciphertext &destination, MemoryPoolHandle pool)
+    {
+        destination = encrypted;
+        apply_galois_inplace(destination, galois_elt, galois_keys, move(pool));
+    }
+
+    // evaluator.cpp:1945-2000
+    void Evaluator::rotate_internal(Ciphertext &encrypted, int steps, const GaloisKeys &galois_keys)
+    {
+        auto context_data_ptr = context_->get_context_data(encrypted.parms_id());
+        if (!context_data_ptr)
+            throw invalid_argument("encrypted is not valid for encryption parameters");
+        if (!context_data_ptr->qualifiers().using_batching)
+            throw logic_error("encryption parameters do not support batching");
+        if (galois_keys.parms_id() != context_->key_parms_id())
+            throw invalid_argument("galois_keys is not valid for encryption parameters");
+        if (steps == 0)
+            return;
+        const size_t coeff_count = context_data_ptr->parms().poly_modulus_degree();
+        auto galois_tool = context_data_ptr->galois_tool();
+        if (galois_keys.has_key(galois_tool->get_elt_from_step(steps)))
+        {
+            apply_galois_inplace(encrypted, galois_tool->get_elt_from_step(steps), galois_keys, MemoryManager::GetPool());
+            return;
+        }
+        const vector<int> naf_steps = seal::util::naf(steps);
+        if (naf_steps.size() == 1)
+            throw invalid_argument("Galois key not present");
+        for (int step : naf_steps)
+            if (static_cast<size_t>(abs(step)) != (coeff_count >> 1))
+                rotate_internal(encrypted, step, galois_keys);
+    }
+
+    void Evaluator::rotate_vector_inplace(Ciphertext &encrypted, int steps, const GaloisKeys &galois_keys, MemoryPoolHandle)
+    {
+        // evaluator.h:1201-1209
+        if (context_->key_context_data()->parms().scheme() != scheme_type::CKKS)
+            throw logic_error("unsupported scheme");
+        rotate_internal(encrypted, steps, galois_keys);
+    }
+
+    void Evaluator::rotate_vector(
+        const Ciphertext &encrypted, int steps, const GaloisKeys &galois_keys, Ciphertext &destination, MemoryPoolHandle pool)
+    {
+        destination = encrypted;
+        rotate_vector_inplace(destination, steps, galois_keys, move(pool));
+    }
+
+    void Evaluator::complex_conjugate_inplace(Ciphertext &encrypted, const GaloisKeys &galois_keys, MemoryPoolHandle pool)
+    {
+        // evaluator.h:1343-1352: conjugation is the Galois element 2N-1 (galois.h get_elt_from_step(0))
+        apply_galois_inplace(encrypted, static_cast<uint32_t>(2 * N_ - 1), galois_keys, move(pool));
+    }
+
+    // ---- batched extension ------------------------------------------------------------------------------
+    void Evaluator::multiply_relinearize_rescale_inplace(
+        vector<Ciphertext *> &encrypted1, const vector<const Ciphertext *> &encrypted2, const RelinKeys &relin_keys)
+    {
+        const size_t n = encrypted1.size();
+        if (n == 0 || encrypted2.size() != n)
+            throw invalid_argument("batch size mismatch");
+        if (relin_keys.parms_id() != context_->key_parms_id() || relin_keys.size() < 1)
+            throw invalid_argument("relin_keys is not valid for encryption parameters");
+        const auto parms_id = encrypted1[0]->parms_id();
+        if (context_->last_parms_id() == parms_id)
+            throw invalid_argument("end of modulus switching chain reached");
+        auto &context_data = *context_->get_context_data(parms_id);
+        for (size_t i = 0; i < n; i++)
+        {
+            validate(*encrypted1[i], "encrypted1");
+            validate(*encrypted2[i], "encrypted2");
+            if (encrypted1[i]->parms_id() != parms_id || encrypted2[i]->parms_id() != parms_id)
+                throw invalid_argument("encrypted1 and encrypted2 parameter mismatch");
+            if (!encrypted1[i]->is_ntt_form() || !encrypted2[i]->is_ntt_form() || encrypted1[i]->size() != 2 || encrypted2[i]->size() != 2)
+                throw invalid_argument("operands must be size-2 NTT-form ciphertexts");
+            const double s = encrypted1[i]->scale() * encrypted2[i]->scale();
+            if (s <= 0 || (static_cast<int>(log2(s)) >= context_data.total_coeff_modulus_bit_count()))
+                throw invalid_argument("scale out of bounds");
+        }
+        ensure_relin(relin_keys, RelinKeys::get_index(2));
+        const size_t L = context_data.parms().coeff_modulus().size(), in_w = 2 * L * N_, out_w = 2 * (L - 1) * N_;
+        void *ha = nullptr, *hb = nullptr, *ho = nullptr; // pinned staging so the copies are real DMA
+        check(gsb_malloc_host(n * in_w * sizeof(uint64_t), &ha));
+        int rc = gsb_malloc_host(n * in_w * sizeof(uint64_t), &hb);
+        if (rc == GSB_OK)
+            rc = gsb_malloc_host(n * out_w * sizeof(uint64_t), &ho);
+        if (rc == GSB_OK)
+        {
+            for (size_t i = 0; i < n; i++)
+            {
+                memcpy(static_cast<uint64_t *>(ha) + i * in_w, encrypted1[i]->data(), in_w * sizeof(uint64_t));
+                memcpy(static_cast<uint64_t *>(hb) + i * in_w, encrypted2[i]->data(), in_w * sizeof(uint64_t));
+            }
+            rc = gsb_mul_relin_rescale_host(
+                ctx_, static_cast<uint64_t *>(ha), static_cast<uint64_t *>(hb), static_cast<uint64_t *>(ho), n, L);
+        }
+        if (rc == GSB_OK)
+        {
+            const double q_last = static_cast<double>(context_data.parms().coeff_modulus().back().value());
+            auto next_id = context_data.next_context_data()->parms_id();
+            for (size_t i = 0; i < n; i++)
+            {
+                const double s = encrypted1[i]->scale() * encrypted2[i]->scale() / q_last;
+                encrypted1[i]->resize(context_, next_id, 2);
+                memcpy(encrypted1[i]->data(), static_cast<uint64_t *>(ho) + i * out_w, out_w * sizeof(uint64_t));
+                encrypted1[i]->is_ntt_form() = true;
+                encrypted1[i]->scale() = s;
+            }
+        }
+        gsb_free_host(ha);
+        gsb_free_host(hb);
+        gsb_free_host(ho);
+        check(rc);
+    }
+
+    // ---- util::ntt_* over NTTTables (util/ntt.h:189-368) -------------------------------------------------
+    namespace util
+    {
+        namespace
+        {
+            mutex g_mu;
+            map<pair<int, uint64_t>, gsb_ctx *> g_ctx; // one single-modulus device context per (log2 N, q)
+
+            gsb_ctx *ctx_for(const seal::util::NTTTables &t)
+            {
+                lock_guard<mutex> lock(g_mu);
+                const auto key = make_pair(t.coeff_count_power(), t.modulus().value());
+                auto it = g_ctx.find(key);
+                if (it != g_ctx.end())
+                    return it->second;
+                gsb_ctx *c = nullptr;
+                const uint64_t q = key.second;
+                check(gsb_ctx_create(0, key.first, &q, 1, 1, &c));
+                g_ctx[key] = c;
+                return c;
+            }
+        } // namespace
+
+        void ntt_negacyclic_harvey(uint64_t *operand, const seal::util::NTTTables &tables)
+        {
+            check(gsb_ntt_forward_host(ctx_for(tables), operand, 1, 1, 0, GSB_NTT_STRICT));
+        }
+        void ntt_negacyclic_harvey_lazy(uint64_t *operand, const seal::util::NTTTables &tables)
+        {
+            check(gsb_ntt_forward_host(ctx_for(tables), operand, 1, 1, 0, GSB_NTT_LAZY));
+        }
+        void inverse_ntt_negacyclic_harvey(uint64_t *operand, const seal::util::NTTTables &tables)
+        {
+            check(gsb_ntt_inverse_host(ctx_for(tables), operand, 1, 1, 0, GSB_NTT_STRICT));
+        }
+        void inverse_ntt_negacyclic_harvey_lazy(uint64_t *operand, const seal::util::NTTTables &tables)
+        {
+            check(gsb_ntt_inverse_host(ctx_for(tables), operand, 1, 1, 0, GSB_NTT_LAZY));
+        }
+        void ntt_negacyclic_harvey(uint64_t *operand, size_t coeff_modulus_size, const seal::util::NTTTables *tables)
+        {
+            for (size_t i = 0; i < coeff_modulus_size; i++)
+                ntt_negacyclic_harvey(operand + (i << tables[i].coeff_count_power()), tables[i]);
+        }
+        void inverse_ntt_negacyclic_harvey(uint64_t *operand, size_t coeff_modulus_size, const seal::util::NTTTables *tables)
+        {
+            for (size_t i = 0; i < coeff_modulus_size; i++)
+                inverse_ntt_negacyclic_harvey(operand + (i << tables[i].coeff_count_power()), tables[i]);
+        }
+    } // namespace util
+} // namespace gsb_seal

@@ -1,0 +1,115 @@
+// Drop-in C++ host shim: seal::Evaluator / seal::util::ntt_* entry points of the reference, served by
+// the B200 library through the C ABI (include/gseal_b200.h).  Compiles against the reference's own
+// headers (native/src); existing callers keep their seal::Ciphertext / RelinKeys / GaloisKeys /
+// NTTTables objects and switch the evaluator type:
+//
+//     gsb_seal::Evaluator evaluator(context);          // was: seal::Evaluator evaluator(context);
+//     evaluator.multiply_inplace(x, y);                // evaluator.h:246
+//     evaluator.relinearize_inplace(x, relin_keys);    // evaluator.h:344
+//     evaluator.rescale_to_next_inplace(x);            // evaluator.h:583
+//     evaluator.rotate_vector_inplace(x, 1, gal_keys); // evaluator.h:1201
+//
+// Same argument meaning, same in-place semantics (resize, scale, parms_id, is_ntt_form), same
+// exception types and messages as native/src/seal/evaluator.cpp; CUDA failures surface as
+// std::runtime_error.  CKKS only (the north-star path); anything else throws std::logic_error, it is
+// never silently routed to a CPU implementation.
+#pragma once
+#include "gseal_b200.h"
+#include "seal/seal.h"
+#include "seal/util/ntt.h"
+#include <cstdint>
+#include <map>
+#include <memory>
+#include <mutex>
+#include <vector>
+
+namespace gsb_seal
+{
+    class Evaluator
+    {
+    public:
+        explicit Evaluator(std::shared_ptr<seal::SEALContext> context, int device = 0);
+        ~Evaluator();
+        Evaluator(const Evaluator &) = delete;
+        Evaluator &operator=(const Evaluator &) = delete;
+
+        // evaluator.h:246-258 / evaluator.cpp:235-272,447-527
+        void multiply_inplace(
+            seal::Ciphertext &encrypted1, const seal::Ciphertext &encrypted2,
+            seal::MemoryPoolHandle pool = seal::MemoryManager::GetPool());
+        void multiply(
+            const seal::Ciphertext &encrypted1, const seal::Ciphertext &encrypted2, seal::Ciphertext &destination,
+            seal::MemoryPoolHandle pool = seal::MemoryManager::GetPool());
+
+        // evaluator.h:344-378 / evaluator.cpp:772-827
+        void relinearize_inplace(
+            seal::Ciphertext &encrypted, const seal::RelinKeys &relin_keys,
+            seal::MemoryPoolHandle pool = seal::MemoryManager::GetPool());
+        void relinearize(
+            const seal::Ciphertext &encrypted, const seal::RelinKeys &relin_keys, seal::Ciphertext &destination,
+            seal::MemoryPoolHandle pool = seal::MemoryManager::GetPool());
+
+        // evaluator.h:565-600 / evaluator.cpp:1090-1126,829-892
+        void rescale_to_next(
+            const seal::Ciphertext &encrypted, seal::Ciphertext &destination,
+            seal::MemoryPoolHandle pool = seal::MemoryManager::GetPool());
+        void rescale_to_next_inplace(seal::Ciphertext &encrypted, seal::MemoryPoolHandle pool = seal::MemoryManager::GetPool());
+
+        // evaluator.h:984-1023 / evaluator.cpp:1841-1943
+        void apply_galois_inplace(
+            seal::Ciphertext &encrypted, std::uint32_t galois_elt, const seal::GaloisKeys &galois_keys,
+            seal::MemoryPoolHandle pool = seal::MemoryManager::GetPool());
+        void apply_galois(
+            const seal::Ciphertext &encrypted, std::uint32_t galois_elt, const seal::GaloisKeys &galois_keys,
+            seal::Ciphertext &destination, seal::MemoryPoolHandle pool = seal::MemoryManager::GetPool());
+
+        // evaluator.h:1201-1252 / evaluator.cpp:1945-2000 (NAF decomposition when a key is missing)
+        void rotate_vector_inplace(
+            seal::Ciphertext &encrypted, int steps, const seal::GaloisKeys &galois_keys,
+            seal::MemoryPoolHandle pool = seal::MemoryManager::GetPool());
+        void rotate_vector(
+            const seal::Ciphertext &encrypted, int steps, const seal::GaloisKeys &galois_keys, seal::Ciphertext &destination,
+            seal::MemoryPoolHandle pool = seal::MemoryManager::GetPool());
+
+        // evaluator.h:1269-1311
+        void complex_conjugate_inplace(
+            seal::Ciphertext &encrypted, const seal::GaloisKeys &galois_keys,
+            seal::MemoryPoolHandle pool = seal::MemoryManager::GetPool());
+
+        // Batched extension (not in the reference): multiply + relinearize + rescale_to_next on n
+        // independent ciphertext pairs in one device pass; results replace encrypted1[i].
+        void multiply_relinearize_rescale_inplace(
+            std::vector<seal::Ciphertext *> &encrypted1, const std::vector<const seal::Ciphertext *> &encrypted2,
+            const seal::RelinKeys &relin_keys);
+
+        gsb_ctx *device_context() const { return ctx_; }
+
+    private:
+        void validate(const seal::Ciphertext &ct, const char *what) const;
+        std::size_t level_limbs(const seal::Ciphertext &ct) const;
+        void ensure_relin(const seal::RelinKeys &keys, std::size_t index);
+        void ensure_galois(const seal::GaloisKeys &keys, std::uint32_t elt);
+        void upload_key(int kind, std::uint32_t slot, const std::vector<seal::PublicKey> &bundles);
+        void rotate_internal(seal::Ciphertext &encrypted, int steps, const seal::GaloisKeys &galois_keys);
+        [[noreturn]] void fail(int rc) const;
+
+        std::shared_ptr<seal::SEALContext> context_;
+        gsb_ctx *ctx_ = nullptr;
+        std::size_t N_ = 0, K_ = 0, k_ = 0;
+        std::mutex mu_;
+        // which host key object (by data pointer) currently sits in each device key slot
+        std::map<std::uint32_t, const void *> relin_loaded_, galois_loaded_;
+    };
+
+    namespace util
+    {
+        // util/ntt.h:189-368 over one limb (CoeffIter) or an RNS polynomial (RNSIter + tables array);
+        // tables are matched to a cached device context by (coeff_count_power, modulus).
+        void ntt_negacyclic_harvey(std::uint64_t *operand, const seal::util::NTTTables &tables);
+        void ntt_negacyclic_harvey_lazy(std::uint64_t *operand, const seal::util::NTTTables &tables);
+        void inverse_ntt_negacyclic_harvey(std::uint64_t *operand, const seal::util::NTTTables &tables);
+        void inverse_ntt_negacyclic_harvey_lazy(std::uint64_t *operand, const seal::util::NTTTables &tables);
+        void ntt_negacyclic_harvey(std::uint64_t *operand, std::size_t coeff_modulus_size, const seal::util::NTTTables *tables);
+        void inverse_ntt_negacyclic_harvey(std::uint64_t *operand, std::size_t coeff_modulus_size, const seal::util::NTTTables *tables);
+    } // namespace util
+} // namespace gsb_seal

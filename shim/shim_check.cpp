@@ -1,0 +1,193 @@
+// TEST program: the reference's seal::Evaluator (CPU) and gsb_seal::Evaluator (B200) side by side on the
+// SAME seal::Ciphertext / RelinKeys / GaloisKeys objects produced by the reference's own KeyGenerator
+// and Encryptor; every output ciphertext is compared word for word (plus metadata), then decrypted.
+// Built by oracle/Makefile (target `shim`) where /root/reference exists; run on the GPU box by
+// tests/test_gpu_shim.py.  Exit code 0 and a final "SHIM_CHECK PASS" line on success.
+#include "gsb_seal_shim.h"
+#include <cmath>
+#include <complex>
+#include <cstdio>
+#include <cstring>
+#include <iostream>
+#include <random>
+
+using namespace seal;
+using namespace std;
+
+static int failures = 0;
+
+static void same(const char *what, const Ciphertext &r, const Ciphertext &d)
+{
+    bool ok = r.size() == d.size() && r.parms_id() == d.parms_id() && r.is_ntt_form() == d.is_ntt_form() && r.scale() == d.scale() &&
+              r.coeff_modulus_size() == d.coeff_modulus_size() &&
+              memcmp(r.data(), d.data(), r.size() * r.coeff_modulus_size() * r.poly_modulus_degree() * sizeof(uint64_t)) == 0;
+    printf("%-34s %s\n", what, ok ? "bit-exact" : "MISMATCH");
+    failures += !ok;
+}
+
+template <class F>
+static void expect_throw(const char *what, F &&f, int kind) // 0 invalid_argument, 1 logic_error
+{
+    int got = -1;
+    try
+    {
+        f();
+    }
+    catch (const invalid_argument &)
+    {
+        got = 0;
+    }
+    catch (const logic_error &)
+    {
+        got = 1;
+    }
+    catch (...)
+    {
+        got = 2;
+    }
+    printf("%-34s %s\n", what, got == kind ? "same exception type" : "WRONG EXCEPTION");
+    failures += got != kind;
+}
+
+static int run(size_t N, vector<int> bits, int k_special)
+{
+    printf("---- CKKS N=%zu, %zu primes, n_special_primes=%d\n", N, bits.size(), k_special);
+    EncryptionParameters parms(scheme_type::CKKS);
+    parms.set_poly_modulus_degree(N);
+    parms.set_coeff_modulus(CoeffModulus::Create(N, bits));
+    parms.set_n_special_primes(k_special);
+    auto context = SEALContext::Create(parms, true, sec_level_type::none);
+    KeyGenerator keygen(context);
+    auto pk = keygen.public_key();
+    auto sk = keygen.secret_key();
+    RelinKeys rlk = keygen.relin_keys_local();
+    GaloisKeys glk = keygen.galois_keys_local();
+    Encryptor enc(context, pk);
+    Decryptor dec(context, sk);
+    CKKSEncoder encoder(context);
+    Evaluator ref(context);
+    gsb_seal::Evaluator dev(context);
+
+    const size_t slots = encoder.slot_count();
+    mt19937_64 rng(42);
+    uniform_real_distribution<double> dist(-1.0, 1.0);
+    vector<double> va(slots), vb(slots);
+    for (size_t i = 0; i < slots; i++)
+        va[i] = dist(rng), vb[i] = dist(rng);
+    const double scale = pow(2.0, 40);
+    Plaintext pa, pb;
+    encoder.encode(va, scale, pa);
+    encoder.encode(vb, scale, pb);
+    Ciphertext a, b;
+    enc.encrypt(pa, a);
+    enc.encrypt(pb, b);
+
+    Ciphertext r = a, d = a;
+    ref.multiply_inplace(r, b);
+    dev.multiply_inplace(d, b);
+    same("multiply_inplace", r, d);
+    ref.relinearize_inplace(r, rlk);
+    dev.relinearize_inplace(d, rlk);
+    same("relinearize_inplace", r, d);
+    ref.rescale_to_next_inplace(r);
+    dev.rescale_to_next_inplace(d);
+    same("rescale_to_next_inplace", r, d);
+    Ciphertext prod = d;
+    ref.rotate_vector_inplace(r, 1, glk);
+    dev.rotate_vector_inplace(d, 1, glk);
+    same("rotate_vector_inplace(+1)", r, d);
+    ref.rotate_vector_inplace(r, -3, glk); // not a power of two: NAF path, two key switches
+    dev.rotate_vector_inplace(d, -3, glk);
+    same("rotate_vector_inplace(-3, NAF)", r, d);
+    ref.complex_conjugate_inplace(r, glk);
+    dev.complex_conjugate_inplace(d, glk);
+    same("complex_conjugate_inplace", r, d);
+    {
+        Ciphertext r2 = a, d2 = a;
+        ref.square_inplace(r2);
+        dev.multiply_inplace(d2, d2);
+        same("multiply_inplace(x, x) vs square", r2, d2);
+    }
+    {
+        // batched extension vs three reference calls
+        vector<Ciphertext> xs(3, a), ys(3, b);
+        enc.encrypt(pb, xs[1]);
+        enc.encrypt(pa, ys[2]);
+        vector<Ciphertext> want = xs;
+        for (size_t i = 0; i < 3; i++)
+        {
+            ref.multiply_inplace(want[i], ys[i]);
+            ref.relinearize_inplace(want[i], rlk);
+            ref.rescale_to_next_inplace(want[i]);
+        }
+        vector<Ciphertext *> px{ &xs[0], &xs[1], &xs[2] };
+        vector<const Ciphertext *> py{ &ys[0], &ys[1], &ys[2] };
+        dev.multiply_relinearize_rescale_inplace(px, py, rlk);
+        for (size_t i = 0; i < 3; i++)
+            same("batched mul+relin+rescale", want[i], xs[i]);
+    }
+    // semantic check: decrypt the device product
+    Plaintext pd;
+    dec.decrypt(prod, pd);
+    vector<double> out;
+    encoder.decode(pd, out);
+    double err = 0;
+    for (size_t i = 0; i < slots; i++)
+        err = max(err, fabs(out[i] - va[i] * vb[i]));
+    printf("%-34s max |err| = %.3g %s\n", "decrypt(device a*b)", err, err < 1e-4 ? "ok" : "TOO LARGE");
+    failures += !(err < 1e-4);
+
+    // util::ntt_* over the context's own NTTTables
+    {
+        auto tables = context->key_context_data()->small_ntt_tables();
+        vector<uint64_t> x(N), y;
+        for (auto &v : x)
+            v = rng() % tables[0].modulus().value();
+        y = x;
+        seal::util::ntt_negacyclic_harvey(x.data(), tables[0]);
+        gsb_seal::util::ntt_negacyclic_harvey(y.data(), tables[0]);
+        bool ok = x == y;
+        seal::util::inverse_ntt_negacyclic_harvey_lazy(x.data(), tables[0]);
+        gsb_seal::util::inverse_ntt_negacyclic_harvey_lazy(y.data(), tables[0]);
+        ok = ok && x == y;
+        printf("%-34s %s\n", "util::ntt / inverse lazy", ok ? "bit-exact" : "MISMATCH");
+        failures += !ok;
+    }
+    // error convention
+    {
+        RelinKeys empty;
+        Ciphertext c3 = a;
+        ref.multiply_inplace(c3, b);
+        expect_throw("relinearize with foreign keys", [&] { Ciphertext t = c3; dev.relinearize_inplace(t, empty); }, 0);
+        expect_throw("apply_galois even element", [&] { Ciphertext t = a; dev.apply_galois_inplace(t, 4, glk); }, 0);
+        expect_throw("apply_galois on size 3", [&] { Ciphertext t = c3; dev.apply_galois_inplace(t, 3, glk); }, 0);
+        Plaintext plast;
+        encoder.encode(va, context->last_parms_id(), pow(2.0, 15), plast);
+        Ciphertext last;
+        enc.encrypt(plast, last);
+        expect_throw("rescale at last level", [&] { Ciphertext t = last; dev.rescale_to_next_inplace(t); }, 0);
+        expect_throw("multiply level mismatch", [&] { Ciphertext t = a; dev.multiply_inplace(t, last); }, 0);
+    }
+    return failures;
+}
+
+int main()
+{
+    try
+    {
+        run(8192, { 50, 40, 40, 40, 50 }, 1);
+        run(4096, { 40, 30, 30, 30, 40, 40 }, 2);
+    }
+    catch (const exception &e)
+    {
+        printf("exception: %s\n", e.what());
+        return 2;
+    }
+    if (failures)
+    {
+        printf("SHIM_CHECK FAIL (%d)\n", failures);
+        return 1;
+    }
+    printf("SHIM_CHECK PASS\n");
+    return 0;
+}

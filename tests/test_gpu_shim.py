@@ -1,0 +1,36 @@
+"""Drop-in check of the C++ shim (shim/gsb_seal_shim.{h,cpp}) on the GPU box: oracle/_ref/shim_check
+links the UNMODIFIED reference and the B200 library into one program and compares
+seal::Evaluator (CPU) with gsb_seal::Evaluator (device) on the same seal::Ciphertext / RelinKeys /
+GaloisKeys objects -- word for word, metadata, decryption, exception types.  The binary is built in
+the container that has /root/reference (oracle/Makefile target `shim`) and travels with the repo."""
+import os
+import subprocess
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+BIN = os.path.join(ROOT, "oracle", "_ref", "shim_check")
+
+
+@pytest.mark.gpu
+def test_shim_matches_reference_evaluator():
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    if not os.path.exists(BIN):
+        pytest.skip("oracle/_ref/shim_check not built (needs /root/reference at build time)")
+    p = subprocess.run([BIN], capture_output=True, text=True, timeout=600)
+    print(p.stdout[-4000:])
+    assert p.returncode == 0, p.stdout[-3000:] + p.stderr[-1000:]
+    assert "SHIM_CHECK PASS" in p.stdout
+    assert "MISMATCH" not in p.stdout
+
+
+def test_shim_compiles_against_reference_headers():
+    """CPU-side: where the reference is present, the shim must compile against its headers."""
+    if not os.path.isdir("/root/reference/native/src/seal"):
+        pytest.skip("/root/reference absent")
+    from gemini_seal_b200 import build
+    build.build()
+    subprocess.run(["make", "-s", "-C", os.path.join(ROOT, "oracle"), "shim"], check=True)
+    assert os.path.exists(BIN)
