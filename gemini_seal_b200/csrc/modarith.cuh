@@ -24,23 +24,84 @@ namespace gsb
         return __umul64hi(a, b);
     }
 
+    // lo64(x*y + h*nq + add) as one multiply-add chain: 2 IMAD.WIDE + 4 IMAD, no separate carry / add
+    // instructions (IMAD.WIDE runs at half the IMAD rate on sm_100 and the FMA-heavy pipe is what
+    // bounds the butterflies, so nothing but multiplies may land on it).
+    GSB_DEV uint64_t mad_lo64_2(uint64_t x, uint64_t y, uint64_t h, uint64_t nq, uint64_t add)
+    {
+#ifdef GSB_CUSIM
+        return x * y + h * nq + add;
+#else
+        uint64_t r;
+        asm("{\n\t"
+            ".reg .u32 x0, x1, y0, y1, h0, h1, n0, n1, lo, hi;\n\t"
+            ".reg .u64 t;\n\t"
+            "mov.b64 {x0, x1}, %1;\n\t"
+            "mov.b64 {y0, y1}, %2;\n\t"
+            "mov.b64 {h0, h1}, %3;\n\t"
+            "mov.b64 {n0, n1}, %4;\n\t"
+            "mad.wide.u32 t, x0, y0, %5;\n\t"
+            "mad.wide.u32 t, h0, n0, t;\n\t"
+            "mov.b64 {lo, hi}, t;\n\t"
+            "mad.lo.u32 hi, x0, y1, hi;\n\t"
+            "mad.lo.u32 hi, x1, y0, hi;\n\t"
+            "mad.lo.u32 hi, h0, n1, hi;\n\t"
+            "mad.lo.u32 hi, h1, n0, hi;\n\t"
+            "mov.b64 %0, {lo, hi};\n\t"
+            "}"
+            : "=l"(r)
+            : "l"(x), "l"(y), "l"(h), "l"(nq), "l"(add));
+        return r;
+#endif
+    }
+
+    // lo64(h*nq + add): 1 IMAD.WIDE + 2 IMAD
+    GSB_DEV uint64_t mad_lo64_1(uint64_t h, uint64_t nq, uint64_t add)
+    {
+#ifdef GSB_CUSIM
+        return h * nq + add;
+#else
+        uint64_t r;
+        asm("{\n\t"
+            ".reg .u32 h0, h1, n0, n1, lo, hi;\n\t"
+            ".reg .u64 t;\n\t"
+            "mov.b64 {h0, h1}, %1;\n\t"
+            "mov.b64 {n0, n1}, %2;\n\t"
+            "mad.wide.u32 t, h0, n0, %3;\n\t"
+            "mov.b64 {lo, hi}, t;\n\t"
+            "mad.lo.u32 hi, h0, n1, hi;\n\t"
+            "mad.lo.u32 hi, h1, n0, hi;\n\t"
+            "mov.b64 %0, {lo, hi};\n\t"
+            "}"
+            : "=l"(r)
+            : "l"(h), "l"(nq), "l"(add));
+        return r;
+#endif
+    }
+
     // SlothfulNTT::mulmodLazy (util/ntt.cpp:230-234): x*y - hi64(x*y')*q  (mod 2^64), in [0,2q).
+    // x*y - h*q == x*y + h*(2^64 - q) (mod 2^64).
     GSB_DEV uint64_t mulmod_lazy(uint64_t x, uint64_t y, uint64_t ys, uint64_t q)
     {
-        // x*y - h*q == x*y + h*(2^64 - q) (mod 2^64): one multiply-add chain, no negate
-        return x * y + mulhi(x, ys) * (0 - q);
+        return mad_lo64_2(x, y, mulhi(x, ys), 0 - q, 0);
+    }
+
+    // add + mulmodLazy(x, y, y') (mod 2^64): the butterfly's "u + v" folded into the multiply chain.
+    GSB_DEV uint64_t mulmod_lazy_add(uint64_t x, uint64_t y, uint64_t ys, uint64_t q, uint64_t add)
+    {
+        return mad_lo64_2(x, y, mulhi(x, ys), 0 - q, add);
     }
 
     // SlothfulNTT::reduceBarrettLazy (util/ntt.cpp:237-241)
     GSB_DEV uint64_t reduce_barrett_lazy(uint64_t x, uint64_t rdp, uint64_t q)
     {
-        return x + mulhi(x, rdp) * (0 - q);
+        return mad_lo64_1(mulhi(x, rdp), 0 - q, x);
     }
 
     // MulModShoup::operator() (multi_special_primes.cpp:13-19) / FastMulMod (uintarithsmallmod.h:312-322)
     GSB_DEV uint64_t mulmod_shoup(uint64_t x, uint64_t c, uint64_t cs, uint64_t p)
     {
-        uint64_t t = x * c + mulhi(x, cs) * (0 - p);
+        uint64_t t = mad_lo64_2(x, c, mulhi(x, cs), 0 - p, 0);
         return t - (t >= p ? p : 0);
     }
 
@@ -56,14 +117,14 @@ namespace gsb
         uint64_t s = tmp1 + lo;
         carry = hi + (s < tmp1 ? 1 : 0);
         uint64_t quot = z1 * cr1 + tmp3 + carry;
-        uint64_t r = z0 + quot * (0 - q);
+        uint64_t r = mad_lo64_1(quot, 0 - q, z0);
         return r - (r >= q ? q : 0);
     }
 
     // barrett_reduce_63 (util/uintarithsmallmod.h:181-207)
     GSB_DEV uint64_t barrett63(uint64_t x, uint64_t q, uint64_t cr1)
     {
-        uint64_t r = x + mulhi(x, cr1) * (0 - q);
+        uint64_t r = mad_lo64_1(mulhi(x, cr1), 0 - q, x);
         return r - (r >= q ? q : 0);
     }
 

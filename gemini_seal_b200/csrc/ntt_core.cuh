@@ -230,9 +230,11 @@ namespace gsb
                         uint64_t u = x[a];
                         if (LAST && g == 0)
                             u = reduce_barrett_lazy(u, c.rdp, c.q);
-                        const uint64_t v = mulmod_lazy(x[b], w.x, w.y, c.q);
-                        x[a] = u + v;
-                        x[b] = u - v + c.two_q;
+                        // x[a] = u + v with u folded into v's multiply chain; x[b] = u - v + 2q
+                        //      = (2u + 2q) - x[a]  (all mod 2^64, exactly the reference's words)
+                        const uint64_t s = mulmod_lazy_add(x[b], w.x, w.y, c.q, u);
+                        x[b] = u + u + c.two_q - s;
+                        x[a] = s;
                     }
                 }
             }
