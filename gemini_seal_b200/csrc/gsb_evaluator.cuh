@@ -201,8 +201,8 @@ namespace gsb
 
     // switch_key_inplace for `B` ciphertexts (evaluator.cpp:2259-2368).  scratch must hold
     // B * ks_words_per_ct words (+ alignment slack).
-    template <int LOGN>
-    static void switch_key_core(
+    template <int LOGN, bool K1>
+    static void switch_key_core_t(
         gsb_ctx *ctx, void *scratch, const uint64_t *target, size_t target_stride, const SwitchKey &key, const KsOutput &o,
         size_t B, size_t L, cudaStream_t st)
     {
@@ -225,14 +225,14 @@ namespace gsb
         // Step 2 + first NTT pass of step 3 (:2310, :2322): mod-up fused into the column pass.
         if constexpr (two)
         {
-            IoPair<ModupLoad, PlainStore<OUT_RAW>> io{ ModupArgs{ ks, coef }, PlainStoreArgs{ ext1, E * N } };
+            IoPair<ModupLoadT<K1>, PlainStore<OUT_RAW>> io{ ModupArgs{ ks, coef }, PlainStoreArgs{ ext1, E * N } };
             launch_fwd_cols<LOGN>(io, tab, ModMap{ iL, static_cast<int>(ctx->L0), 0 }, iE, static_cast<int>(B * beta), st, "modup");
         }
         // Step 3 + Barrett part of step 4: last NTT pass fused with the key inner product.
         {
             typedef MacPlan<LOGN> MP;
             KsMacArgs a{ ks, target, target_stride, coef, ext1, key.d, red, static_cast<uint32_t>(ctx->K) };
-            auto kfn = ks_mac_kernel<LOGN>;
+            auto kfn = ks_mac_kernel<LOGN, K1>;
             allow_smem(kfn, MP::TP::smem_bytes);
             dim3 grid(static_cast<unsigned>(B), 1u << (LOGN - MP::T - 3), static_cast<unsigned>(E));
             GSB_LAUNCH("ks_mac", "", kfn, grid, dim3(1 << MP::T), MP::TP::smem_bytes, st, a, tab);
@@ -247,16 +247,27 @@ namespace gsb
         const ModMap mm{ 1 << 30, 0, 0 };
         if constexpr (two)
         {
-            IoPair<MdLoad, PlainStore<OUT_RAW>> io1{ la, PlainStoreArgs{ tmp, L * N } };
+            IoPair<MdLoadT<K1>, PlainStore<OUT_RAW>> io1{ la, PlainStoreArgs{ tmp, L * N } };
             launch_fwd_cols<LOGN>(io1, tab, mm, iL, static_cast<int>(2 * B), st, "moddown");
             IoPair<PlainLoad, MdStore> io2{ PlainArgs{ tmp, L * N }, sa };
             launch_fwd_contig<LOGN>(io2, tab, mm, iL, static_cast<int>(2 * B), st, "moddown");
         }
         else
         {
-            IoPair<MdLoad, MdStore> io{ la, sa };
+            IoPair<MdLoadT<K1>, MdStore> io{ la, sa };
             launch_fwd_contig<LOGN>(io, tab, mm, iL, static_cast<int>(2 * B), st, "moddown");
         }
+    }
+
+    template <int LOGN>
+    static void switch_key_core(
+        gsb_ctx *ctx, void *scratch, const uint64_t *target, size_t target_stride, const SwitchKey &key, const KsOutput &o,
+        size_t B, size_t L, cudaStream_t st)
+    {
+        if (ctx->k == 1)
+            switch_key_core_t<LOGN, true>(ctx, scratch, target, target_stride, key, o, B, L, st);
+        else
+            switch_key_core_t<LOGN, false>(ctx, scratch, target, target_stride, key, o, B, L, st);
     }
 
     // rescale for n_polys polynomials of L limbs (util/rns.cpp:777-851). t = n_polys*N words scratch.

@@ -64,7 +64,10 @@ namespace gsb
 
     // ---- mod-up prologue (modup_to_single_rns, multi_special_primes.cpp:80-148) --------------------
     // Source = coefficient-form bundle limbs coef[b][s0 .. s0+cnt); destination modulus = ext slot kap.
-    struct ModupCore
+    // K1: the context has one special prime, so every bundle is a single limb and only the
+    // copy / Barrett-63 path exists (keeps the k > 1 conversion code out of the k = 1 kernels).
+    template <bool K1>
+    struct ModupCoreT
     {
         const uint64_t *src; // coef + (b*L + s0)*N
         const uint64_t *a;   // modup_a + (j*k)*2
@@ -74,7 +77,7 @@ namespace gsb
         uint32_t N, E;
         int cnt;
         bool reduce; // single-limb bundle with q_src > q_dst -> barrett_reduce_63 (:104-107)
-        GSB_DEV ModupCore(const KsDev &ks, const uint64_t *coef, int b, int j, int kap, const LimbC &c)
+        GSB_DEV ModupCoreT(const KsDev &ks, const uint64_t *coef, int b, int j, int kap, const LimbC &c)
         {
             const int s0 = j * static_cast<int>(ks.k);
             const int s1 = s0 + static_cast<int>(ks.k) < static_cast<int>(ks.L) ? s0 + static_cast<int>(ks.k) : static_cast<int>(ks.L);
@@ -102,10 +105,10 @@ namespace gsb
         }
         // single-limb bundle: raw = the load, xform = the optional Barrett-63; multi-limb bundle: the
         // whole conversion happens in raw (several source limbs per word)
-        GSB_DEV uint64_t raw(uint32_t d) const { return cnt == 1 ? src[d] : convert(d); }
+        GSB_DEV uint64_t raw(uint32_t d) const { return (K1 || cnt == 1) ? src[d] : convert(d); }
         GSB_DEV void raw2(uint32_t d, uint64_t &x, uint64_t &y) const
         {
-            if (cnt == 1)
+            if (K1 || cnt == 1)
             {
                 const ulonglong2 v = *reinterpret_cast<const ulonglong2 *>(src + d);
                 x = v.x;
@@ -119,6 +122,7 @@ namespace gsb
         }
         GSB_DEV uint64_t xform(uint64_t v) const { return reduce ? barrett63(v, q, cr1) : v; }
     };
+    typedef ModupCoreT<false> ModupCore;
 
     // grid: y = ext slot kap, z = b*beta + j; slots inside the source bundle are skipped.
     struct ModupArgs
@@ -132,11 +136,12 @@ namespace gsb
             return y >= s0 && y < s0 + static_cast<int>(ks.k) && y < static_cast<int>(ks.L);
         }
     };
-    struct ModupLoad : ModupCore
+    template <bool K1>
+    struct ModupLoadT : ModupCoreT<K1>
     {
         typedef ModupArgs Args;
-        GSB_DEV ModupLoad(const Args &a, int y, int z, int, const LimbC &c, uint32_t)
-            : ModupCore(a.ks, a.coef, z / static_cast<int>(a.ks.beta), z % static_cast<int>(a.ks.beta), y, c)
+        GSB_DEV ModupLoadT(const Args &a, int y, int z, int, const LimbC &c, uint32_t)
+            : ModupCoreT<K1>(a.ks, a.coef, z / static_cast<int>(a.ks.beta), z % static_cast<int>(a.ks.beta), y, c)
         {}
     };
 
@@ -149,7 +154,8 @@ namespace gsb
         const uint64_t *red;
         GSB_DEV bool skip(int, int) const { return false; }
     };
-    struct MdLoad
+    template <bool K1>
+    struct MdLoadT
     {
         typedef MdLoadArgs Args;
         const uint64_t *sp;  // red + (z*E + L)*N
@@ -159,7 +165,7 @@ namespace gsb
         uint64_t q, cr0, cr1, p0, p0cr1;
         uint32_t N;
         int k;
-        GSB_DEV MdLoad(const Args &a, int y, int z, int, const LimbC &c, uint32_t N_)
+        GSB_DEV MdLoadT(const Args &a, int y, int z, int, const LimbC &c, uint32_t N_)
         {
             sp = a.red + (static_cast<size_t>(z) * a.ks.E + a.ks.L) * N_;
             ih = a.ks.inv_hat;
@@ -183,7 +189,7 @@ namespace gsb
             }
             return barrett128(lo, hi, q, cr0, cr1);
         }
-        GSB_DEV uint64_t raw(uint32_t d) const { return k == 1 ? sp[d] : convert(d); }
+        GSB_DEV uint64_t raw(uint32_t d) const { return (K1 || k == 1) ? sp[d] : convert(d); }
         GSB_DEV void raw2(uint32_t d, uint64_t &x, uint64_t &y) const
         {
             x = raw(d);
@@ -191,7 +197,7 @@ namespace gsb
         }
         GSB_DEV uint64_t xform(uint64_t v) const
         {
-            if (k != 1)
+            if (!K1 && k != 1)
                 return v;
             // :268-275: negate(barrett_reduce_63(c_p)) then barrett_reduce_128 of (v, 0)
             const uint64_t t = neg_mod(barrett63(v, p0, p0cr1), p0);
@@ -360,7 +366,7 @@ namespace gsb
         typedef TilePlan<T, G_HI, 0> TP;
     };
 
-    template <int LOGN>
+    template <int LOGN, bool K1>
     __global__ void __launch_bounds__(1 << MacPlan<LOGN>::T, MacPlan<LOGN>::T <= 8 ? 2 : 1) ks_mac_kernel(KsMacArgs p, NttTables tab)
     {
         typedef MacPlan<LOGN> MP;
@@ -406,7 +412,7 @@ namespace gsb
             }
             else
             {
-                const ModupCore pro(ks, p.coef, b, j, kap, c);
+                const ModupCoreT<K1> pro(ks, p.coef, b, j, kap, c);
                 xf_load_raw<T, MP::G_HI, 0, false>(xn, tid, tile, map, pro);
             }
         };
@@ -423,7 +429,7 @@ namespace gsb
             const bool direct = in_bundle(j);
             if (!MP::two_pass && !direct)
             {
-                const ModupCore pro(ks, p.coef, b, j, kap, c);
+                const ModupCoreT<K1> pro(ks, p.coef, b, j, kap, c);
 #pragma unroll
                 for (int r = 0; r < 8; r++)
                     x[r] = pro.xform(xn[r]);
@@ -434,27 +440,22 @@ namespace gsb
                 for (int r = 0; r < 8; r++)
                     x[r] = xn[r];
             }
-            // key words of this bundle and the next bundle's operand: in flight during the butterflies
-            const uint64_t *k0 = p.key + (static_cast<size_t>(j * 2) * p.K + mod) * N + d0;
-            const uint64_t *k1 = k0 + static_cast<size_t>(p.K) * N;
-            ulonglong2 u[4], v[4];
-#pragma unroll
-            for (int r = 0; r < 4; r++)
-            {
-                u[r] = __ldg(reinterpret_cast<const ulonglong2 *>(k0) + r);
-                v[r] = __ldg(reinterpret_cast<const ulonglong2 *>(k1) + r);
-            }
+            // the next bundle's operand stays in flight during the butterflies
             if (j + 1 < nb)
                 load_bundle(j + 1, xn);
             if (!direct)
                 fwd_compute<T, MP::G_HI, 0, true, 0>(x, smem, tid, tw, c, parity);
+            const uint64_t *k0 = p.key + (static_cast<size_t>(j * 2) * p.K + mod) * N + d0;
+            const uint64_t *k1 = k0 + static_cast<size_t>(p.K) * N;
 #pragma unroll
             for (int r = 0; r < 4; r++)
             {
-                mac128(lo[0][2 * r], hi[0][2 * r], x[2 * r], u[r].x);
-                mac128(lo[0][2 * r + 1], hi[0][2 * r + 1], x[2 * r + 1], u[r].y);
-                mac128(lo[1][2 * r], hi[1][2 * r], x[2 * r], v[r].x);
-                mac128(lo[1][2 * r + 1], hi[1][2 * r + 1], x[2 * r + 1], v[r].y);
+                const ulonglong2 u = __ldg(reinterpret_cast<const ulonglong2 *>(k0) + r);
+                const ulonglong2 v = __ldg(reinterpret_cast<const ulonglong2 *>(k1) + r);
+                mac128(lo[0][2 * r], hi[0][2 * r], x[2 * r], u.x);
+                mac128(lo[0][2 * r + 1], hi[0][2 * r + 1], x[2 * r + 1], u.y);
+                mac128(lo[1][2 * r], hi[1][2 * r], x[2 * r], v.x);
+                mac128(lo[1][2 * r + 1], hi[1][2 * r + 1], x[2 * r + 1], v.y);
             }
         }
 #pragma unroll

@@ -232,8 +232,10 @@ namespace gsb
                             u = reduce_barrett_lazy(u, c.rdp, c.q);
                         // x[a] = u + v with u folded into v's multiply chain; x[b] = u - v + 2q
                         //      = (2u + 2q) - x[a]  (all mod 2^64, exactly the reference's words)
+                        // (c.pad is a run-time zero: it keeps both sums three-input IADD3s on the ALU pipe
+                        // instead of IMAD.X on the FMA-heavy pipe that bounds these kernels)
                         const uint64_t s = mulmod_lazy_add(x[b], w.x, w.y, c.q, u);
-                        x[b] = u + u + c.two_q - s;
+                        x[b] = (u + u + c.two_q) + (c.pad - s);
                         x[a] = s;
                     }
                 }
@@ -265,7 +267,7 @@ namespace gsb
                     {
                         const int a = sub * (1 << R) + (grp << (s + 1)) + i, b = a + (1 << s);
                         const uint64_t u = x[a], v = x[b];
-                        uint64_t t = u + v;
+                        uint64_t t = u + v + c.pad; // c.pad == 0 at run time, see fwd_round
                         t -= (t >= c.two_q) ? c.two_q : 0;
                         if (LAST && s == R - 1)
                             t = mulmod_lazy(t, c.inv_n, c.inv_n_s, c.q);
