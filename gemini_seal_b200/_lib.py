@@ -82,7 +82,7 @@ def load(path=None):
     global _lib
     if path is None and _lib is not None:
         return _lib
-    p = path or LIB_PATH
+    p = path or os.environ.get("GSB_B200_LIB") or LIB_PATH  # GSB_B200_LIB: an alternative nvcc build (tuning experiments)
     if not os.path.exists(p):
         raise RuntimeError(
             "gemini_seal_b200: CUDA library %s is missing; run `python -m gemini_seal_b200.build` "

@@ -233,9 +233,9 @@ namespace gsb
             typedef MacPlan<LOGN> MP;
             KsMacArgs a{ ks, target, target_stride, coef, ext1, key.d, red, static_cast<uint32_t>(ctx->K) };
             auto kfn = ks_mac_kernel<LOGN, K1>;
-            allow_smem(kfn, MP::TP::smem_bytes);
+            allow_smem(kfn, MP::smem_bytes);
             dim3 grid(static_cast<unsigned>(B), 1u << (LOGN - MP::T - 3), static_cast<unsigned>(E));
-            GSB_LAUNCH("ks_mac", "", kfn, grid, dim3(1 << MP::T), MP::TP::smem_bytes, st, a, tab);
+            GSB_LAUNCH("ks_mac", "", kfn, grid, dim3(1 << MP::T), MP::smem_bytes, st, a, tab);
         }
         // Step 4 (:2353-2357): lazy inverse NTT of the special slots.
         ntt_inverse_plain<LOGN>(

@@ -364,6 +364,25 @@ namespace gsb
         static constexpr int T = two_pass ? 8 : Split<LOGN>::T1;
         static constexpr int G_HI = two_pass ? LOGN - Split<LOGN>::A - 1 : LOGN - 1;
         typedef TilePlan<T, G_HI, 0> TP;
+        static constexpr uint32_t TILE = 8u << T;
+        // two-pass plans stage the operand tile (TILE words) and the two key tiles (2*TILE words)
+        // through shared memory with bulk copies, behind three mbarriers
+        static constexpr size_t stage_words = two_pass ? size_t(3) * TILE : 0;
+        static constexpr size_t smem_bytes = TP::smem_bytes + stage_words * sizeof(uint64_t) + 16;
+    };
+
+    // reads of a staged (linear) operand tile in the first round's register layout
+    struct StagedPro
+    {
+        const uint64_t *st;
+        GSB_DEV uint64_t raw(uint32_t d) const { return st[d]; }
+        GSB_DEV void raw2(uint32_t d, uint64_t &a, uint64_t &b) const
+        {
+            const ulonglong2 v = *reinterpret_cast<const ulonglong2 *>(st + d);
+            a = v.x;
+            b = v.y;
+        }
+        GSB_DEV uint64_t xform(uint64_t v) const { return v; }
     };
 
     template <int LOGN, bool K1>
@@ -382,76 +401,117 @@ namespace gsb
         const uint32_t d0 = map.coeff(tile, tid * 8);
         uint64_t *smem = dyn_smem();
         Twiddle *tws = reinterpret_cast<Twiddle *>(smem + TP::exch_words);
-        uint64_t *bar = reinterpret_cast<uint64_t *>(tws + TP::PAIRS);
-        if (tid == 0)
-            mbar_init(bar);
-        __syncthreads();
-        if (tid == 0)
-            TP::TwC::stage(tws, WW, N, map.off(tile), false, bar);
-        const typename TP::TwC tw{ tws, TwGlobal{ WW, N, map.off(tile), N } };
+        uint64_t *st_op = reinterpret_cast<uint64_t *>(tws + TP::PAIRS);
+        uint64_t *st_key = st_op + (MP::two_pass ? MP::TILE : 0);
+        uint64_t *bar = st_op + MP::stage_words; // [0] twiddles, [1] operand tile, [2] key tiles
         const int nb = static_cast<int>(ks.beta), k = static_cast<int>(ks.k), L = static_cast<int>(ks.L);
         auto in_bundle = [&](int j) { return kap >= j * k && kap < j * k + k && kap < L; };
-        // raw loads of bundle j's operand tile into xn (first-round register layout, or the final
-        // layout for the in-bundle limb that needs no transform)
-        auto load_bundle = [&](int j, uint64_t (&xn)[8]) {
-            if (in_bundle(j))
-            {
-                const uint64_t *t = p.target + static_cast<size_t>(b) * p.target_stride + static_cast<size_t>(kap) * N + d0;
-#pragma unroll
-                for (int r = 0; r < 8; r += 2)
-                {
-                    const ulonglong2 v = *reinterpret_cast<const ulonglong2 *>(t + r);
-                    xn[r] = v.x;
-                    xn[r + 1] = v.y;
-                }
-            }
-            else if constexpr (MP::two_pass)
-            {
-                const PlainPro pro(p.ext1, static_cast<size_t>(ks.E) * N, kap, b * nb + j, N);
-                xf_load_raw<T, MP::G_HI, 0, false>(xn, tid, tile, map, pro);
-            }
-            else
-            {
-                const ModupCoreT<K1> pro(ks, p.coef, b, j, kap, c);
-                xf_load_raw<T, MP::G_HI, 0, false>(xn, tid, tile, map, pro);
-            }
+        constexpr uint32_t tile_bytes = MP::TILE * static_cast<uint32_t>(sizeof(uint64_t));
+        // bulk copy of bundle j's operand tile: the column-pass output, or the original NTT-form
+        // target limb for the bundle that contains kap (:2319-2320)
+        auto issue_operand = [&](int j) {
+            const uint64_t *src = in_bundle(j)
+                                      ? p.target + static_cast<size_t>(b) * p.target_stride + static_cast<size_t>(kap) * N
+                                      : p.ext1 + (static_cast<size_t>(b * nb + j) * ks.E + kap) * N;
+            mbar_expect(bar + 1, tile_bytes);
+            bulk_g2s(st_op, src + map.off(tile), tile_bytes, bar + 1);
         };
-        uint64_t lo[2][8], hi[2][8], xn[8];
+        auto issue_key = [&](int j) {
+            const uint64_t *k0 = p.key + (static_cast<size_t>(j * 2) * p.K + mod) * N + map.off(tile);
+            mbar_expect(bar + 2, 2 * tile_bytes);
+            bulk_g2s(st_key, k0, tile_bytes, bar + 2);
+            bulk_g2s(st_key + MP::TILE, k0 + static_cast<size_t>(p.K) * N, tile_bytes, bar + 2);
+        };
+        if (tid == 0)
+        {
+            mbar_init(bar);
+            if constexpr (MP::two_pass)
+            {
+                mbar_init(bar + 1);
+                mbar_init(bar + 2);
+            }
+        }
+        __syncthreads();
+        if (tid == 0)
+        {
+            if constexpr (MP::two_pass)
+                issue_operand(0);
+            TP::TwC::stage(tws, WW, N, map.off(tile), false, bar);
+        }
+        const typename TP::TwC tw{ tws, TwGlobal{ WW, N, map.off(tile), N } };
+        uint64_t lo[2][8], hi[2][8];
 #pragma unroll
         for (int r = 0; r < 8; r++)
             lo[0][r] = hi[0][r] = lo[1][r] = hi[1][r] = 0;
-        load_bundle(0, xn);
         mbar_wait(bar, 0);
         int parity = 0;
         for (int j = 0; j < nb; j++)
         {
             uint64_t x[8];
             const bool direct = in_bundle(j);
-            if (!MP::two_pass && !direct)
+            if constexpr (MP::two_pass)
             {
-                const ModupCoreT<K1> pro(ks, p.coef, b, j, kap, c);
+                mbar_wait(bar + 1, j & 1);
+                if (direct)
+                {
 #pragma unroll
-                for (int r = 0; r < 8; r++)
-                    x[r] = pro.xform(xn[r]);
+                    for (int r = 0; r < 8; r += 2)
+                    {
+                        const ulonglong2 v = *reinterpret_cast<const ulonglong2 *>(st_op + tid * 8 + r);
+                        x[r] = v.x;
+                        x[r + 1] = v.y;
+                    }
+                }
+                else
+                    xf_load_raw<T, MP::G_HI, 0, false>(x, tid, 0, map, StagedPro{ st_op });
+                // every thread holds its operand words and is past the previous bundle's key reads:
+                // both staging areas may be refilled while the butterflies run
+                __syncthreads();
+                if (tid == 0)
+                {
+                    issue_key(j);
+                    if (j + 1 < nb)
+                        issue_operand(j + 1);
+                }
+            }
+            else if (direct)
+            {
+                const uint64_t *t = p.target + static_cast<size_t>(b) * p.target_stride + static_cast<size_t>(kap) * N + d0;
+#pragma unroll
+                for (int r = 0; r < 8; r += 2)
+                {
+                    const ulonglong2 v = *reinterpret_cast<const ulonglong2 *>(t + r);
+                    x[r] = v.x;
+                    x[r + 1] = v.y;
+                }
             }
             else
             {
+                const ModupCoreT<K1> pro(ks, p.coef, b, j, kap, c);
+                xf_load_raw<T, MP::G_HI, 0, false>(x, tid, tile, map, pro);
 #pragma unroll
                 for (int r = 0; r < 8; r++)
-                    x[r] = xn[r];
+                    x[r] = pro.xform(x[r]);
             }
-            // the next bundle's operand stays in flight during the butterflies
-            if (j + 1 < nb)
-                load_bundle(j + 1, xn);
             if (!direct)
                 fwd_compute<T, MP::G_HI, 0, true, 0>(x, smem, tid, tw, c, parity);
-            const uint64_t *k0 = p.key + (static_cast<size_t>(j * 2) * p.K + mod) * N + d0;
-            const uint64_t *k1 = k0 + static_cast<size_t>(p.K) * N;
+            const uint64_t *k0, *k1;
+            if constexpr (MP::two_pass)
+            {
+                mbar_wait(bar + 2, j & 1);
+                k0 = st_key + tid * 8;
+                k1 = k0 + MP::TILE;
+            }
+            else
+            {
+                k0 = p.key + (static_cast<size_t>(j * 2) * p.K + mod) * N + d0;
+                k1 = k0 + static_cast<size_t>(p.K) * N;
+            }
 #pragma unroll
             for (int r = 0; r < 4; r++)
             {
-                const ulonglong2 u = __ldg(reinterpret_cast<const ulonglong2 *>(k0) + r);
-                const ulonglong2 v = __ldg(reinterpret_cast<const ulonglong2 *>(k1) + r);
+                const ulonglong2 u = reinterpret_cast<const ulonglong2 *>(k0)[r];
+                const ulonglong2 v = reinterpret_cast<const ulonglong2 *>(k1)[r];
                 mac128(lo[0][2 * r], hi[0][2 * r], x[2 * r], u.x);
                 mac128(lo[0][2 * r + 1], hi[0][2 * r + 1], x[2 * r + 1], u.y);
                 mac128(lo[1][2 * r], hi[1][2 * r], x[2 * r], v.x);

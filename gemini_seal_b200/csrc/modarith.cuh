@@ -155,8 +155,39 @@ namespace gsb
     // FMAU128 (multi_special_primes.cpp:22-27): (lo,hi) += a*b as an exact 128-bit accumulate.
     GSB_DEV void mac128(uint64_t &lo, uint64_t &hi, uint64_t a, uint64_t b)
     {
+#ifdef GSB_CUSIM
         uint64_t pl = a * b, ph = mulhi(a, b);
         lo += pl;
         hi += ph + (lo < pl ? 1 : 0);
+#else
+        // four 32x32 products; the two aligned ones ride the 64-bit carry chain, the two middle ones
+        // are added word-wise (adds on the ALU pipe; the multiplier pipe bounds this kernel)
+        asm("{\n"
+            ".reg .u32 a0, a1, b0, b1, l0, l1, h0, h1, m0, m1;\n"
+            ".reg .u64 p;\n"
+            "mov.b64 {a0, a1}, %2;\n"
+            "mov.b64 {b0, b1}, %3;\n"
+            "mul.wide.u32 p, a0, b0;\n"
+            "add.cc.u64 %0, %0, p;\n"
+            "mul.wide.u32 p, a1, b1;\n"
+            "addc.u64 %1, %1, p;\n"
+            "mov.b64 {l0, l1}, %0;\n"
+            "mov.b64 {h0, h1}, %1;\n"
+            "mul.wide.u32 p, a0, b1;\n"
+            "mov.b64 {m0, m1}, p;\n"
+            "add.cc.u32 l1, l1, m0;\n"
+            "addc.cc.u32 h0, h0, m1;\n"
+            "addc.u32 h1, h1, 0;\n"
+            "mul.wide.u32 p, a1, b0;\n"
+            "mov.b64 {m0, m1}, p;\n"
+            "add.cc.u32 l1, l1, m0;\n"
+            "addc.cc.u32 h0, h0, m1;\n"
+            "addc.u32 h1, h1, 0;\n"
+            "mov.b64 %0, {l0, l1};\n"
+            "mov.b64 %1, {h0, h1};\n"
+            "}"
+            : "+l"(lo), "+l"(hi)
+            : "l"(a), "l"(b));
+#endif
     }
 } // namespace gsb

@@ -8,6 +8,13 @@
 #pragma once
 #include "ntt_core.cuh"
 
+#ifndef GSB_PREFETCH
+#define GSB_PREFETCH 1
+#endif
+#ifndef GSB_TILE_MIN_CTAS
+#define GSB_TILE_MIN_CTAS 2
+#endif
+
 namespace gsb
 {
     enum : int
@@ -108,7 +115,7 @@ namespace gsb
     };
 
     template <bool INVERSE, int T_LOG, int G_HI, int G_LO, bool LAST, int A, class IO>
-    __global__ void __launch_bounds__(1 << T_LOG) ntt_tile_kernel(IO io, NttTables tab, ModMap mm, int nz, int zb)
+    __global__ void __launch_bounds__(1 << T_LOG, T_LOG <= 8 ? GSB_TILE_MIN_CTAS : 1) ntt_tile_kernel(IO io, NttTables tab, ModMap mm, int nz, int zb)
     {
         typedef TilePlan<T_LOG, G_HI, A> TP;
         const int y = blockIdx.y, mod = mm.mod(y);
@@ -146,17 +153,26 @@ namespace gsb
                 int zn = z + 1;
                 while (zn < z1 && io.skip(y, zn))
                     zn++;
+#if GSB_PREFETCH
                 if (zn < z1)
                 {
                     const typename IO::Pro pro(io, y, zn, mod, c, N);
                     xf_load_raw<T_LOG, G_HI, G_LO, INVERSE>(xn, tid, tile, map, pro);
                 }
+#endif
                 if constexpr (INVERSE)
                     inv_compute<T_LOG, G_HI, G_LO, LAST, 0>(x, smem, tid, tw, c, parity);
                 else
                     fwd_compute<T_LOG, G_HI, G_LO, LAST, 0>(x, smem, tid, tw, c, parity);
                 const typename IO::Epi epi(io, y, z, mod, c, N);
                 xf_store<T_LOG, G_HI, G_LO, INVERSE>(x, tid, tile, map, epi);
+#if !GSB_PREFETCH
+                if (zn < z1)
+                {
+                    const typename IO::Pro pro(io, y, zn, mod, c, N);
+                    xf_load_raw<T_LOG, G_HI, G_LO, INVERSE>(xn, tid, tile, map, pro);
+                }
+#endif
                 z = zn;
             }
         };
