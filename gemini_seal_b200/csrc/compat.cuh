@@ -67,6 +67,7 @@ namespace gsb
     {
         __syncthreads();
     }
+    GSB_DEV void fence_proxy_async() {}
 #else
     GSB_DEV uint32_t smem_u32(const void *p)
     {
@@ -86,6 +87,11 @@ namespace gsb
         asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
                      "l"(src), "r"(bytes), "r"(smem_u32(bar))
                      : "memory");
+    }
+    // orders this thread's generic-proxy shared-memory accesses with later async-proxy (bulk copy) ones
+    GSB_DEV void fence_proxy_async()
+    {
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     }
     GSB_DEV void mbar_wait(uint64_t *bar, uint32_t parity)
     {

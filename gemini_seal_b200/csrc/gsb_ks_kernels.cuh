@@ -465,7 +465,10 @@ namespace gsb
                 else
                     xf_load_raw<T, MP::G_HI, 0, false>(x, tid, 0, map, StagedPro{ st_op });
                 // every thread holds its operand words and is past the previous bundle's key reads:
-                // both staging areas may be refilled while the butterflies run
+                // both staging areas may be refilled while the butterflies run.  The refill is an
+                // async-proxy write after generic-proxy reads of the same bytes, which only a proxy
+                // fence orders (without it a late LDS occasionally saw the next bundle's tile).
+                fence_proxy_async();
                 __syncthreads();
                 if (tid == 0)
                 {
