@@ -112,6 +112,25 @@ def algorithmic_bytes(label, B):
     return limbs.get(label, 0) * LIMB_BYTES
 
 
+# forward butterfly stages each (bundle, ext slot) pair goes through in the two key-switch kernels at N = 2^15
+BUTTERFLY_STAGES = {"ks_mac": 9, "fwd_cols/modup": 6}
+
+
+def ncu_traffic(label, batch_per_launch):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of `label` from the committed ncu --set full
+    capture (profiles/r1_ncu_traffic.json, written by scripts/ncu_traffic.py), or None when that capture was
+    taken at another batch per launch."""
+    path = os.path.join(ROOT, "profiles", "r1_ncu_traffic.json")
+    if not os.path.exists(path):
+        return None
+    with open(path) as f:
+        t = json.load(f)
+    k = t.get("kernels", {}).get(label)
+    if not k or k.get("batch_per_launch") != batch_per_launch:
+        return None
+    return k["dram_bytes_per_launch"]
+
+
 def measured_peaks():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(path):
@@ -320,7 +339,16 @@ def run_ours(args):
         top = max(kernels, key=lambda x: kernels[x]["ms"])
         achieved = kernels[top]["algorithmic_gbs"]
         roofline = {"bound": "hbm", "kernel": top, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                    "traffic": None, "peak_source": how, "kernel_share_of_step": kernels[top]["share"]}
+                    "traffic": ncu_traffic(top, B // kernels[top]["launches"]), "peak_source": how,
+                    "kernel_share_of_step": kernels[top]["share"]}
+        # the binding limit of these kernels is the integer multiplier pipe, not HBM: report the
+        # butterfly rate of the dominant kernel against the register-resident butterfly peak measured now
+        bf = C.c_double()
+        if lib.gsb_int_peak(ctx.handle, 2, None, None, C.byref(bf)) == 0 and top in BUTTERFLY_STAGES:
+            per_s = B * (L * (L + K_SPECIAL) - L) * BUTTERFLY_STAGES[top] * (N // 2) / (kernels[top]["ms"] * 1e-3)
+            roofline["int_pipe"] = {"achieved": per_s / 1e9, "peak": bf.value / 1e9, "unit": "G butterflies/s",
+                                    "frac": per_s / bf.value,
+                                    "peak_source": "gsb_int_peak: register-resident Harvey butterflies, 2 CTAs x 256 threads per SM"}
 
     # ---- CPU baseline on this box's host cores (rank 0, N = 1 only)
     cpu = None
