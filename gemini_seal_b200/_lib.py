@@ -10,6 +10,7 @@ import os
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "_C", "libgseal_b200.so")
 
+u64 = C.c_uint64
 u64p = C.POINTER(C.c_uint64)
 vp = C.c_void_p
 sz = C.c_size_t
@@ -57,6 +58,13 @@ PROTOTYPES = {
     "gsb_rescale_host": (i32, [vp, vp, vp, sz, sz, sz]),
     "gsb_apply_galois_host": (i32, [vp, u32, vp, vp, sz, sz]),
     "gsb_mul_relin_rescale_host": (i32, [vp, vp, vp, vp, sz, sz]),
+    "gsb_bfv_multiply_dev": (i32, [vp, vp, u64, vp, vp, vp, sz, sz, vp]),
+    "gsb_bfv_multiply_host": (i32, [vp, u64, vp, vp, vp, sz, sz]),
+    "gsb_bfv_aux_base": (i32, [vp, sz, u64, u64p, sz, C.POINTER(sz)]),
+    "gsb_bfv_relinearize_dev": (i32, [vp, vp, vp, vp, sz, sz, vp]),
+    "gsb_bfv_apply_galois_dev": (i32, [vp, vp, u32, vp, vp, sz, sz, vp]),
+    "gsb_bfv_relinearize_host": (i32, [vp, vp, vp, sz, sz]),
+    "gsb_bfv_apply_galois_host": (i32, [vp, u32, vp, vp, sz, sz]),
     "gsb_int_peak": (i32, [vp, i32, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double)]),
 }
 # measurement aids that the test-only simulator build does not provide

@@ -267,6 +267,13 @@ void gsb_ctx_destroy(gsb_ctx *ctx)
         cudaFree(kv.second.d);
     for (auto &kv : ctx->galois_tables)
         cudaFree(kv.second);
+    for (auto &kv : ctx->bfv_tools)
+    {
+        cudaFree(kv.second.d_WW);
+        cudaFree(kv.second.d_VV);
+        cudaFree(kv.second.d_limb);
+        cudaFree(kv.second.d_consts);
+    }
     cudaFree(ctx->default_ws.buf);
     cudaFree(ctx->host_io.buf);
     if (ctx->pipe_ready)

@@ -5,6 +5,7 @@
 #include "../../include/gseal_b200.h"
 #include "host_tables.h"
 #include "ntt_kernels.cuh"
+#include "gsb_bfv_kernels.cuh"
 #include <functional>
 #include <map>
 #include <mutex>
@@ -53,6 +54,18 @@ namespace gsb
         uint64_t *d_neg_half = nullptr;  // [L-1]
     };
 
+    // Device side of the RNSTool of one (level L, plain modulus t) pair: NTT tables over the extended
+    // base q u Bsk and the BEHZ conversion constants (util/rns.cpp:540-728).
+    struct BfvTool
+    {
+        size_t L = 0, nB = 0, nBsk = 0;
+        std::vector<uint64_t> bsk;
+        Twiddle *d_WW = nullptr, *d_VV = nullptr;
+        LimbC *d_limb = nullptr;
+        uint64_t *d_consts = nullptr; // one allocation, carved up by `dev`
+        BehzDev dev{};
+    };
+
     struct SwitchKey
     {
         uint64_t *d = nullptr; // [beta0][2][K][N]
@@ -83,6 +96,7 @@ struct gsb_ctx
     std::map<uint32_t, gsb::SwitchKey> relin; // RelinKeys::get_index(key_power) -> key
     std::map<uint32_t, gsb::SwitchKey> galois;
     std::map<uint32_t, uint32_t *> galois_tables; // device permutation tables per element
+    std::map<std::pair<size_t, uint64_t>, gsb::BfvTool> bfv_tools; // (L, plain modulus) -> BEHZ tool
     std::mutex mu;      // guards the lazily built maps below
     std::mutex host_mu; // serialises the *_host entry points (they share host_io / default_ws)
     gsb_ws default_ws;  // compute scratch for callers that pass ws = NULL
@@ -97,4 +111,5 @@ struct gsb_ctx
     }
     const gsb::KsLevelConsts &consts_for(size_t L);
     const uint32_t *galois_table(uint32_t elt);
+    const gsb::BfvTool &bfv_tool(size_t L, uint64_t plain_modulus);
 };

@@ -124,6 +124,75 @@ const gsb::KsLevelConsts &gsb_ctx::consts_for(size_t L)
     return level_consts.emplace(L, c).first->second;
 }
 
+const gsb::BfvTool &gsb_ctx::bfv_tool(size_t L, uint64_t plain_modulus)
+{
+    using namespace gsb;
+    std::lock_guard<std::mutex> lock(mu);
+    const auto key = std::make_pair(L, plain_modulus);
+    auto it = bfv_tools.find(key);
+    if (it != bfv_tools.end())
+        return it->second;
+    require(L >= 1 && L <= L0, GSB_E_INVALID_ARG, "no ciphertext level with that many limbs");
+    // context.cpp:178-186: plain_modulus must be smaller than every coeff modulus prime, at least 2
+    require(plain_modulus >= 2 && (plain_modulus >> 59) == 0, GSB_E_INVALID_ARG, "plain_modulus out of range");
+    std::vector<uint64_t> q(L);
+    for (size_t i = 0; i < L; i++)
+        q[i] = tables[i].mod.q;
+    host::BehzConsts bc;
+    require(host::build_behz(logn, q.data(), L, plain_modulus, bc), GSB_E_LOGIC, "invalid rns bases");
+    const size_t M = L + bc.nBsk;
+    require(M <= BEHZ_MAX, GSB_E_LOGIC, "invalid rns bases");
+    std::vector<Twiddle> ww(M * N), vv(M * N);
+    std::vector<LimbC> limb(M);
+    for (size_t i = 0; i < M; i++)
+    {
+        host::LimbTables aux;
+        if (i >= L)
+            require(host::build_limb_tables(logn, bc.bsk[i - L], aux), GSB_E_LOGIC, "invalid rns bases");
+        const host::LimbTables &t = i < L ? tables[i] : aux;
+        for (size_t d = 0; d < N; d++)
+        {
+            ww[i * N + d] = make_ulonglong2(t.w[d], t.ws[d]);
+            vv[i * N + d] = make_ulonglong2(t.v[d], t.vs[d]);
+        }
+        LimbC c;
+        c.q = t.mod.q;
+        c.two_q = t.mod.q << 1;
+        c.rdp = t.rdp;
+        c.cr0 = t.mod.cr0;
+        c.cr1 = t.mod.cr1;
+        c.inv_n = t.inv_n;
+        c.inv_n_s = t.inv_n_s;
+        c.pad = 0;
+        limb[i] = c;
+    }
+    BfvTool tool;
+    tool.L = L;
+    tool.nB = bc.nB;
+    tool.nBsk = bc.nBsk;
+    tool.bsk = bc.bsk;
+    GSB_CUDA_CHECK(cudaMalloc(reinterpret_cast<void **>(&tool.d_WW), ww.size() * sizeof(Twiddle)));
+    GSB_CUDA_CHECK(cudaMalloc(reinterpret_cast<void **>(&tool.d_VV), vv.size() * sizeof(Twiddle)));
+    GSB_CUDA_CHECK(cudaMalloc(reinterpret_cast<void **>(&tool.d_limb), limb.size() * sizeof(LimbC)));
+    GSB_CUDA_CHECK(cudaMemcpy(tool.d_WW, ww.data(), ww.size() * sizeof(Twiddle), cudaMemcpyHostToDevice));
+    GSB_CUDA_CHECK(cudaMemcpy(tool.d_VV, vv.data(), vv.size() * sizeof(Twiddle), cudaMemcpyHostToDevice));
+    GSB_CUDA_CHECK(cudaMemcpy(tool.d_limb, limb.data(), limb.size() * sizeof(LimbC), cudaMemcpyHostToDevice));
+    std::vector<uint64_t> all;
+    auto put = [&](const std::vector<uint64_t> &v) {
+        const size_t off = all.size();
+        all.insert(all.end(), v.begin(), v.end());
+        return off;
+    };
+    const size_t o1 = put(bc.inv_punct_q), o2 = put(bc.mat_q), o3 = put(bc.inv_punct_b), o4 = put(bc.mat_b),
+                 o5 = put(bc.prod_q_mod_bsk), o6 = put(bc.inv_prod_q_mod_bsk), o7 = put(bc.inv_mtilde_mod_bsk), o8 = put(bc.prod_b_mod_q);
+    tool.d_consts = upload_words(all);
+    tool.dev = BehzDev{ tool.d_limb, tool.d_consts + o1, tool.d_consts + o2, tool.d_consts + o3, tool.d_consts + o4,
+                        tool.d_consts + o5, tool.d_consts + o6, tool.d_consts + o7, tool.d_consts + o8,
+                        bc.inv_prod_q_mod_mtilde, bc.inv_prod_b_mod_msk, plain_modulus,
+                        static_cast<uint32_t>(L), static_cast<uint32_t>(bc.nB), static_cast<uint32_t>(bc.nBsk), static_cast<uint32_t>(N) };
+    return bfv_tools.emplace(key, std::move(tool)).first->second;
+}
+
 const uint32_t *gsb_ctx::galois_table(uint32_t elt)
 {
     using namespace gsb;
@@ -197,6 +266,8 @@ namespace gsb
         uint64_t *dst;
         size_t dst_bs, dst_ls;
         const uint32_t *table;
+        bool zero_l1 = false; // component 1 gets no addend (set with a Galois table, or for BFV Galois)
+        bool bfv = false;     // BFV branch: coefficient-form target and result (is_ckks == false)
     };
 
     // switch_key_inplace for `B` ciphertexts (evaluator.cpp:2259-2368).  scratch must hold
@@ -219,8 +290,14 @@ namespace gsb
         uint64_t *tmp = two ? ar.words(B * 2 * L * N) : nullptr;
         const int iB = static_cast<int>(B), iL = static_cast<int>(L), iE = static_cast<int>(E);
 
-        // Step 1 (:2302-2307): strict inverse NTT of every target limb (all bundles at once).
-        ntt_inverse_plain<LOGN>(tab, ModMap{ 1 << 30, 0, 0 }, target, target_stride, coef, L * N, iL, iB, false, st, "ks_target");
+        // Step 1 (:2302-2307): strict inverse NTT of every target limb (all bundles at once); a BFV
+        // target is in coefficient form already and is only gathered into the batch-dense layout.
+        if (o.bfv)
+            GSB_CUDA_CHECK(cudaMemcpy2DAsync(
+                coef, L * N * sizeof(uint64_t), target, target_stride * sizeof(uint64_t), L * N * sizeof(uint64_t), B,
+                cudaMemcpyDeviceToDevice, st));
+        else
+            ntt_inverse_plain<LOGN>(tab, ModMap{ 1 << 30, 0, 0 }, target, target_stride, coef, L * N, iL, iB, false, st, "ks_target");
 
         // Step 2 + first NTT pass of step 3 (:2310, :2322): mod-up fused into the column pass.
         if constexpr (two)
@@ -243,9 +320,26 @@ namespace gsb
             static_cast<int>(2 * B), true, st, "ks_special");
         // Step 5 (mod-down) + final add (:2360-2366).
         const MdLoadArgs la{ ks, red };
-        const MdStoreArgs sa{ ks, red, o.add_src, o.add_bs, o.add_ls, o.dst, o.dst_bs, o.dst_ls, o.table };
+        const MdStoreArgs sa{ ks, red, o.add_src, o.add_bs, o.add_ls, o.dst, o.dst_bs, o.dst_ls, o.table, o.zero_l1 || o.table != nullptr };
         const ModMap mm{ 1 << 30, 0, 0 };
-        if constexpr (two)
+        if (o.bfv)
+        {
+            // multi_special_primes.cpp:287-289: the accumulated c_i goes back to coefficient form
+            // (lazy inverse NTT) and the correction is added there.
+            const MdStoreBfvArgs ba{ la, sa };
+            if constexpr (two)
+            {
+                launch_inv_contig<LOGN>(IoPlain<OUT_RAW>{ red, tmp, E * N, L * N }, tab, mm, iL, static_cast<int>(2 * B), st, "moddown_bfv");
+                IoPair<PlainLoad, MdStoreBfv> io2{ PlainArgs{ tmp, L * N }, ba };
+                launch_inv_cols<LOGN>(io2, tab, mm, iL, static_cast<int>(2 * B), st, "moddown_bfv");
+            }
+            else
+            {
+                IoPair<PlainLoad, MdStoreBfv> io{ PlainArgs{ red, E * N }, ba };
+                launch_inv_contig<LOGN>(io, tab, mm, iL, static_cast<int>(2 * B), st, "moddown_bfv");
+            }
+        }
+        else if constexpr (two)
         {
             IoPair<MdLoadT<K1>, PlainStore<OUT_RAW>> io1{ la, PlainStoreArgs{ tmp, L * N } };
             launch_fwd_cols<LOGN>(io1, tab, mm, iL, static_cast<int>(2 * B), st, "moddown");
@@ -506,7 +600,7 @@ int gsb_switch_key_dev(
     });
 }
 
-int gsb_relinearize_dev(gsb_ctx *ctx, gsb_ws *ws, const uint64_t *in, uint64_t *out, size_t batch, size_t L, void *stream)
+static int relinearize_impl(gsb_ctx *ctx, gsb_ws *ws, const uint64_t *in, uint64_t *out, size_t batch, size_t L, void *stream, bool bfv)
 {
     return guarded([&] {
         check_batch(ctx, batch, L, 1);
@@ -520,8 +614,83 @@ int gsb_relinearize_dev(gsb_ctx *ctx, gsb_ws *ws, const uint64_t *in, uint64_t *
         {
             const size_t B = std::min(chunk, batch - b0);
             const uint64_t *i3 = in + b0 * 3 * LN;
-            const KsOutput o{ i3, 3 * LN, LN, out + b0 * 2 * LN, 2 * LN, LN, nullptr };
+            const KsOutput o{ i3, 3 * LN, LN, out + b0 * 2 * LN, 2 * LN, LN, nullptr, false, bfv };
             GSB_DISPATCH_LOGN(ctx->logn, switch_key_core<LOGN>(ctx, scratch, i3 + 2 * LN, 3 * LN, key, o, B, L, st));
+        }
+        GSB_CUDA_CHECK(cudaGetLastError());
+    });
+}
+
+int gsb_relinearize_dev(gsb_ctx *ctx, gsb_ws *ws, const uint64_t *in, uint64_t *out, size_t batch, size_t L, void *stream)
+{
+    return relinearize_impl(ctx, ws, in, out, batch, L, stream, false);
+}
+
+int gsb_bfv_relinearize_dev(gsb_ctx *ctx, gsb_ws *ws, const uint64_t *in, uint64_t *out, size_t batch, size_t L, void *stream)
+{
+    return relinearize_impl(ctx, ws, in, out, batch, L, stream, true);
+}
+
+int gsb_bfv_multiply_dev(
+    gsb_ctx *ctx, gsb_ws *ws, uint64_t plain_modulus, const uint64_t *a, const uint64_t *b, uint64_t *out, size_t batch, size_t L, void *stream)
+{
+    return guarded([&] {
+        check_batch(ctx, batch, L, 1);
+        require(a && b && out, GSB_E_INVALID_ARG, "null operand");
+        GSB_CUDA_CHECK(cudaSetDevice(ctx->device));
+        const BfvTool &tool = ctx->bfv_tool(L, plain_modulus);
+        gsb_ws *w = pick_ws(ctx, ws);
+        cudaStream_t st = static_cast<cudaStream_t>(stream);
+        const size_t N = ctx->N, M = L + tool.nBsk, LN = L * N, MN = M * N;
+        const size_t per = 4 * MN + 3 * MN, chunk = chunk_for(per, batch);
+        void *scratch = w->reserve((chunk * per + 1024) * sizeof(uint64_t));
+        const NttTables tab{ tool.d_WW, tool.d_VV, tool.d_limb, static_cast<uint32_t>(N), ctx->logn };
+        const ModMap mm{ 1 << 30, 0, 0 };
+        for (size_t b0 = 0; b0 < batch; b0 += chunk)
+        {
+            const size_t B = std::min(chunk, batch - b0);
+            Arena ar(scratch);
+            uint64_t *ext = ar.words(4 * B * MN); // [2 operands][B][2][M][N]
+            uint64_t *dest = ar.words(3 * B * MN); // [B][3][M][N]
+            // (1)-(2): lift both operands to q u Bsk; (3): lazy NTT of every limb of every polynomial
+            const size_t lift = 2 * B * N;
+            GSB_LAUNCH("behz_lift", "", behz_lift_kernel, dim3(grid_for(lift, 256)), dim3(256), 0, st, tool.dev, a + b0 * 2 * LN, ext, lift);
+            GSB_LAUNCH("behz_lift", "", behz_lift_kernel, dim3(grid_for(lift, 256)), dim3(256), 0, st, tool.dev, b + b0 * 2 * LN, ext + 2 * B * MN, lift);
+            GSB_DISPATCH_LOGN(ctx->logn, ntt_forward_plain<LOGN>(tab, mm, ext, MN, ext, MN, static_cast<int>(M), static_cast<int>(4 * B), true, st, "bfv"));
+            // (4): the size-2 x size-2 tensor product over all M limbs (same dyadic + add arithmetic as CKKS)
+            CkksMulArgs p{ ext, ext + 2 * B * MN, dest, tool.d_limb, static_cast<uint32_t>(N), static_cast<uint32_t>(M), B * MN / 2 };
+            GSB_LAUNCH("bfv_tensor", "", ckks_multiply_kernel, dim3(grid_for(p.pairs, 256)), dim3(256), 0, st, p);
+            // (5): strict inverse NTT
+            GSB_DISPATCH_LOGN(ctx->logn, ntt_inverse_plain<LOGN>(tab, mm, dest, MN, dest, MN, static_cast<int>(M), static_cast<int>(3 * B), false, st, "bfv"));
+            // (6)-(8): times t, divide by q and floor into Bsk, Shenoy-Kumaresan back to q
+            const size_t fl = 3 * B * N;
+            GSB_LAUNCH("behz_floor", "", behz_floor_kernel, dim3(grid_for(fl, 256)), dim3(256), 0, st, tool.dev, dest, out + b0 * 3 * LN, fl);
+        }
+        GSB_CUDA_CHECK(cudaGetLastError());
+    });
+}
+
+int gsb_bfv_apply_galois_dev(gsb_ctx *ctx, gsb_ws *ws, uint32_t galois_elt, const uint64_t *in, uint64_t *out, size_t batch, size_t L, void *stream)
+{
+    return guarded([&] {
+        check_batch(ctx, batch, L, 1);
+        require(in && out, GSB_E_INVALID_ARG, "null operand");
+        require((galois_elt & 1u) && galois_elt < 2u * ctx->N, GSB_E_INVALID_ARG, "Galois element is not valid");
+        const SwitchKey &key = find_key(ctx, GSB_KEY_GALOIS, galois_elt);
+        gsb_ws *w = pick_ws(ctx, ws);
+        cudaStream_t st = static_cast<cudaStream_t>(stream);
+        const size_t N = ctx->N, LN = L * N, per = ks_words_per_ct(ctx, L) + 2 * LN, chunk = chunk_for(per, batch);
+        char *scratch = static_cast<char *>(w->reserve((chunk * per + 1024) * sizeof(uint64_t)));
+        for (size_t b0 = 0; b0 < batch; b0 += chunk)
+        {
+            const size_t B = std::min(chunk, batch - b0);
+            // evaluator.cpp:1893-1904: both components through the coefficient-form automorphism; the
+            // permuted c1 is the key-switch target, the permuted c0 the addend of component 0.
+            uint64_t *perm = reinterpret_cast<uint64_t *>(scratch);
+            GaloisCoeffArgs p{ in + b0 * 2 * LN, LN, perm, ctx->d_limb, galois_elt, static_cast<uint32_t>(N), static_cast<uint32_t>(L), ctx->logn, B * 2 * LN };
+            GSB_LAUNCH("galois_coeff", "", galois_coeff_kernel, dim3(grid_for(p.total, 256)), dim3(256), 0, st, p);
+            const KsOutput o{ perm, 2 * LN, LN, out + b0 * 2 * LN, 2 * LN, LN, nullptr, true, true };
+            GSB_DISPATCH_LOGN(ctx->logn, switch_key_core<LOGN>(ctx, scratch + B * 2 * LN * sizeof(uint64_t), perm + LN, 2 * LN, key, o, B, L, st));
         }
         GSB_CUDA_CHECK(cudaGetLastError());
     });
@@ -680,6 +849,43 @@ int gsb_apply_galois_host(gsb_ctx *ctx, uint32_t galois_elt, const uint64_t *in,
     const size_t w = ctx ? L * ctx->N : 0;
     return host_call(ctx, in, 2 * w, nullptr, 0, out, 2 * w, batch, [&](gsb_ws *ws, uint64_t *di, uint64_t *, uint64_t *dout, size_t B, void *st) {
         return gsb_apply_galois_dev(ctx, ws, galois_elt, di, dout, B, L, st);
+    });
+}
+
+int gsb_bfv_multiply_host(gsb_ctx *ctx, uint64_t plain_modulus, const uint64_t *a, const uint64_t *b, uint64_t *out, size_t batch, size_t L)
+{
+    const size_t w = ctx ? L * ctx->N : 0;
+    return host_call(ctx, a, 2 * w, b, 2 * w, out, 3 * w, batch, [&](gsb_ws *ws, uint64_t *da, uint64_t *db, uint64_t *dout, size_t B, void *st) {
+        return gsb_bfv_multiply_dev(ctx, ws, plain_modulus, da, db, dout, B, L, st);
+    });
+}
+
+int gsb_bfv_aux_base(gsb_ctx *ctx, size_t L, uint64_t plain_modulus, uint64_t *moduli_out, size_t cap, size_t *n_out)
+{
+    return guarded([&] {
+        require(ctx != nullptr && moduli_out != nullptr && n_out != nullptr, GSB_E_INVALID_ARG, "null argument");
+        GSB_CUDA_CHECK(cudaSetDevice(ctx->device));
+        const BfvTool &tool = ctx->bfv_tool(L, plain_modulus);
+        require(cap >= tool.bsk.size(), GSB_E_RANGE, "output too small");
+        for (size_t i = 0; i < tool.bsk.size(); i++)
+            moduli_out[i] = tool.bsk[i];
+        *n_out = tool.bsk.size();
+    });
+}
+
+int gsb_bfv_relinearize_host(gsb_ctx *ctx, const uint64_t *in, uint64_t *out, size_t batch, size_t L)
+{
+    const size_t w = ctx ? L * ctx->N : 0;
+    return host_call(ctx, in, 3 * w, nullptr, 0, out, 2 * w, batch, [&](gsb_ws *ws, uint64_t *di, uint64_t *, uint64_t *dout, size_t B, void *st) {
+        return gsb_bfv_relinearize_dev(ctx, ws, di, dout, B, L, st);
+    });
+}
+
+int gsb_bfv_apply_galois_host(gsb_ctx *ctx, uint32_t galois_elt, const uint64_t *in, uint64_t *out, size_t batch, size_t L)
+{
+    const size_t w = ctx ? L * ctx->N : 0;
+    return host_call(ctx, in, 2 * w, nullptr, 0, out, 2 * w, batch, [&](gsb_ws *ws, uint64_t *di, uint64_t *, uint64_t *dout, size_t B, void *st) {
+        return gsb_bfv_apply_galois_dev(ctx, ws, galois_elt, di, dout, B, L, st);
     });
 }
 

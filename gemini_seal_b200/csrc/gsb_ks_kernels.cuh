@@ -217,7 +217,8 @@ namespace gsb
         size_t add_bs, add_ls; // word strides: ciphertext, component
         uint64_t *dst;
         size_t dst_bs, dst_ls;
-        const uint32_t *table; // nullptr unless Galois
+        const uint32_t *table; // nullptr unless (NTT-form) Galois
+        bool zero_l1;          // component 1 has no addend (apply_galois_inplace wipes it, :1928)
     };
     struct MdStore
     {
@@ -233,22 +234,47 @@ namespace gsb
             r = a.red + (static_cast<size_t>(z) * a.ks.E + y) * N;
             o = a.dst + static_cast<size_t>(b) * a.dst_bs + static_cast<size_t>(l) * a.dst_ls + static_cast<size_t>(y) * N;
             table = a.table;
-            s = (a.table && l == 1) ? nullptr
-                                    : a.add_src + static_cast<size_t>(b) * a.add_bs + static_cast<size_t>(l) * a.add_ls + static_cast<size_t>(y) * N;
+            s = (a.zero_l1 && l == 1) ? nullptr
+                                      : a.add_src + static_cast<size_t>(b) * a.add_bs + static_cast<size_t>(l) * a.add_ls + static_cast<size_t>(y) * N;
             q = c.q;
             ip = a.ks.inv_p[2 * y];
             ips = a.ks.inv_p[2 * y + 1];
         }
-        GSB_DEV uint64_t one(uint32_t d, uint64_t v) const
+        GSB_DEV uint64_t fin(uint32_t d, uint64_t sum) const
         {
-            const uint64_t val = mulmod_shoup(r[d] + v, ip, ips, q);
+            const uint64_t val = mulmod_shoup(sum, ip, ips, q);
             const uint64_t addend = s ? (table ? s[__ldg(table + d)] : s[d]) : 0;
             return add_mod(val, addend, q);
         }
+        GSB_DEV uint64_t one(uint32_t d, uint64_t v) const { return fin(d, r[d] + v); }
         GSB_DEV void store(uint32_t d, uint64_t v, int) const { o[d] = one(d, v); }
         GSB_DEV void store2(uint32_t d, uint64_t a, uint64_t b, int) const
         {
             *reinterpret_cast<ulonglong2 *>(o + d) = make_ulonglong2(one(d, a), one(d + 1, b));
+        }
+    };
+
+    // ---- BFV mod-down epilogue (multi_special_primes.cpp:287-302 with is_ckks == false) -------------
+    // The transform is the lazy INVERSE NTT of red[z][i] (:288); the correction term of steps 1-2 stays in
+    // coefficient form and is computed here from the special slots: val = MulModShoup(c_i + temp; P^-1).
+    struct MdStoreBfvArgs
+    {
+        MdLoadArgs la;
+        MdStoreArgs sa;
+    };
+    struct MdStoreBfv
+    {
+        typedef MdStoreBfvArgs Args;
+        MdLoadT<false> ml;
+        MdStore ms;
+        GSB_DEV MdStoreBfv(const Args &a, int y, int z, int mod, const LimbC &c, uint32_t N)
+            : ml(a.la, y, z, mod, c, N), ms(a.sa, y, z, mod, c, N)
+        {}
+        GSB_DEV uint64_t one(uint32_t d, uint64_t v) const { return ms.fin(d, v + ml.xform(ml.raw(d))); }
+        GSB_DEV void store(uint32_t d, uint64_t v, int) const { ms.o[d] = one(d, v); }
+        GSB_DEV void store2(uint32_t d, uint64_t a, uint64_t b, int) const
+        {
+            *reinterpret_cast<ulonglong2 *>(ms.o + d) = make_ulonglong2(one(d, a), one(d + 1, b));
         }
     };
 
@@ -529,6 +555,36 @@ namespace gsb
             for (int r = 0; r < 8; r += 2)
                 *reinterpret_cast<ulonglong2 *>(o + r) = make_ulonglong2(
                     barrett128(lo[l][r], hi[l][r], c.q, c.cr0, c.cr1), barrett128(lo[l][r + 1], hi[l][r + 1], c.q, c.cr0, c.cr1));
+        }
+    }
+
+    // ---- GaloisTool::apply_galois, coefficient form (util/galois.cpp:144-186) ------------------------
+    // in = [n][L][N] at in + p*in_zs -> out [n][L][N]: out[(i*elt) mod N] = +-in[i], negated when
+    // bit logN of i*elt is set.
+    struct GaloisCoeffArgs
+    {
+        const uint64_t *in;
+        size_t in_zs;
+        uint64_t *out;
+        const LimbC *limb;
+        uint32_t elt, N, L;
+        int logn;
+        size_t total; // n*L*N
+    };
+
+    __global__ void __launch_bounds__(256) galois_coeff_kernel(GaloisCoeffArgs p)
+    {
+        const size_t LN = static_cast<size_t>(p.L) * p.N;
+        for (size_t t = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; t < p.total;
+             t += static_cast<size_t>(gridDim.x) * blockDim.x)
+        {
+            const size_t poly = t / LN, rem = t - poly * LN;
+            const uint32_t limb = static_cast<uint32_t>(rem / p.N), i = static_cast<uint32_t>(rem - static_cast<size_t>(limb) * p.N);
+            const uint64_t raw = static_cast<uint64_t>(i) * p.elt;
+            uint64_t v = p.in[poly * p.in_zs + rem];
+            if ((raw >> p.logn) & 1)
+                v = neg_mod(v, p.limb[limb].q);
+            p.out[poly * LN + static_cast<size_t>(limb) * p.N + (raw & (p.N - 1))] = v;
         }
     }
 

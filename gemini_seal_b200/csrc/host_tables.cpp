@@ -197,5 +197,131 @@ namespace gsb
                 e = (e * 5u) & (m - 1); // GaloisTool::generator_ = 5 (util/galois.h:169)
             return static_cast<uint32_t>(e);
         }
+        // ---- BEHZ auxiliary base and constants (util/rns.cpp:540-728, util/numth.cpp:179-322) ---------
+        static uint64_t mulmod128(uint64_t a, uint64_t b, uint64_t m)
+        {
+            return static_cast<uint64_t>((static_cast<u128>(a) * b) % m);
+        }
+
+        // Primality of a 64-bit integer; the reference's Miller-Rabin draws random bases
+        // (numth.cpp:253-274), the answer does not depend on them.
+        static bool is_prime64(uint64_t n)
+        {
+            static const uint64_t bases[12] = { 2, 3, 5, 7, 11, 13, 17, 19, 23, 29, 31, 37 };
+            if (n < 2)
+                return false;
+            for (uint64_t b : bases)
+            {
+                if (n == b)
+                    return true;
+                if (n % b == 0)
+                    return false;
+            }
+            uint64_t d = n - 1;
+            int r = 0;
+            for (; !(d & 1); d >>= 1)
+                r++;
+            for (uint64_t b : bases)
+            {
+                uint64_t x = 1, base = b % n, e = d;
+                for (; e; e >>= 1, base = mulmod128(base, base, n))
+                    if (e & 1)
+                        x = mulmod128(x, base, n);
+                if (x == 1 || x == n - 1)
+                    continue;
+                bool witness = true;
+                for (int j = 1; j < r && witness; j++)
+                {
+                    x = mulmod128(x, x, n);
+                    witness = x != n - 1;
+                }
+                if (witness)
+                    return false;
+            }
+            return true;
+        }
+
+        // prod_{l in [0, n), l != skip} v[l] mod m  (skip = n: the whole product)
+        static uint64_t punctured(const std::vector<uint64_t> &v, size_t skip, uint64_t m)
+        {
+            uint64_t p = 1 % m;
+            for (size_t l = 0; l < v.size(); l++)
+                if (l != skip)
+                    p = mulmod128(p, v[l] % m, m);
+            return p;
+        }
+
+        bool build_behz(int logn, const uint64_t *q, size_t L, uint64_t t, BehzConsts &o)
+        {
+            const uint64_t n = uint64_t(1) << logn, m_tilde = uint64_t(1) << 32;
+            o = BehzConsts();
+            o.L = L;
+            o.t = t;
+            // |B| = |q|, one more when K*n*t*q^2 would not fit (rns.cpp:566-573); needs the bit length
+            // of prod(q): multiply it out word by word
+            std::vector<uint64_t> w(1, 1);
+            for (size_t i = 0; i < L; i++)
+            {
+                uint64_t carry = 0;
+                for (auto &x : w)
+                {
+                    const u128 z = static_cast<u128>(x) * q[i] + carry;
+                    x = static_cast<uint64_t>(z);
+                    carry = static_cast<uint64_t>(z >> 64);
+                }
+                if (carry)
+                    w.push_back(carry);
+            }
+            int q_bits = static_cast<int>(w.size() - 1) * 64, t_bits = 0;
+            for (uint64_t x = w.back(); x; x >>= 1)
+                q_bits++;
+            for (uint64_t x = t; x; x >>= 1)
+                t_bits++;
+            o.nB = L + ((32 + t_bits + q_bits >= 61 * static_cast<int>(L) + 61) ? 1 : 0);
+            o.nBsk = o.nB + 1;
+            // get_primes(n, SEAL_USER_MOD_BIT_COUNT_MAX + 1 = 60, |B| + 2): m_sk, gamma, B... (rns.cpp:585-590)
+            std::vector<uint64_t> primes;
+            const uint64_t factor = 2 * n;
+            for (uint64_t v = (uint64_t(1) << 60) - factor + 1; primes.size() < o.nB + 2 && v > (uint64_t(1) << 59); v -= factor)
+                if (is_prime64(v))
+                    primes.push_back(v);
+            if (primes.size() < o.nB + 2)
+                return false;
+            o.m_sk = primes[0];
+            const std::vector<uint64_t> B(primes.begin() + 2, primes.end()), Q(q, q + L);
+            o.bsk = B;
+            o.bsk.push_back(o.m_sk);
+            o.inv_punct_q.resize(L);
+            o.inv_punct_b.resize(o.nB);
+            for (size_t i = 0; i < L; i++)
+                if (!inv_mod(punctured(Q, i, q[i]), q[i], o.inv_punct_q[i]))
+                    return false;
+            for (size_t i = 0; i < o.nB; i++)
+                if (!inv_mod(punctured(B, i, B[i]), B[i], o.inv_punct_b[i]))
+                    return false;
+            o.mat_q.resize((o.nBsk + 1) * L);
+            for (size_t j = 0; j <= o.nBsk; j++)
+                for (size_t i = 0; i < L; i++)
+                    o.mat_q[j * L + i] = punctured(Q, i, j < o.nBsk ? o.bsk[j] : m_tilde);
+            o.mat_b.resize((L + 1) * o.nB);
+            for (size_t j = 0; j <= L; j++)
+                for (size_t i = 0; i < o.nB; i++)
+                    o.mat_b[j * o.nB + i] = punctured(B, i, j < L ? q[j] : o.m_sk);
+            o.prod_q_mod_bsk.resize(o.nBsk);
+            o.inv_prod_q_mod_bsk.resize(o.nBsk);
+            o.inv_mtilde_mod_bsk.resize(o.nBsk);
+            for (size_t j = 0; j < o.nBsk; j++)
+            {
+                o.prod_q_mod_bsk[j] = punctured(Q, L, o.bsk[j]);
+                if (!inv_mod(o.prod_q_mod_bsk[j], o.bsk[j], o.inv_prod_q_mod_bsk[j]) ||
+                    !inv_mod(m_tilde % o.bsk[j], o.bsk[j], o.inv_mtilde_mod_bsk[j]))
+                    return false;
+            }
+            o.prod_b_mod_q.resize(L);
+            for (size_t i = 0; i < L; i++)
+                o.prod_b_mod_q[i] = punctured(B, o.nB, q[i]);
+            return inv_mod(punctured(B, o.nB, o.m_sk), o.m_sk, o.inv_prod_b_mod_msk) &&
+                   inv_mod(punctured(Q, L, m_tilde), m_tilde, o.inv_prod_q_mod_mtilde);
+        }
     } // namespace host
 } // namespace gsb

@@ -37,6 +37,24 @@ namespace gsb
         // false if q does not support a negacyclic NTT of size 2^logn
         bool build_limb_tables(int logn, uint64_t q, LimbTables &out);
 
+        // RNSTool constants BEHZ multiplication needs for base q = q[0..L) and plain modulus t
+        // (util/rns.cpp:540-728).  Extended base = q followed by Bsk = B u {m_sk}; M = L + nBsk.
+        struct BehzConsts
+        {
+            size_t L = 0, nB = 0, nBsk = 0;
+            uint64_t t = 0, m_sk = 0;
+            std::vector<uint64_t> bsk;            // nBsk moduli: the |B| primes, then m_sk
+            std::vector<uint64_t> inv_punct_q;    // [L]    (prod_{l != i} q_l)^-1 mod q_i
+            std::vector<uint64_t> mat_q;          // [nBsk + 1][L]: prod_{l != i} q_l mod Bsk_j; last row mod m_tilde
+            std::vector<uint64_t> inv_punct_b;    // [nB]
+            std::vector<uint64_t> mat_b;          // [L + 1][nB]: prod_{l != i} B_l mod q_j; last row mod m_sk
+            std::vector<uint64_t> prod_q_mod_bsk, inv_prod_q_mod_bsk, inv_mtilde_mod_bsk; // [nBsk]
+            std::vector<uint64_t> prod_b_mod_q;   // [L]
+            uint64_t inv_prod_q_mod_mtilde = 0, inv_prod_b_mod_msk = 0;
+        };
+        // false when the auxiliary base cannot be built (not enough primes / not invertible)
+        bool build_behz(int logn, const uint64_t *q, size_t L, uint64_t t, BehzConsts &out);
+
         // Galois permutation for NTT-form polynomials (util/galois.cpp:18-47)
         void galois_table_ntt(int logn, uint32_t elt, std::vector<uint32_t> &table);
         // util/galois.cpp:49-91; returns 0 for an out-of-range step

@@ -267,3 +267,64 @@ class Evaluator:
         else:
             _check(self.lib, self.lib.gsb_mul_relin_rescale_host(self.ctx.handle, _ptr(a), _ptr(b), _ptr(out), B, L))
         return out
+
+
+class BfvEvaluator(Evaluator):
+    """The BFV branches of the same seal::Evaluator entry points (coefficient-form ciphertexts):
+    relinearize_inplace (evaluator.cpp:772-827 -> :2259-2368 with is_ckks == false) and
+    apply_galois_inplace / rotate_rows / rotate_columns (evaluator.cpp:1893-1904, evaluator.h:1079-1176)."""
+
+    def relinearize(self, c):
+        B, _, L = self._shape(c, 3)
+        out = _empty_like(c, (B, 2, L, self.ctx.N))
+        if _is_torch(c):
+            _check(self.lib, self.lib.gsb_bfv_relinearize_dev(self.ctx.handle, None, _ptr(c), _ptr(out), B, L, _stream()))
+        else:
+            _check(self.lib, self.lib.gsb_bfv_relinearize_host(self.ctx.handle, _ptr(c), _ptr(out), B, L))
+        return out
+
+    def apply_galois(self, c, galois_elt):
+        B, _, L = self._shape(c, 2)
+        out = _empty_like(c, tuple(c.shape))
+        if _is_torch(c):
+            _check(self.lib, self.lib.gsb_bfv_apply_galois_dev(self.ctx.handle, None, int(galois_elt), _ptr(c), _ptr(out), B, L, _stream()))
+        else:
+            _check(self.lib, self.lib.gsb_bfv_apply_galois_host(self.ctx.handle, int(galois_elt), _ptr(c), _ptr(out), B, L))
+        return out
+
+    def rotate_rows(self, c, steps):
+        """rotate_rows (evaluator.h:1079-1130): same element as rotate_vector."""
+        return self.rotate_vector(c, steps)
+
+    def rotate_columns(self, c):
+        """rotate_columns (evaluator.h:1147-1176): Galois element 2N-1."""
+        return self.apply_galois(c, 2 * self.ctx.N - 1)
+
+    def __init__(self, context, plain_modulus):
+        super().__init__(context)
+        self.plain_modulus = int(plain_modulus)
+
+    def multiply(self, a, b):
+        """multiply_inplace -> bfv_multiply (BEHZ, evaluator.cpp:274-445) of size-2 ciphertexts -> size 3."""
+        B, _, L = self._shape(a, 2)
+        if tuple(b.shape) != tuple(a.shape):
+            raise ValueError("encrypted1 and encrypted2 parameter mismatch")
+        out = _empty_like(a, (B, 3, L, self.ctx.N))
+        if _is_torch(a):
+            _check(self.lib, self.lib.gsb_bfv_multiply_dev(self.ctx.handle, None, self.plain_modulus, _ptr(a), _ptr(b), _ptr(out), B, L, _stream()))
+        else:
+            _check(self.lib, self.lib.gsb_bfv_multiply_host(self.ctx.handle, self.plain_modulus, _ptr(a), _ptr(b), _ptr(out), B, L))
+        return out
+
+    def aux_base(self, L):
+        """Moduli of Bsk for level L (RNSTool::base_Bsk)."""
+        import ctypes as C
+        buf = (C.c_uint64 * 80)()
+        n = C.c_size_t()
+        _check(self.lib, self.lib.gsb_bfv_aux_base(self.ctx.handle, L, self.plain_modulus, buf, 80, C.byref(n)))
+        return [int(buf[i]) for i in range(n.value)]
+
+    def _unsupported(self, *a, **k):
+        raise NotImplementedError("not part of the BFV surface built so far (no CPU fallback)")
+
+    mul_relin_rescale = rescale_to_next = _unsupported

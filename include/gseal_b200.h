@@ -157,6 +157,29 @@ int gsb_apply_galois_dev(gsb_ctx *ctx, gsb_ws *ws, uint32_t galois_elt, const ui
  * the headline metric): a, b = [batch][2][L][N] -> out = [batch][2][L-1][N]. */
 int gsb_mul_relin_rescale_dev(gsb_ctx *ctx, gsb_ws *ws, const uint64_t *a, const uint64_t *b, uint64_t *out, size_t batch, size_t L, void *stream);
 
+/* ---- BFV branches of the same functions (BASELINE config #1) -----------------
+ * Ciphertexts are in coefficient form (is_ntt_form() == false).  These mirror what the reference
+ * computes for scheme_type::BFV word for word, including the in-bundle slot of the inner product
+ * reading the coefficient-form target as it is (evaluator.cpp:2319-2320 with is_ckks == false).
+ * Evaluator::relinearize_inplace, BFV (evaluator.cpp:772-827 -> :2259-2368, multi_special_primes.cpp:
+ * 287-289): in = [batch][3][L][N] -> out = [batch][2][L][N]. */
+int gsb_bfv_relinearize_dev(gsb_ctx *ctx, gsb_ws *ws, const uint64_t *in, uint64_t *out, size_t batch, size_t L, void *stream);
+/* Evaluator::apply_galois_inplace, BFV branch (evaluator.cpp:1893-1904; GaloisTool::apply_galois,
+ * util/galois.cpp:144-186; rotate_rows / rotate_columns, evaluator.h:1079-1176): in, out =
+ * [batch][2][L][N]. */
+int gsb_bfv_apply_galois_dev(gsb_ctx *ctx, gsb_ws *ws, uint32_t galois_elt, const uint64_t *in, uint64_t *out, size_t batch, size_t L, void *stream);
+/* Evaluator::multiply_inplace, BFV branch = bfv_multiply (BEHZ RNS multiplication, evaluator.cpp:
+ * 274-445; RNSTool::{fastbconv_m_tilde, sm_mrq, fast_floor, fastbconv_sk}, util/rns.cpp:853-1066):
+ * a, b = [batch][2][L][N] coefficient form -> out = [batch][3][L][N].  The auxiliary base Bsk and
+ * its constants for (L, plain_modulus) are derived on first use exactly as RNSTool::initialize does
+ * (util/rns.cpp:540-728) and cached in the context. */
+int gsb_bfv_multiply_dev(gsb_ctx *ctx, gsb_ws *ws, uint64_t plain_modulus, const uint64_t *a, const uint64_t *b, uint64_t *out, size_t batch, size_t L, void *stream);
+int gsb_bfv_multiply_host(gsb_ctx *ctx, uint64_t plain_modulus, const uint64_t *a, const uint64_t *b, uint64_t *out, size_t batch, size_t L);
+/* The moduli of Bsk = B u {m_sk} for (L, plain_modulus) (RNSTool::base_Bsk, util/rns.cpp:585-603). */
+int gsb_bfv_aux_base(gsb_ctx *ctx, size_t L, uint64_t plain_modulus, uint64_t *moduli_out, size_t cap, size_t *n_out);
+int gsb_bfv_relinearize_host(gsb_ctx *ctx, const uint64_t *in, uint64_t *out, size_t batch, size_t L);
+int gsb_bfv_apply_galois_host(gsb_ctx *ctx, uint32_t galois_elt, const uint64_t *in, uint64_t *out, size_t batch, size_t L);
+
 /* Host-buffer forms (what the C++ shim calls with seal::Ciphertext::data()): copy in, run, copy out,
  * synchronise.  Shapes as above. */
 int gsb_ckks_multiply_host(gsb_ctx *ctx, const uint64_t *a, const uint64_t *b, uint64_t *out, size_t batch, size_t L);

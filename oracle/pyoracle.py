@@ -59,6 +59,11 @@ class Oracle:
         lib.so_rescale.argtypes = [vp, sz, sz, vp, vp]
         lib.so_apply_galois.argtypes = [vp, sz, u32, vp, vp, vp]
         lib.so_mul_relin_rescale.argtypes = [vp, sz, vp, vp, vp, vp]
+        lib.so_relinearize_bfv.argtypes = [vp, sz, vp, vp, vp]
+        lib.so_bfv_multiply.argtypes = [i32, C.POINTER(u64), sz, u64, vp, vp, vp]
+        lib.so_bfv_aux_base.argtypes = [i32, C.POINTER(u64), sz, u64, vp]
+        lib.so_apply_galois_bfv.argtypes = [vp, sz, u32, vp, vp, vp]
+        lib.so_apply_galois_coeff.argtypes = [i32, u32, u64, vp, vp]
         lib.so_const_ratio.argtypes = [u64, C.POINTER(u64)]
         lib.so_barrett_reduce_128.argtypes = [u64, u64, u64, C.POINTER(u64)]
         lib.so_barrett_reduce_128.restype = u64
@@ -113,6 +118,19 @@ class Oracle:
         bb = np.ascontiguousarray(b, dtype=np.uint64) if b is not None else a
         assert self.lib.so_poly_op(op, q, _p(a), _p(bb), scalar, a.size, _p(out)) == 0
         return out
+
+    def bfv_multiply(self, logn, moduli, plain_modulus, a, b):
+        """bfv_multiply of two size-2 coefficient-form ciphertexts [2][L][N] -> [3][L][N]."""
+        L = a.shape[1]
+        out = np.empty((3, L, 1 << logn), dtype=np.uint64)
+        assert self.lib.so_bfv_multiply(logn, _u64arr(moduli[:L]), L, plain_modulus, _p(a), _p(b), _p(out)) == 0
+        return out
+
+    def bfv_aux_base(self, logn, moduli, plain_modulus):
+        out = np.zeros(64, dtype=np.uint64)
+        assert self.lib.so_bfv_aux_base(logn, _u64arr(moduli), len(moduli), plain_modulus, _p(out)) == 0
+        nb = int(out[0])
+        return nb, [int(x) for x in out[1:nb + 2]]
 
     def galois_table_ntt(self, logn, elt):
         t = np.empty(1 << logn, dtype=np.uint32)
@@ -172,6 +190,19 @@ class OracleCtx:
         assert self.lib.so_mul_relin_rescale(self.h, L, _p(a), _p(b), _p(key), _p(out)) == 0
         return out
 
+    # -- BFV branches: coefficient-form ciphertexts
+    def relinearize_bfv(self, c3, key):
+        L = c3.shape[1]
+        out = np.empty((2, L, self.N), dtype=np.uint64)
+        assert self.lib.so_relinearize_bfv(self.h, L, _p(c3), _p(key), _p(out)) == 0
+        return out
+
+    def apply_galois_bfv(self, c, elt, key):
+        L = c.shape[1]
+        out = np.empty((2, L, self.N), dtype=np.uint64)
+        assert self.lib.so_apply_galois_bfv(self.h, L, elt, _p(c), _p(key), _p(out)) == 0
+        return out
+
 
 class RefLib:
     """The unmodified reference behind oracle/ref_harness.cpp.  Raises FileNotFoundError when the
@@ -191,6 +222,8 @@ class RefLib:
         lib.ref_create_moduli.argtypes = [sz, C.POINTER(i32), sz, vp]
         lib.ref_ckks_create.argtypes = [sz, C.POINTER(u64), sz, sz]
         lib.ref_ckks_create.restype = vp
+        lib.ref_bfv_create.argtypes = [sz, C.POINTER(u64), sz, sz, u64]
+        lib.ref_bfv_create.restype = vp
         lib.ref_ckks_destroy.argtypes = [vp]
         lib.ref_keygen.argtypes = [vp, C.POINTER(u32), sz]
         lib.ref_make_synthetic_keys.argtypes = [vp, C.POINTER(u32), sz, u64]
@@ -251,15 +284,19 @@ class RefLib:
         assert self.lib.ref_create_moduli(N, arr, len(bits), _p(out)) == 0, self.err()
         return [int(x) for x in out]
 
-    def context(self, N, moduli, k_special):
-        return RefCtx(self, N, moduli, k_special)
+    def context(self, N, moduli, k_special, bfv_plain_modulus=None):
+        """CKKS context, or a BFV one (coefficient-form ciphertexts) when a plain modulus is given."""
+        return RefCtx(self, N, moduli, k_special, bfv_plain_modulus)
 
 
 class RefCtx:
-    def __init__(self, ref, N, moduli, k_special):
+    def __init__(self, ref, N, moduli, k_special, bfv_plain_modulus=None):
         self.ref, self.lib = ref, ref.lib
         self.N, self.moduli, self.k, self.K = N, list(moduli), k_special, len(moduli)
-        self.h = self.lib.ref_ckks_create(N, _u64arr(moduli), self.K, k_special)
+        if bfv_plain_modulus is None:
+            self.h = self.lib.ref_ckks_create(N, _u64arr(moduli), self.K, k_special)
+        else:
+            self.h = self.lib.ref_bfv_create(N, _u64arr(moduli), self.K, k_special, bfv_plain_modulus)
         if not self.h:
             raise ValueError(ref.err())
 

@@ -38,6 +38,7 @@ namespace
         RelinKeys relin;
         GaloisKeys galois;
         bool have_relin = false, have_galois = false;
+        bool bfv = false; // BFV context: coefficient-form ciphertexts, scale 1
         size_t N = 0, K = 0, k = 0, L0 = 0;
 
         parms_id_type parms_at(size_t L) const
@@ -56,8 +57,8 @@ namespace
         {
             Ciphertext ct(context, parms_at(L));
             ct.resize(size);
-            ct.is_ntt_form() = true;
-            ct.scale() = scale;
+            ct.is_ntt_form() = !bfv;
+            ct.scale() = bfv ? 1.0 : scale;
             std::memcpy(ct.data(), src, size * L * N * sizeof(uint64_t));
             return ct;
         }
@@ -214,6 +215,41 @@ extern "C"
             c = new RefCtx();
             c->context = ctx;
             c->evaluator.reset(new Evaluator(ctx));
+            c->N = N;
+            c->K = K;
+            c->k = k_special;
+            c->L0 = K - k_special;
+        });
+        if (rc)
+        {
+            delete c;
+            return nullptr;
+        }
+        return c;
+    }
+
+    // BFV context over the same moduli (scheme_type::BFV, evaluator.cpp:274-445 and the BFV branches
+    // of switch_key_inplace / apply_galois_inplace); ciphertexts handed to the ops below are then in
+    // coefficient form.
+    void *ref_bfv_create(size_t N, const uint64_t *moduli, size_t K, size_t k_special, uint64_t plain_modulus)
+    {
+        RefCtx *c = nullptr;
+        int rc = guarded([&] {
+            EncryptionParameters parms(scheme_type::BFV);
+            parms.set_poly_modulus_degree(N);
+            std::vector<Modulus> mods;
+            for (size_t i = 0; i < K; i++)
+                mods.emplace_back(moduli[i]);
+            parms.set_coeff_modulus(mods);
+            parms.set_plain_modulus(plain_modulus);
+            parms.set_n_special_primes(static_cast<int>(k_special));
+            auto ctx = SEALContext::Create(parms, true, sec_level_type::none);
+            if (!ctx->parameters_set())
+                throw std::invalid_argument(std::string("parameters not set: ") + ctx->parameter_error_message());
+            c = new RefCtx();
+            c->context = ctx;
+            c->evaluator.reset(new Evaluator(ctx));
+            c->bfv = true;
             c->N = N;
             c->K = K;
             c->k = k_special;

@@ -571,7 +571,7 @@ static void modup_to_single(const so_ctx *c, const uint64_t *src, size_t idx0, s
 }
 
 /* multi_special_primes.cpp:237-304: ext [L+k][N] (special part in coefficient form) -> first L limbs */
-static void rescale_special(const so_ctx *c, size_t L, uint64_t *ext)
+static void rescale_special(const so_ctx *c, size_t L, uint64_t *ext, int is_ckks)
 {
     const size_t N = c->N, k = c->k, sp0 = c->L0;
     uint64_t inv_hat[64], inv_hat_s[64];
@@ -613,7 +613,10 @@ static void rescale_special(const so_ctx *c, size_t L, uint64_t *ext)
             }
             temp[d] = so_barrett_reduce_128((uint64_t)acc, (uint64_t)(acc >> 64), qi, cri);
         }
-        so_ntt_fwd_lazy(temp, &c->tab[i]); /* step 3 (CKKS), :285-286 */
+        if (is_ckks) /* step 3, :285-289 */
+            so_ntt_fwd_lazy(temp, &c->tab[i]);
+        else
+            so_ntt_inv_lazy(ext + i * N, &c->tab[i]);
         uint64_t P = 1, invP;              /* step 4, :291-302 */
         for (size_t j = 0; j < k; j++)
             P = so_multiply_uint_mod(P, c->q[sp0 + j], qi, cri);
@@ -626,7 +629,7 @@ static void rescale_special(const so_ctx *c, size_t L, uint64_t *ext)
     free(temp);
 }
 
-int so_switch_key(const so_ctx *c, size_t L, uint64_t *enc, const uint64_t *target, const uint64_t *key)
+static int switch_key_scheme(const so_ctx *c, size_t L, uint64_t *enc, const uint64_t *target, const uint64_t *key, int is_ckks)
 {
     if (L < 1 || L > c->L0)
         return -1;
@@ -639,11 +642,13 @@ int so_switch_key(const so_ctx *c, size_t L, uint64_t *enc, const uint64_t *targ
     for (size_t j = 0; j < beta; j++)
     {
         const size_t r0 = j * k, r1 = (r0 + k < L) ? r0 + k : L;
-        /* step 1 (:2302-2307): strict inverse NTT of the bundle's limbs */
+        /* step 1 (:2302-2307): strict inverse NTT of the bundle's limbs (CKKS); BFV targets are
+           already in coefficient form */
         for (size_t i = r0; i < r1; i++)
         {
             memcpy(ext + i * N, target + i * N, N * 8);
-            so_ntt_inv(ext + i * N, &c->tab[i]);
+            if (is_ckks)
+                so_ntt_inv(ext + i * N, &c->tab[i]);
         }
         /* step 2 (:2310, modup_rns multi_special_primes.cpp:151-185) */
         for (size_t kap = 0; kap < E; kap++)
@@ -685,7 +690,7 @@ int so_switch_key(const so_ctx *c, size_t L, uint64_t *enc, const uint64_t *targ
                 so_ntt_inv_lazy(ext + kap * N, &c->tab[ridx]);
         }
         /* step 5 (:2360-2366) */
-        rescale_special(c, L, ext);
+        rescale_special(c, L, ext, is_ckks);
         uint64_t *e = enc + l * L * N;
         for (size_t i = 0; i < L; i++)
             for (size_t d = 0; d < N; d++)
@@ -695,6 +700,60 @@ int so_switch_key(const so_ctx *c, size_t L, uint64_t *enc, const uint64_t *targ
     free(acc[1]);
     free(ext);
     return 0;
+}
+
+int so_switch_key(const so_ctx *c, size_t L, uint64_t *enc, const uint64_t *target, const uint64_t *key)
+{
+    return switch_key_scheme(c, L, enc, target, key, 1);
+}
+
+/* BFV branch of the same function: is_ckks == false at :2305, :2320 (the in-bundle slot multiplies
+   the coefficient-form target as it is) and multi_special_primes.cpp:287-289. */
+int so_switch_key_bfv(const so_ctx *c, size_t L, uint64_t *enc, const uint64_t *target, const uint64_t *key)
+{
+    return switch_key_scheme(c, L, enc, target, key, 0);
+}
+
+int so_relinearize_bfv(const so_ctx *c, size_t L, const uint64_t *in, const uint64_t *key, uint64_t *out)
+{
+    const size_t N = c->N;
+    uint64_t *tmp = (uint64_t *)malloc(3 * L * N * 8);
+    memcpy(tmp, in, 3 * L * N * 8);
+    int rc = so_switch_key_bfv(c, L, tmp, tmp + 2 * L * N, key);
+    if (!rc)
+        memcpy(out, tmp, 2 * L * N * 8);
+    free(tmp);
+    return rc;
+}
+
+/* GaloisTool::apply_galois, coefficient form (util/galois.cpp:144-186) */
+void so_apply_galois_coeff(int logn, uint32_t elt, uint64_t q, const uint64_t *in, uint64_t *out)
+{
+    const uint64_t n = (uint64_t)1 << logn;
+    uint64_t index_raw = 0;
+    for (uint64_t i = 0; i < n; i++, index_raw += elt)
+    {
+        uint64_t v = in[i];
+        if ((index_raw >> logn) & 1)
+            v = v ? q - v : 0;
+        out[index_raw & (n - 1)] = v;
+    }
+}
+
+/* evaluator.cpp:1841-1943, BFV branch (:1893-1904) */
+int so_apply_galois_bfv(const so_ctx *c, size_t L, uint32_t elt, const uint64_t *in, const uint64_t *key, uint64_t *out)
+{
+    const size_t N = c->N;
+    uint64_t *temp = (uint64_t *)malloc(L * N * 8);
+    for (size_t i = 0; i < L; i++)
+    {
+        so_apply_galois_coeff(c->logn, elt, c->q[i], in + i * N, out + i * N);
+        so_apply_galois_coeff(c->logn, elt, c->q[i], in + (L + i) * N, temp + i * N);
+    }
+    memset(out + L * N, 0, L * N * 8);
+    int rc = so_switch_key_bfv(c, L, out, temp, key);
+    free(temp);
+    return rc;
 }
 
 /* evaluator.cpp:772-827 (size 3 -> 2) */

@@ -87,6 +87,16 @@ int so_relinearize(const so_ctx *c, size_t L, const uint64_t *in, const uint64_t
 int so_rescale(const so_ctx *c, size_t L, size_t size, const uint64_t *in, uint64_t *out);
 /* in/out [2][L][N] */
 int so_apply_galois(const so_ctx *c, size_t L, uint32_t elt, const uint64_t *in, const uint64_t *key, uint64_t *out);
+/* ---- BFV branches (coefficient-form ciphertexts) ----------------------- */
+int so_switch_key_bfv(const so_ctx *c, size_t L, uint64_t *enc, const uint64_t *target, const uint64_t *key);
+int so_relinearize_bfv(const so_ctx *c, size_t L, const uint64_t *in, const uint64_t *key, uint64_t *out);
+void so_apply_galois_coeff(int logn, uint32_t elt, uint64_t q, const uint64_t *in, uint64_t *out);
+int so_apply_galois_bfv(const so_ctx *c, size_t L, uint32_t elt, const uint64_t *in, const uint64_t *key, uint64_t *out);
+/* Evaluator::bfv_multiply (BEHZ, evaluator.cpp:274-445; seal_oracle_bfv.c): a, b [2][L][N] in
+ * coefficient form over q[0..L) -> out [3][L][N] */
+int so_bfv_multiply(int logn, const uint64_t *q, size_t L, uint64_t plain_modulus, const uint64_t *a, const uint64_t *b, uint64_t *out);
+/* out[0] = |B|, out[1..] = the |B|+1 moduli of Bsk (rns.cpp:585-603) */
+int so_bfv_aux_base(int logn, const uint64_t *q, size_t L, uint64_t plain_modulus, uint64_t *out);
 /* a,b [2][L][N] -> out [2][L-1][N] */
 int so_mul_relin_rescale(const so_ctx *c, size_t L, const uint64_t *a, const uint64_t *b, const uint64_t *key, uint64_t *out);
 

@@ -222,6 +222,13 @@ static inline cudaError_t cudaMemcpyAsync(void *d, const void *s, size_t n, cuda
     memmove(d, s, n);
     return 0;
 }
+static inline cudaError_t cudaMemcpy2DAsync(
+    void *d, size_t dpitch, const void *s, size_t spitch, size_t width, size_t height, cudaMemcpyKind, cudaStream_t)
+{
+    for (size_t r = 0; r < height; r++)
+        memmove(static_cast<char *>(d) + r * dpitch, static_cast<const char *>(s) + r * spitch, width);
+    return 0;
+}
 static inline cudaError_t cudaMemsetAsync(void *d, int v, size_t n, cudaStream_t)
 {
     memset(d, v, n);

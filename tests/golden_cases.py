@@ -37,12 +37,23 @@ EVAL = {
     "n32768_k4_L12": (15, BFV_DEFAULT[32768], 4, 12, 1, 1),
     "n65536_k1_L2": (16, [59, 59, 59], 1, 2, 1, 1),
 }
+# BFV branches (BASELINE config #1 = the first one): coefficient-form ciphertexts.
+# name -> (logn, moduli spec, k special, level L, batch, rotation step, plain modulus)
+BFV = {
+    "c1_bfv_n4096_default": (12, BFV_DEFAULT[4096], 1, 2, 2, 1, 786433),  # 7_performance.cpp:543-552
+    "bfv_n2048_k2_L4": (11, [50, 40, 45, 45, 50, 51], 2, 4, 1, -1, 65537),
+    "bfv_n1024_k1_L3": (10, [40, 40, 40, 41], 1, 3, 2, 3, 12289),
+    "bfv_n8192_default": (13, BFV_DEFAULT[8192], 1, 4, 1, 1, 786433),
+    "bfv_n16384_default": (14, BFV_DEFAULT[16384], 1, 8, 1, 1, 786433),
+}
+
 # (logn, bits): 3 polys x 3 limbs, all four transforms
 NTT = {"ntt_n%d_b%d" % (ln, b): (ln, b) for ln in (10, 11, 12, 13, 14, 15, 16) for b in (30, 59)}
 NTT["ntt_n12_b60_wrap"] = (12, 60)  # lazy forward transform wraps mod 2^64
 NTT["ntt_n15_b60_wrap"] = (15, 60)
 
-SMALL = [n for n, c in EVAL.items() if c[0] <= 12] + [n for n, c in NTT.items() if c[0] <= 13]
+SMALL = ([n for n, c in EVAL.items() if c[0] <= 12] + [n for n, c in NTT.items() if c[0] <= 13] +
+         [n for n, c in BFV.items() if c[0] <= 12])
 
 
 def case_seed(name):
@@ -62,6 +73,18 @@ def eval_inputs(name):
         relin=rand_key(rng, mods, nb, N), galois=rand_key(rng, mods, nb, N))
 
 
+def bfv_inputs(name):
+    logn, spec, k, L, batch, step, t = BFV[name]
+    N = 1 << logn
+    mods = list(spec) if spec[0] > 64 else mixed_moduli(logn, spec)
+    rng = np.random.default_rng(case_seed(name))
+    nb = (len(mods) - k + k - 1) // k
+    return dict(
+        logn=logn, N=N, mods=mods, k=k, L=L, batch=batch, step=step, t=t,
+        a=rand_poly(rng, mods[:L], (batch, 2), N), b=rand_poly(rng, mods[:L], (batch, 2), N),
+        relin=rand_key(rng, mods, nb, N), galois=rand_key(rng, mods, nb, N), conj=rand_key(rng, mods, nb, N))
+
+
 def ntt_inputs(name):
     logn, bits = NTT[name]
     mods = ntt_primes(logn, bits, 3)
@@ -75,6 +98,17 @@ def run_case(name, be):
         c = ntt_inputs(name)
         for kind in range(4):
             out["kind%d" % kind] = digest(be.ntt(c["logn"], c["mods"], c["x"], kind))
+        return out
+    if name in BFV:
+        c = bfv_inputs(name)
+        be.setup(c["logn"], c["mods"], c["k"], bfv_t=c["t"])
+        elt, conj = be.elt_from_step(c["logn"], c["step"]), 2 * c["N"] - 1
+        be.set_keys(c["relin"], elt, c["galois"], conj, c["conj"])
+        c3 = be.multiply(c["a"], c["b"])
+        out["bfv_multiply"] = digest(c3)
+        out["bfv_relinearize"] = digest(be.relinearize(c3))
+        out["bfv_rotate_rows"] = digest(be.apply_galois(c["a"], elt))
+        out["bfv_rotate_columns"] = digest(be.apply_galois(c["b"], conj))
         return out
     c = eval_inputs(name)
     be.setup(c["logn"], c["mods"], c["k"])
@@ -105,20 +139,24 @@ class OracleBackend(_PerCt):
     def ntt(self, logn, mods, x, kind):
         return self.o.ntt_rns(logn, mods, x, kind)
 
-    def setup(self, logn, mods, k):
-        self.logn = logn
+    def setup(self, logn, mods, k, bfv_t=None):
+        self.logn, self.mods, self.t = logn, mods, bfv_t
         self.c = self.o.context(logn, mods, k)
 
     def elt_from_step(self, logn, step):
         return self.o.elt_from_step(logn, step)
 
-    def set_keys(self, relin, elt, galois):
-        self.relin, self.elt, self.gal = relin, elt, galois
+    def set_keys(self, relin, elt, galois, elt2=None, galois2=None):
+        self.relin, self.gal = relin, {elt: galois, elt2: galois2}
 
     def multiply(self, a, b):
+        if self.t is not None:
+            return self.each(lambda x, y: self.o.bfv_multiply(self.logn, self.mods, self.t, x, y), a, b)
         return self.each(self.c.multiply, a, b)
 
     def relinearize(self, c3):
+        if self.t is not None:
+            return self.each(lambda x: self.c.relinearize_bfv(x, self.relin), c3)
         return self.each(lambda x: self.c.relinearize(x, self.relin), c3)
 
     def rescale(self, c):
@@ -128,7 +166,9 @@ class OracleBackend(_PerCt):
         return self.each(lambda x, y: self.c.mul_relin_rescale(x, y, self.relin), a, b)
 
     def apply_galois(self, c, elt):
-        return self.each(lambda x: self.c.apply_galois(x, elt, self.gal), c)
+        if self.t is not None:
+            return self.each(lambda x: self.c.apply_galois_bfv(x, elt, self.gal[elt]), c)
+        return self.each(lambda x: self.c.apply_galois(x, elt, self.gal[elt]), c)
 
 
 class RefBackend(_PerCt):
@@ -143,16 +183,18 @@ class RefBackend(_PerCt):
             out[:, y, :] = self.r.ntt(logn, q, np.ascontiguousarray(x[:, y, :]), kind)
         return out
 
-    def setup(self, logn, mods, k):
-        self.c = self.r.context(1 << logn, mods, k)
+    def setup(self, logn, mods, k, bfv_t=None):
+        self.c = self.r.context(1 << logn, mods, k, bfv_plain_modulus=bfv_t)
 
     def elt_from_step(self, logn, step):
         return self.c.elt_from_step(step)
 
-    def set_keys(self, relin, elt, galois):
-        self.c.keygen([elt])
+    def set_keys(self, relin, elt, galois, elt2=None, galois2=None):
+        self.c.keygen([elt] + ([elt2] if elt2 is not None else []))
         self.c.set_key(0, 0, relin)
         self.c.set_key(1, elt, galois)
+        if elt2 is not None:
+            self.c.set_key(1, elt2, galois2)
 
     def multiply(self, a, b):
         return self.each(self.c.multiply, a, b)
@@ -191,19 +233,21 @@ class DeviceBackend:
         ctx.close()
         return out
 
-    def setup(self, logn, mods, k):
-        from gemini_seal_b200 import Evaluator
+    def setup(self, logn, mods, k, bfv_t=None):
+        from gemini_seal_b200 import BfvEvaluator, Evaluator
         if self.ctx is not None:
             self.ctx.close()
         self.ctx = self._ctx(logn, mods, k)
-        self.ev = Evaluator(self.ctx)
+        self.ev = Evaluator(self.ctx) if bfv_t is None else BfvEvaluator(self.ctx, bfv_t)
 
     def elt_from_step(self, logn, step):
         return self.ctx.galois_elt_from_step(step)
 
-    def set_keys(self, relin, elt, galois):
+    def set_keys(self, relin, elt, galois, elt2=None, galois2=None):
         self.ctx.set_relin_keys(relin)
         self.ctx.set_galois_key(elt, galois)
+        if elt2 is not None:
+            self.ctx.set_galois_key(elt2, galois2)
 
     def multiply(self, a, b):
         return self.ev.multiply(a, b)

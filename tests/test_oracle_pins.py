@@ -186,6 +186,27 @@ def test_evaluator_real_keys_vs_reference(oracle, reflib):
     assert np.array_equal(oc.apply_galois(a, elt, gal), rc.rotate(a, -3))
 
 
+def test_bfv_branches_vs_reference(oracle, reflib):
+    """BASELINE config #1 (BFV N = 4096, default 109-bit modulus, t = 786433 as in 7_performance.cpp:543-552)
+    and a k = 2 context: bfv_multiply (BEHZ), relinearize and apply_galois on coefficient-form ciphertexts,
+    keys from the reference's own KeyGenerator."""
+    import golden_cases
+    from common import mixed_moduli, rand_poly
+    for logn, mods, k, t in [(12, golden_cases.BFV_DEFAULT[4096], 1, 786433), (11, mixed_moduli(11, [50, 40, 45, 45, 50, 51]), 2, 65537)]:
+        N, L = 1 << logn, len(mods) - k
+        rc = reflib.context(N, mods, k, bfv_plain_modulus=t)
+        oc = oracle.context(logn, mods, k)
+        elt = oracle.elt_from_step(logn, 1)
+        rc.keygen([elt, 2 * N - 1])
+        rng = np.random.default_rng(logn)
+        a, b = rand_poly(rng, mods[:L], (2,), N), rand_poly(rng, mods[:L], (2,), N)
+        c3 = rc.multiply(a, b)
+        assert np.array_equal(oracle.bfv_multiply(logn, mods, t, a, b), c3)
+        assert np.array_equal(oc.relinearize_bfv(c3, rc.get_key(0)), rc.relinearize(c3))
+        for e in (elt, 2 * N - 1):
+            assert np.array_equal(oc.apply_galois_bfv(a, e, rc.get_key(1, e)), rc.apply_galois(a, e))
+
+
 # ---- (c) golden digests produced by the reference ---------------------------------------------------
 def test_golden_digests(oracle):
     path = os.path.join(os.path.dirname(__file__), "golden", "evaluator_digests.json")
