@@ -46,8 +46,10 @@ namespace gsb_seal
         if (!context_->parameters_set())
             throw invalid_argument("encryption parameters are not set correctly");
         auto &key_parms = context_->key_context_data()->parms();
-        if (key_parms.scheme() != scheme_type::CKKS)
-            throw logic_error("gsb_seal::Evaluator serves the CKKS path only");
+        if (key_parms.scheme() != scheme_type::CKKS && key_parms.scheme() != scheme_type::BFV)
+            throw logic_error("unsupported scheme");
+        bfv_ = key_parms.scheme() == scheme_type::BFV;
+        plain_modulus_ = bfv_ ? key_parms.plain_modulus().value() : 0;
         N_ = key_parms.poly_modulus_degree();
         K_ = key_parms.coeff_modulus().size();
         k_ = K_ - context_->first_context_data()->parms().coeff_modulus().size(); // evaluator.cpp:2273-2276
@@ -85,6 +87,11 @@ namespace gsb_seal
         validate(encrypted2, "encrypted2");
         if (encrypted1.parms_id() != encrypted2.parms_id())
             throw invalid_argument("encrypted1 and encrypted2 parameter mismatch");
+        if (bfv_)
+        {
+            bfv_multiply(encrypted1, encrypted2);
+            return;
+        }
         if (!(encrypted1.is_ntt_form() && encrypted2.is_ntt_form()))
             throw invalid_argument("encrypted1 or encrypted2 must be in NTT form");
         auto &context_data = *context_->get_context_data(encrypted1.parms_id());
@@ -104,6 +111,31 @@ namespace gsb_seal
         encrypted1.resize(context_, context_data.parms_id(), 3);
         check(gsb_ckks_multiply_host(ctx_, encrypted1.data(), pb, encrypted1.data(), 1, L));
         encrypted1.scale() = new_scale;
+#ifdef SEAL_THROW_ON_TRANSPARENT_CIPHERTEXT
+        if (encrypted1.is_transparent())
+            throw logic_error("result ciphertext is transparent");
+#endif
+    }
+
+    // evaluator.cpp:274-445 (BEHZ); size-2 operands, coefficient form
+    void Evaluator::bfv_multiply(Ciphertext &encrypted1, const Ciphertext &encrypted2)
+    {
+        if (encrypted1.is_ntt_form() || encrypted2.is_ntt_form())
+            throw invalid_argument("encrypted1 or encrypted2 cannot be in NTT form");
+        if (encrypted1.size() != 2 || encrypted2.size() != 2)
+            throw logic_error("device multiply serves size-2 operands (relinearize first)");
+        auto &context_data = *context_->get_context_data(encrypted1.parms_id());
+        const size_t L = level_limbs(encrypted1);
+        vector<uint64_t> b;
+        const uint64_t *pb = encrypted2.data();
+        if (&encrypted1 == &encrypted2)
+        {
+            b.assign(encrypted2.data(), encrypted2.data() + 2 * L * N_);
+            pb = b.data();
+        }
+        vector<uint64_t> a(encrypted1.data(), encrypted1.data() + 2 * L * N_);
+        encrypted1.resize(context_, context_data.parms_id(), 3);
+        check(gsb_bfv_multiply_host(ctx_, plain_modulus_, a.data(), pb, encrypted1.data(), 1, L));
 #ifdef SEAL_THROW_ON_TRANSPARENT_CIPHERTEXT
         if (encrypted1.is_transparent())
             throw logic_error("result ciphertext is transparent");
@@ -176,14 +208,17 @@ namespace gsb_seal
             throw invalid_argument("not enough relinearization keys");
         if (size <= 2)
             return;
-        if (!encrypted.is_ntt_form())
-            throw logic_error("device key switching serves CKKS (NTT-form) ciphertexts");
+        if (encrypted.is_ntt_form() == bfv_) // BFV ciphertexts are in coefficient form, CKKS ones in NTT form
+            throw logic_error(bfv_ ? "BFV encrypted cannot be in NTT form" : "CKKS encrypted must be in NTT form");
         const size_t L = level_limbs(encrypted), LN = L * N_;
+        if (size > 3 && bfv_)
+            throw logic_error("device BFV relinearization serves size-3 ciphertexts");
         if (size == 3)
         {
             ensure_relin(relin_keys, RelinKeys::get_index(2));
             vector<uint64_t> out(2 * LN);
-            check(gsb_relinearize_host(ctx_, encrypted.data(), out.data(), 1, L));
+            check(bfv_ ? gsb_bfv_relinearize_host(ctx_, encrypted.data(), out.data(), 1, L)
+                       : gsb_relinearize_host(ctx_, encrypted.data(), out.data(), 1, L));
             encrypted.resize(context_, context_data_ptr->parms_id(), 2);
             memcpy(encrypted.data(), out.data(), 2 * LN * sizeof(uint64_t));
         }
@@ -265,12 +300,13 @@ namespace gsb_seal
             throw invalid_argument("Galois element is not valid");
         if (encrypted.size() > 2)
             throw invalid_argument("encrypted size must be 2");
-        if (!encrypted.is_ntt_form())
-            throw logic_error("device key switching serves CKKS (NTT-form) ciphertexts");
+        if (encrypted.is_ntt_form() == bfv_)
+            throw logic_error(bfv_ ? "BFV encrypted cannot be in NTT form" : "CKKS encrypted must be in NTT form");
         ensure_galois(galois_keys, galois_elt);
         const size_t L = level_limbs(encrypted);
         vector<uint64_t> out(2 * L * N_);
-        check(gsb_apply_galois_host(ctx_, galois_elt, encrypted.data(), out.data(), 1, L));
+        check(bfv_ ? gsb_bfv_apply_galois_host(ctx_, galois_elt, encrypted.data(), out.data(), 1, L)
+                   : gsb_apply_galois_host(ctx_, galois_elt, encrypted.data(), out.data(), 1, L));
         memcpy(encrypted.data(), out.data(), out.size() * sizeof(uint64_t));
 #ifdef SEAL_THROW_ON_TRANSPARENT_CIPHERTEXT
         if (encrypted.is_transparent())
@@ -325,6 +361,27 @@ namespace gsb_seal
     {
         destination = encrypted;
         rotate_vector_inplace(destination, steps, galois_keys, move(pool));
+    }
+
+    void Evaluator::rotate_rows_inplace(Ciphertext &encrypted, int steps, const GaloisKeys &galois_keys, MemoryPoolHandle)
+    {
+        // evaluator.h:1049-1057
+        if (context_->key_context_data()->parms().scheme() != scheme_type::BFV)
+            throw logic_error("unsupported scheme");
+        rotate_internal(encrypted, steps, galois_keys);
+    }
+
+    void Evaluator::rotate_columns_inplace(Ciphertext &encrypted, const GaloisKeys &galois_keys, MemoryPoolHandle pool)
+    {
+        // evaluator.h:1125-1133 -> conjugate_internal (:1343-1363): Galois element 2N-1
+        if (context_->key_context_data()->parms().scheme() != scheme_type::BFV)
+            throw logic_error("unsupported scheme");
+        auto context_data_ptr = context_->get_context_data(encrypted.parms_id());
+        if (!context_data_ptr)
+            throw invalid_argument("encrypted is not valid for encryption parameters");
+        if (!context_data_ptr->qualifiers().using_batching)
+            throw logic_error("encryption parameters do not support batching");
+        apply_galois_inplace(encrypted, static_cast<uint32_t>(2 * N_ - 1), galois_keys, move(pool));
     }
 
     void Evaluator::complex_conjugate_inplace(Ciphertext &encrypted, const GaloisKeys &galois_keys, MemoryPoolHandle pool)

@@ -11,8 +11,9 @@
 //
 // Same argument meaning, same in-place semantics (resize, scale, parms_id, is_ntt_form), same
 // exception types and messages as native/src/seal/evaluator.cpp; CUDA failures surface as
-// std::runtime_error.  CKKS only (the north-star path); anything else throws std::logic_error, it is
-// never silently routed to a CPU implementation.
+// std::runtime_error.  CKKS (the north-star path) and the BFV branches of multiply / relinearize /
+// rotate_rows / rotate_columns (BASELINE config #1); anything else throws std::logic_error, it is never
+// silently routed to a CPU implementation.
 #pragma once
 #include "gseal_b200.h"
 #include "seal/seal.h"
@@ -71,6 +72,14 @@ namespace gsb_seal
             const seal::Ciphertext &encrypted, int steps, const seal::GaloisKeys &galois_keys, seal::Ciphertext &destination,
             seal::MemoryPoolHandle pool = seal::MemoryManager::GetPool());
 
+        // BFV: rotate_rows / rotate_columns (evaluator.h:1049-1176)
+        void rotate_rows_inplace(
+            seal::Ciphertext &encrypted, int steps, const seal::GaloisKeys &galois_keys,
+            seal::MemoryPoolHandle pool = seal::MemoryManager::GetPool());
+        void rotate_columns_inplace(
+            seal::Ciphertext &encrypted, const seal::GaloisKeys &galois_keys,
+            seal::MemoryPoolHandle pool = seal::MemoryManager::GetPool());
+
         // evaluator.h:1269-1311
         void complex_conjugate_inplace(
             seal::Ciphertext &encrypted, const seal::GaloisKeys &galois_keys,
@@ -86,6 +95,7 @@ namespace gsb_seal
 
     private:
         void validate(const seal::Ciphertext &ct, const char *what) const;
+        void bfv_multiply(seal::Ciphertext &encrypted1, const seal::Ciphertext &encrypted2);
         std::size_t level_limbs(const seal::Ciphertext &ct) const;
         void ensure_relin(const seal::RelinKeys &keys, std::size_t index);
         void ensure_galois(const seal::GaloisKeys &keys, std::uint32_t elt);
@@ -96,6 +106,8 @@ namespace gsb_seal
         std::shared_ptr<seal::SEALContext> context_;
         gsb_ctx *ctx_ = nullptr;
         std::size_t N_ = 0, K_ = 0, k_ = 0;
+        bool bfv_ = false;
+        std::uint64_t plain_modulus_ = 0;
         std::mutex mu_;
         // which host key object (by data pointer) currently sits in each device key slot
         std::map<std::uint32_t, const void *> relin_loaded_, galois_loaded_;

@@ -171,12 +171,70 @@ static int run(size_t N, vector<int> bits, int k_special)
     return failures;
 }
 
+// BASELINE config #1: BFV, N = 4096, CoeffModulus::BFVDefault (109 bits), t = 786433 -- what
+// native/examples/7_performance.cpp:543-552 runs: multiply, relinearize, rotate rows / columns on real
+// encryptions.  (The reference's BFV outputs are not semantically valid at this N, SURVEY F6: the check
+// is word-for-word equality with the reference, not decryption.)
+static int run_bfv(size_t N)
+{
+    printf("---- BFV N=%zu, BFVDefault modulus, t=786433\n", N);
+    EncryptionParameters parms(scheme_type::BFV);
+    parms.set_poly_modulus_degree(N);
+    parms.set_coeff_modulus(CoeffModulus::BFVDefault(N));
+    parms.set_plain_modulus(786433);
+    auto context = SEALContext::Create(parms, true, sec_level_type::none);
+    KeyGenerator keygen(context);
+    auto pk = keygen.public_key();
+    RelinKeys rlk = keygen.relin_keys_local();
+    GaloisKeys glk = keygen.galois_keys_local();
+    Encryptor enc(context, pk);
+    BatchEncoder encoder(context);
+    Evaluator ref(context);
+    gsb_seal::Evaluator dev(context);
+    vector<uint64_t> va(encoder.slot_count()), vb(encoder.slot_count());
+    mt19937_64 rng(7);
+    for (size_t i = 0; i < va.size(); i++)
+        va[i] = rng() % 786433, vb[i] = rng() % 786433;
+    Plaintext pa, pb;
+    encoder.encode(va, pa);
+    encoder.encode(vb, pb);
+    Ciphertext a, b;
+    enc.encrypt(pa, a);
+    enc.encrypt(pb, b);
+    Ciphertext r = a, d = a;
+    ref.multiply_inplace(r, b);
+    dev.multiply_inplace(d, b);
+    same("BFV multiply_inplace", r, d);
+    ref.relinearize_inplace(r, rlk);
+    dev.relinearize_inplace(d, rlk);
+    same("BFV relinearize_inplace", r, d);
+    ref.rotate_rows_inplace(r, 1, glk);
+    dev.rotate_rows_inplace(d, 1, glk);
+    same("BFV rotate_rows_inplace(+1)", r, d);
+    ref.rotate_rows_inplace(r, -5, glk); // NAF path
+    dev.rotate_rows_inplace(d, -5, glk);
+    same("BFV rotate_rows_inplace(-5, NAF)", r, d);
+    ref.rotate_columns_inplace(r, glk);
+    dev.rotate_columns_inplace(d, glk);
+    same("BFV rotate_columns_inplace", r, d);
+    {
+        Ciphertext r2 = a, d2 = a;
+        ref.square_inplace(r2);
+        dev.multiply_inplace(d2, d2);
+        same("BFV multiply_inplace(x, x) vs square", r2, d2);
+    }
+    expect_throw("BFV rotate_vector (CKKS only)", [&] { Ciphertext t = a; dev.rotate_vector_inplace(t, 1, glk); }, 1);
+    return failures;
+}
+
 int main()
 {
     try
     {
         run(8192, { 50, 40, 40, 40, 50 }, 1);
         run(4096, { 40, 30, 30, 30, 40, 40 }, 2);
+        run_bfv(4096);
+        run_bfv(8192);
     }
     catch (const exception &e)
     {
