@@ -89,6 +89,10 @@ struct gsb_ctx
     int device = 0;
     int logn = 0;
     size_t N = 0, K = 0, k = 0, L0 = 0;
+    // no-wrap bounds over q_max = max modulus, n = log2 N, beta0 = ceil(L0 / k) (see KsDev):
+    //   lazy_modup: q_max (2n + 1) < 2^64             (a lazy forward NTT grows by < 2p per stage)
+    //   lazy_mac:   beta0 (2n + 1) q_max^2 < 2^128    (sum of beta0 products operand x key)
+    bool lazy_modup = false, lazy_mac = false;
     std::vector<gsb::host::LimbTables> tables; // host copies (introspection + constants)
     gsb::Twiddle *d_WW = nullptr, *d_VV = nullptr;
     gsb::LimbC *d_limb = nullptr;

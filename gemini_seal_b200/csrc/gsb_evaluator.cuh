@@ -248,6 +248,8 @@ namespace gsb
         ks.E = static_cast<uint32_t>(L + ctx->k);
         ks.beta = static_cast<uint32_t>((L + ctx->k - 1) / ctx->k);
         ks.N = static_cast<uint32_t>(ctx->N);
+        ks.lazy_modup = ctx->lazy_modup && ctx->k == 1;
+        ks.lazy_mac = ctx->lazy_mac && ctx->k == 1;
         return ks;
     }
 
@@ -302,17 +304,31 @@ namespace gsb
         // Step 2 + first NTT pass of step 3 (:2310, :2322): mod-up fused into the column pass.
         if constexpr (two)
         {
-            IoPair<ModupLoadT<K1>, PlainStore<OUT_RAW>> io{ ModupArgs{ ks, coef }, PlainStoreArgs{ ext1, E * N } };
-            launch_fwd_cols<LOGN>(io, tab, ModMap{ iL, static_cast<int>(ctx->L0), 0 }, iE, static_cast<int>(B * beta), st, "modup");
+            const ModMap mup{ iL, static_cast<int>(ctx->L0), 0 };
+            if (K1 && ks.lazy_modup)
+            {
+                IoPair<ModupLoadT<K1, K1>, PlainStore<OUT_RAW>> io{ ModupArgs{ ks, coef }, PlainStoreArgs{ ext1, E * N } };
+                launch_fwd_cols<LOGN>(io, tab, mup, iE, static_cast<int>(B * beta), st, "modup");
+            }
+            else
+            {
+                IoPair<ModupLoadT<K1, false>, PlainStore<OUT_RAW>> io{ ModupArgs{ ks, coef }, PlainStoreArgs{ ext1, E * N } };
+                launch_fwd_cols<LOGN>(io, tab, mup, iE, static_cast<int>(B * beta), st, "modup");
+            }
         }
         // Step 3 + Barrett part of step 4: last NTT pass fused with the key inner product.
         {
             typedef MacPlan<LOGN> MP;
             KsMacArgs a{ ks, target, target_stride, coef, ext1, key.d, red, static_cast<uint32_t>(ctx->K) };
-            auto kfn = ks_mac_kernel<LOGN, K1>;
-            allow_smem(kfn, MP::smem_bytes);
             dim3 grid(static_cast<unsigned>(B), 1u << (LOGN - MP::T - 3), static_cast<unsigned>(E));
-            GSB_LAUNCH("ks_mac", "", kfn, grid, dim3(1 << MP::T), MP::smem_bytes, st, a, tab);
+            auto launch = [&](auto kfn) {
+                allow_smem(kfn, MP::smem_bytes);
+                GSB_LAUNCH("ks_mac", "", kfn, grid, dim3(1 << MP::T), MP::smem_bytes, st, a, tab);
+            };
+            if (K1 && ks.lazy_mac)
+                launch(ks_mac_kernel<LOGN, K1, K1>); // LAZY only exists for the k = 1 kernels
+            else
+                launch(ks_mac_kernel<LOGN, K1, false>);
         }
         // Step 4 (:2353-2357): lazy inverse NTT of the special slots.
         ntt_inverse_plain<LOGN>(

@@ -17,6 +17,15 @@ namespace gsb
         const uint64_t *neg_hat; // [L][k]
         const uint64_t *inv_p;   // [L][2]
         uint32_t L, L0, k, E, beta, N;
+        // Slack in the lazy ranges, used only where a bound fixed at context creation proves that no
+        // 64- or 128-bit intermediate can wrap (gsb_ctx::lazy_modup / lazy_mac): every word then stays
+        // congruent to the reference's, and since the inner product ends in a canonical Barrett-128 the
+        // outputs are identical.
+        //   lazy_modup: a single-limb bundle enters the NTT mod q_kap as it is (< q_max instead of
+        //               < q_kap): barrett_reduce_63 of multi_special_primes.cpp:104-107 is skipped
+        //               (compile-time LAZY of ModupCoreT, selected by the host from this flag).
+        //   lazy_mac:   the operand's last NTT stage skips reduceBarrettLazy (util/ntt.cpp:250-253).
+        uint32_t lazy_modup, lazy_mac;
         GSB_DEV int ext_mod(int kap) const { return kap < static_cast<int>(L) ? kap : static_cast<int>(L0) + kap - static_cast<int>(L); }
     };
 
@@ -66,7 +75,7 @@ namespace gsb
     // Source = coefficient-form bundle limbs coef[b][s0 .. s0+cnt); destination modulus = ext slot kap.
     // K1: the context has one special prime, so every bundle is a single limb and only the
     // copy / Barrett-63 path exists (keeps the k > 1 conversion code out of the k = 1 kernels).
-    template <bool K1>
+    template <bool K1, bool LAZY = false>
     struct ModupCoreT
     {
         const uint64_t *src; // coef + (b*L + s0)*N
@@ -91,7 +100,7 @@ namespace gsb
             q = c.q;
             cr0 = c.cr0;
             cr1 = c.cr1;
-            reduce = cnt == 1 && limb[0].q > q;
+            reduce = !LAZY && cnt == 1 && limb[0].q > q;
         }
         GSB_DEV uint64_t convert(uint32_t d) const
         {
@@ -136,12 +145,12 @@ namespace gsb
             return y >= s0 && y < s0 + static_cast<int>(ks.k) && y < static_cast<int>(ks.L);
         }
     };
-    template <bool K1>
-    struct ModupLoadT : ModupCoreT<K1>
+    template <bool K1, bool LAZY = false>
+    struct ModupLoadT : ModupCoreT<K1, LAZY>
     {
         typedef ModupArgs Args;
         GSB_DEV ModupLoadT(const Args &a, int y, int z, int, const LimbC &c, uint32_t)
-            : ModupCoreT<K1>(a.ks, a.coef, z / static_cast<int>(a.ks.beta), z % static_cast<int>(a.ks.beta), y, c)
+            : ModupCoreT<K1, LAZY>(a.ks, a.coef, z / static_cast<int>(a.ks.beta), z % static_cast<int>(a.ks.beta), y, c)
         {}
     };
 
@@ -411,7 +420,8 @@ namespace gsb
         GSB_DEV uint64_t xform(uint64_t v) const { return v; }
     };
 
-    template <int LOGN, bool K1>
+    // LAZY (see KsDev::lazy_mac): the operand's last stage skips reduceBarrettLazy.
+    template <int LOGN, bool K1, bool LAZY>
     __global__ void __launch_bounds__(1 << MacPlan<LOGN>::T, MacPlan<LOGN>::T <= 8 ? 2 : 1) ks_mac_kernel(KsMacArgs p, NttTables tab)
     {
         typedef MacPlan<LOGN> MP;
@@ -516,14 +526,14 @@ namespace gsb
             }
             else
             {
-                const ModupCoreT<K1> pro(ks, p.coef, b, j, kap, c);
+                const ModupCoreT<K1, LAZY> pro(ks, p.coef, b, j, kap, c);
                 xf_load_raw<T, MP::G_HI, 0, false>(x, tid, tile, map, pro);
 #pragma unroll
                 for (int r = 0; r < 8; r++)
                     x[r] = pro.xform(x[r]);
             }
             if (!direct)
-                fwd_compute<T, MP::G_HI, 0, true, 0>(x, smem, tid, tw, c, parity);
+                fwd_compute<T, MP::G_HI, 0, !LAZY, 0>(x, smem, tid, tw, c, parity);
             const uint64_t *k0, *k1;
             if constexpr (MP::two_pass)
             {
