@@ -207,6 +207,33 @@ def uniform_residues(torch, mods, lead, gen):
     return torch.stack(cols, dim=-2).contiguous()
 
 
+def bfv_config1(torch, g, lib, np, timed, batch=256):
+    """BASELINE config #1 shape (BFV, N = 4096, BFVDefault 109-bit modulus, t = 786433; parity is pinned by the
+    golden digests): device-resident ops/s of bfv_multiply, relinearize and rotate_rows on one GPU."""
+    n, mods, t = 4096, [68719403009, 68719230977, 137438822401], 786433
+    ctx = g.Context(n, mods, 1, device=torch.cuda.current_device(), lib=lib)
+    ev = g.BfvEvaluator(ctx, t)
+    gen = torch.Generator(device="cuda")
+    gen.manual_seed(4096)
+
+    def residues(ms, lead):
+        cols = [torch.randint(0, q, tuple(lead) + (n,), dtype=torch.int64, device="cuda", generator=gen) for q in ms]
+        return torch.stack(cols, dim=-2).contiguous()
+    ctx.set_relin_keys(residues(mods, (2, 2)).cpu().numpy().view(np.uint64))
+    elt = ctx.galois_elt_from_step(1)
+    ctx.set_galois_key(elt, residues(mods, (2, 2)).cpu().numpy().view(np.uint64))
+    a, b = residues(mods[:2], (batch, 2)), residues(mods[:2], (batch, 2))
+    c3 = ev.multiply(a, b)
+    out = {}
+    for name, fn in (("multiply", lambda: ev.multiply(a, b)), ("relinearize", lambda: ev.relinearize(c3)),
+                     ("rotate_rows", lambda: ev.apply_galois(a, elt))):
+        fn()
+        out[name + "_ops_per_s"] = batch * 5 / (timed(fn, 5) / 1e3)
+    out["batch"] = batch
+    ctx.close()
+    return out
+
+
 def run_ours(args):
     import numpy as np
     import torch
@@ -318,6 +345,8 @@ def run_ours(args):
     extra["limb_ntt_per_s"] = world * 2 * B * 2 * L * 3 / (timed(step_ntt, 3) / 1e3)
     assert torch.equal(work, a), "forward/inverse NTT round trip failed"
     del work, rot_out
+    if rank == 0:
+        extra["bfv_n4096"] = bfv_config1(torch, g, lib, np, timed)
 
     # ---- per-kernel CUDA-event timing of one more step -> roofline of the dominant kernel
     roofline, kernels = None, {}

@@ -244,6 +244,59 @@ class Evaluator:
             _check(self.lib, self.lib.gsb_apply_galois_host(self.ctx.handle, int(galois_elt), _ptr(c), _ptr(out), B, L))
         return out
 
+    # ---- thin compositions; ciphertext batches [B][size][L][N] ------------------
+    def add(self, a, b):
+        """add_inplace (evaluator.cpp:90-152) for equal-size operands."""
+        self._shape(a)
+        if tuple(a.shape) != tuple(b.shape):
+            raise ValueError("encrypted1 and encrypted2 parameter mismatch")
+        return poly_op(self.ctx, "add", a, b)
+
+    def sub(self, a, b):
+        """sub_inplace (evaluator.cpp:174-233) for equal-size operands."""
+        self._shape(a)
+        if tuple(a.shape) != tuple(b.shape):
+            raise ValueError("encrypted1 and encrypted2 parameter mismatch")
+        return poly_op(self.ctx, "sub", a, b)
+
+    def negate(self, a):
+        """negate_inplace (evaluator.cpp:65-88)."""
+        self._shape(a)
+        return poly_op(self.ctx, "negate", a)
+
+    def multiply_plain(self, c, plain):
+        """multiply_plain_ntt (evaluator.cpp:1605-1646): every component times an NTT-form plaintext [L][N]."""
+        B, size, L = self._shape(c)
+        if tuple(plain.shape) != (L, self.ctx.N):
+            raise ValueError("encrypted_ntt and plain_ntt parameter mismatch")
+        if _is_torch(c):
+            p = plain.expand(B, size, L, self.ctx.N).contiguous()
+        else:
+            p = np.ascontiguousarray(np.broadcast_to(plain, c.shape))
+        return poly_op(self.ctx, "dyadic", c, p)
+
+    def square(self, c):
+        """square_inplace (evaluator.cpp:529-558,704-770): the words of multiply(c, c)."""
+        return self.multiply(c, c)
+
+    def mod_switch_to_next(self, c):
+        """CKKS mod_switch_to_next = mod_switch_drop_to_next (evaluator.cpp:894-957): drops the last limb."""
+        B, size, L = self._shape(c)
+        if L < 2:
+            raise ValueError("end of modulus switching chain reached")
+        out = c[:, :, :L - 1, :]
+        return out.contiguous() if _is_torch(c) else np.ascontiguousarray(out)
+
+    def transform_to_ntt(self, c):
+        """transform_to_ntt_inplace (evaluator.cpp:1746-1792)."""
+        self._shape(c)
+        return ntt_negacyclic_harvey(c.clone() if _is_torch(c) else c.copy(), self.ctx)
+
+    def transform_from_ntt(self, c):
+        """transform_from_ntt_inplace (evaluator.cpp:1794-1840)."""
+        self._shape(c)
+        return inverse_ntt_negacyclic_harvey(c.clone() if _is_torch(c) else c.copy(), self.ctx)
+
     def rotate_vector(self, c, steps):
         """rotate_vector (evaluator.cpp:1945-2000) for a step whose Galois key is present."""
         if steps == 0:

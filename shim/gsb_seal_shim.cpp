@@ -155,6 +155,170 @@ namespace gsb_seal
         }
     }
 
+    // ---- elementwise ops and form / level changes ---------------------------------
+    // evaluator.cpp:65-88
+    void Evaluator::negate_inplace(Ciphertext &encrypted)
+    {
+        validate(encrypted, "encrypted");
+        const size_t L = level_limbs(encrypted);
+        check(gsb_poly_op_host(ctx_, GSB_OP_NEGATE, encrypted.data(), nullptr, nullptr, encrypted.data(), encrypted.size(), L, 0));
+#ifdef SEAL_THROW_ON_TRANSPARENT_CIPHERTEXT
+        if (encrypted.is_transparent())
+            throw logic_error("result ciphertext is transparent");
+#endif
+    }
+
+    // evaluator.cpp:90-152 (add), :174-233 (sub)
+    void Evaluator::add_sub(Ciphertext &encrypted1, const Ciphertext &encrypted2, bool subtract)
+    {
+        validate(encrypted1, "encrypted1");
+        validate(encrypted2, "encrypted2");
+        if (encrypted1.parms_id() != encrypted2.parms_id())
+            throw invalid_argument("encrypted1 and encrypted2 parameter mismatch");
+        if (encrypted1.is_ntt_form() != encrypted2.is_ntt_form())
+            throw invalid_argument("NTT form mismatch");
+        if (!seal::util::are_close<double>(encrypted1.scale(), encrypted2.scale())) // are_same_scale, evaluator.cpp:38-41
+            throw invalid_argument("scale mismatch");
+        auto &context_data = *context_->get_context_data(encrypted1.parms_id());
+        const size_t L = level_limbs(encrypted1), LN = L * N_;
+        const size_t s1 = encrypted1.size(), s2 = encrypted2.size(), lo = min(s1, s2), hi = max(s1, s2);
+        encrypted1.resize(context_, context_data.parms_id(), hi);
+        check(gsb_poly_op_host(ctx_, subtract ? GSB_OP_SUB : GSB_OP_ADD, encrypted1.data(), encrypted2.data(), nullptr, encrypted1.data(), lo, L, 0));
+        if (s1 < s2)
+        {
+            if (subtract) // remaining components of encrypted2 are negated (:222-226)
+                check(gsb_poly_op_host(ctx_, GSB_OP_NEGATE, encrypted2.data(lo), nullptr, nullptr, encrypted1.data(lo), s2 - lo, L, 0));
+            else
+                memcpy(encrypted1.data(lo), encrypted2.data(lo), (s2 - lo) * LN * sizeof(uint64_t));
+        }
+#ifdef SEAL_THROW_ON_TRANSPARENT_CIPHERTEXT
+        if (encrypted1.is_transparent())
+            throw logic_error("result ciphertext is transparent");
+#endif
+    }
+
+    void Evaluator::add_inplace(Ciphertext &encrypted1, const Ciphertext &encrypted2)
+    {
+        add_sub(encrypted1, encrypted2, false);
+    }
+
+    void Evaluator::sub_inplace(Ciphertext &encrypted1, const Ciphertext &encrypted2)
+    {
+        add_sub(encrypted1, encrypted2, true);
+    }
+
+    // evaluator.cpp:1438-1475 -> multiply_plain_ntt (:1605-1646); the coefficient-form branch is not served
+    void Evaluator::multiply_plain_inplace(Ciphertext &encrypted, const Plaintext &plain, MemoryPoolHandle pool)
+    {
+        validate(encrypted, "encrypted");
+        if (!is_metadata_valid_for(plain, context_) || !is_buffer_valid(plain))
+            throw invalid_argument("plain is not valid for encryption parameters");
+        if (encrypted.is_ntt_form() != plain.is_ntt_form())
+            throw invalid_argument("NTT form mismatch");
+        if (!pool)
+            throw invalid_argument("pool is uninitialized");
+        if (!encrypted.is_ntt_form())
+            throw logic_error("device multiply_plain serves NTT-form operands");
+        if (encrypted.parms_id() != plain.parms_id())
+            throw invalid_argument("encrypted_ntt and plain_ntt parameter mismatch");
+        auto &context_data = *context_->get_context_data(encrypted.parms_id());
+        const double new_scale = encrypted.scale() * plain.scale();
+        if (new_scale <= 0 || (static_cast<int>(log2(new_scale)) >= context_data.total_coeff_modulus_bit_count()))
+            throw invalid_argument("scale out of bounds");
+        const size_t L = level_limbs(encrypted);
+        for (size_t i = 0; i < encrypted.size(); i++)
+            check(gsb_poly_op_host(ctx_, GSB_OP_DYADIC, encrypted.data(i), plain.data(), nullptr, encrypted.data(i), 1, L, 0));
+        encrypted.scale() = new_scale;
+#ifdef SEAL_THROW_ON_TRANSPARENT_CIPHERTEXT
+        if (encrypted.is_transparent())
+            throw logic_error("result ciphertext is transparent");
+#endif
+    }
+
+    // evaluator.cpp:529-558: ckks_square / bfv_square give the words of multiply(x, x)
+    void Evaluator::square_inplace(Ciphertext &encrypted, MemoryPoolHandle pool)
+    {
+        multiply_inplace(encrypted, encrypted, move(pool));
+    }
+
+    // evaluator.cpp:1746-1792, :1794-1840
+    void Evaluator::transform_to_ntt_inplace(Ciphertext &encrypted)
+    {
+        validate(encrypted, "encrypted");
+        if (encrypted.is_ntt_form())
+            throw invalid_argument("encrypted is already in NTT form");
+        check(gsb_ntt_forward_host(ctx_, encrypted.data(), encrypted.size(), level_limbs(encrypted), 0, GSB_NTT_STRICT));
+        encrypted.is_ntt_form() = true;
+#ifdef SEAL_THROW_ON_TRANSPARENT_CIPHERTEXT
+        if (encrypted.is_transparent())
+            throw logic_error("result ciphertext is transparent");
+#endif
+    }
+
+    void Evaluator::transform_from_ntt_inplace(Ciphertext &encrypted_ntt)
+    {
+        validate(encrypted_ntt, "encrypted");
+        if (!encrypted_ntt.is_ntt_form())
+            throw invalid_argument("encrypted_ntt is not in NTT form");
+        check(gsb_ntt_inverse_host(ctx_, encrypted_ntt.data(), encrypted_ntt.size(), level_limbs(encrypted_ntt), 0, GSB_NTT_STRICT));
+        encrypted_ntt.is_ntt_form() = false;
+#ifdef SEAL_THROW_ON_TRANSPARENT_CIPHERTEXT
+        if (encrypted_ntt.is_transparent())
+            throw logic_error("result ciphertext is transparent");
+#endif
+    }
+
+    // evaluator.cpp:996-1036 -> CKKS: mod_switch_drop_to_next (:894-957), a copy of the first L-1 limbs
+    void Evaluator::mod_switch_to_next_inplace(Ciphertext &encrypted, MemoryPoolHandle pool)
+    {
+        validate(encrypted, "encrypted");
+        if (context_->last_parms_id() == encrypted.parms_id())
+            throw invalid_argument("end of modulus switching chain reached");
+        if (!pool)
+            throw invalid_argument("pool is uninitialized");
+        if (bfv_)
+            throw logic_error("device mod_switch_to_next serves CKKS");
+        if (!encrypted.is_ntt_form())
+            throw invalid_argument("CKKS encrypted must be in NTT form");
+        auto &context_data = *context_->get_context_data(encrypted.parms_id());
+        auto &next = *context_data.next_context_data();
+        if (encrypted.scale() <= 0 || (static_cast<int>(log2(encrypted.scale())) >= next.total_coeff_modulus_bit_count()))
+            throw invalid_argument("scale out of bounds");
+        const size_t L = level_limbs(encrypted), size = encrypted.size();
+        vector<uint64_t> temp(size * (L - 1) * N_);
+        for (size_t i = 0; i < size; i++)
+            memcpy(temp.data() + i * (L - 1) * N_, encrypted.data(i), (L - 1) * N_ * sizeof(uint64_t));
+        const double scale = encrypted.scale();
+        encrypted.resize(context_, next.parms_id(), size);
+        encrypted.is_ntt_form() = true;
+        encrypted.scale() = scale;
+        memcpy(encrypted.data(), temp.data(), temp.size() * sizeof(uint64_t));
+#ifdef SEAL_THROW_ON_TRANSPARENT_CIPHERTEXT
+        if (encrypted.is_transparent())
+            throw logic_error("result ciphertext is transparent");
+#endif
+    }
+
+    // evaluator.cpp:1128-1178
+    void Evaluator::rescale_to_inplace(Ciphertext &encrypted, parms_id_type parms_id, MemoryPoolHandle pool)
+    {
+        validate(encrypted, "encrypted");
+        auto context_data_ptr = context_->get_context_data(encrypted.parms_id());
+        auto target_context_data_ptr = context_->get_context_data(parms_id);
+        if (!context_data_ptr)
+            throw invalid_argument("encrypted is not valid for encryption parameters");
+        if (!target_context_data_ptr)
+            throw invalid_argument("parms_id is not valid for encryption parameters");
+        if (context_data_ptr->chain_index() < target_context_data_ptr->chain_index())
+            throw invalid_argument("cannot switch to higher level modulus");
+        if (!pool)
+            throw invalid_argument("pool is uninitialized");
+        if (bfv_)
+            throw invalid_argument("unsupported operation for scheme type");
+        while (encrypted.parms_id() != parms_id)
+            rescale_to_next_inplace(encrypted, pool);
+    }
+
     // ---- key upload ---------------------------------------------------------------------------------
     void Evaluator::upload_key(int kind, uint32_t slot, const vector<PublicKey> &bundles)
     {

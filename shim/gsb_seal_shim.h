@@ -42,6 +42,24 @@ namespace gsb_seal
             const seal::Ciphertext &encrypted1, const seal::Ciphertext &encrypted2, seal::Ciphertext &destination,
             seal::MemoryPoolHandle pool = seal::MemoryManager::GetPool());
 
+        // evaluator.h:72-206 / evaluator.cpp:65-233: negate, add, sub
+        void negate_inplace(seal::Ciphertext &encrypted);
+        void add_inplace(seal::Ciphertext &encrypted1, const seal::Ciphertext &encrypted2);
+        void sub_inplace(seal::Ciphertext &encrypted1, const seal::Ciphertext &encrypted2);
+        // evaluator.h:276-300 / evaluator.cpp:529-558: square = multiply(x, x)
+        void square_inplace(seal::Ciphertext &encrypted, seal::MemoryPoolHandle pool = seal::MemoryManager::GetPool());
+        // evaluator.h:780-815 / evaluator.cpp:1438-1475,1605-1646: NTT-form plaintext multiplication
+        void multiply_plain_inplace(
+            seal::Ciphertext &encrypted, const seal::Plaintext &plain, seal::MemoryPoolHandle pool = seal::MemoryManager::GetPool());
+        // evaluator.h:858-930 / evaluator.cpp:1746-1840
+        void transform_to_ntt_inplace(seal::Ciphertext &encrypted);
+        void transform_from_ntt_inplace(seal::Ciphertext &encrypted_ntt);
+        // evaluator.h:430-470 / evaluator.cpp:894-957,996-1036 (CKKS: drop the last limb)
+        void mod_switch_to_next_inplace(seal::Ciphertext &encrypted, seal::MemoryPoolHandle pool = seal::MemoryManager::GetPool());
+        // evaluator.h:600-640 / evaluator.cpp:1128-1178
+        void rescale_to_inplace(
+            seal::Ciphertext &encrypted, seal::parms_id_type parms_id, seal::MemoryPoolHandle pool = seal::MemoryManager::GetPool());
+
         // evaluator.h:344-378 / evaluator.cpp:772-827
         void relinearize_inplace(
             seal::Ciphertext &encrypted, const seal::RelinKeys &relin_keys,
@@ -96,6 +114,7 @@ namespace gsb_seal
     private:
         void validate(const seal::Ciphertext &ct, const char *what) const;
         void bfv_multiply(seal::Ciphertext &encrypted1, const seal::Ciphertext &encrypted2);
+        void add_sub(seal::Ciphertext &encrypted1, const seal::Ciphertext &encrypted2, bool subtract);
         std::size_t level_limbs(const seal::Ciphertext &ct) const;
         void ensure_relin(const seal::RelinKeys &keys, std::size_t index);
         void ensure_galois(const seal::GaloisKeys &keys, std::uint32_t elt);

@@ -81,6 +81,7 @@ static int run(size_t N, vector<int> bits, int k_special)
     Ciphertext a, b;
     enc.encrypt(pa, a);
     enc.encrypt(pb, b);
+    Plaintext pb_ntt = pb; // CKKSEncoder plaintexts are already in NTT form at the first level
 
     Ciphertext r = a, d = a;
     ref.multiply_inplace(r, b);
@@ -107,6 +108,43 @@ static int run(size_t N, vector<int> bits, int k_special)
         ref.square_inplace(r2);
         dev.multiply_inplace(d2, d2);
         same("multiply_inplace(x, x) vs square", r2, d2);
+    }
+    {
+        // row f3: thin ops on the same objects (r, d are equal size-2 ciphertexts at the second level)
+        Ciphertext r2 = a, d2 = a, r3 = a, d3 = a;
+        ref.multiply_inplace(r3, b);
+        dev.multiply_inplace(d3, b);
+        ref.add_inplace(r2, b);
+        dev.add_inplace(d2, b);
+        same("add_inplace", r2, d2);
+        r3.scale() = d3.scale() = r2.scale(); // scale is metadata only; sub requires equal scales
+        ref.sub_inplace(r2, r3);
+        dev.sub_inplace(d2, d3);
+        same("sub_inplace (size 2 - size 3)", r2, d2);
+        ref.negate_inplace(r2);
+        dev.negate_inplace(d2);
+        same("negate_inplace", r2, d2);
+        Ciphertext r4 = a, d4 = a;
+        ref.multiply_plain_inplace(r4, pb_ntt);
+        dev.multiply_plain_inplace(d4, pb_ntt);
+        same("multiply_plain_inplace (NTT)", r4, d4);
+        ref.transform_from_ntt_inplace(r4);
+        dev.transform_from_ntt_inplace(d4);
+        same("transform_from_ntt_inplace", r4, d4);
+        ref.transform_to_ntt_inplace(r4);
+        dev.transform_to_ntt_inplace(d4);
+        same("transform_to_ntt_inplace", r4, d4);
+        ref.mod_switch_to_next_inplace(r4);
+        dev.mod_switch_to_next_inplace(d4);
+        same("mod_switch_to_next_inplace", r4, d4);
+        Ciphertext r5 = a, d5 = a;
+        ref.square_inplace(r5);
+        dev.square_inplace(d5);
+        ref.relinearize_inplace(r5, rlk);
+        dev.relinearize_inplace(d5, rlk);
+        ref.rescale_to_inplace(r5, context->last_parms_id());
+        dev.rescale_to_inplace(d5, context->last_parms_id());
+        same("square + relin + rescale_to(last)", r5, d5);
     }
     {
         // batched extension vs three reference calls

@@ -70,3 +70,34 @@ def digest(a):
 NTT_KINDS = {  # (inverse, lazy) -> oracle kind
     (False, True): 0, (False, False): 1, (True, True): 2, (True, False): 3,
 }
+
+
+def check_thin_ops(lib, oracle, logn=11, to_device=None):
+    """add / sub / negate / multiply_plain / square / mod_switch_to_next /
+    transform_{to,from}_ntt of the Evaluator mirror against the oracle's word arithmetic and NTT.
+    `to_device` moves a numpy batch to the buffers under test (identity for host buffers)."""
+    import gemini_seal_b200 as g
+    to_device = to_device or (lambda x: x)
+    back = lambda x: x if isinstance(x, np.ndarray) else x.cpu().numpy().view(np.uint64)
+    N = 1 << logn
+    mods = mixed_moduli(logn, [50, 40, 45, 51])
+    L = 3
+    ctx = g.Context(N, mods, 1, lib=lib)
+    ev = g.Evaluator(ctx)
+    rng = np.random.default_rng(logn)
+    a, b = rand_poly(rng, mods[:L], (2, 2), N), rand_poly(rng, mods[:L], (2, 2), N)
+    plain = rand_poly(rng, mods[:L], (), N)
+    da, db = to_device(a), to_device(b)
+    per_limb = lambda op, x, y=None: np.stack(
+        [oracle.poly_op(op, mods[i], x[..., i, :], None if y is None else y[..., i, :]) for i in range(L)], axis=-2)
+    assert np.array_equal(back(ev.add(da, db)), per_limb(1, a, b))
+    assert np.array_equal(back(ev.sub(da, db)), per_limb(2, a, b))
+    assert np.array_equal(back(ev.negate(da)), per_limb(3, a))
+    assert np.array_equal(back(ev.multiply_plain(da, to_device(plain))), per_limb(0, a, np.broadcast_to(plain, a.shape)))
+    oc = oracle.context(logn, mods, 1)
+    assert np.array_equal(back(ev.square(da)), np.stack([oc.multiply(a[i], a[i]) for i in range(2)]))
+    assert np.array_equal(back(ev.mod_switch_to_next(da)), a[:, :, :L - 1, :])
+    coef = oracle.ntt_rns(logn, mods, a, 3)
+    assert np.array_equal(back(ev.transform_from_ntt(da)), coef)
+    assert np.array_equal(back(ev.transform_to_ntt(to_device(coef))), a)
+    ctx.close()

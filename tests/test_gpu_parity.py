@@ -139,6 +139,14 @@ def test_full_size_repeatability(cudalib, B):
     ctx.close()
 
 
+def test_thin_evaluator_ops(cudalib, oracle):
+    """Row f3 on host buffers (N = 2^13, two-pass NTT) and on device buffers (N = 2^12)."""
+    import torch
+    from common import check_thin_ops
+    check_thin_ops(cudalib, oracle, logn=13)
+    check_thin_ops(cudalib, oracle, logn=12, to_device=lambda x: torch.from_numpy(x.view(np.int64)).cuda())
+
+
 def test_error_convention(cudalib):
     """Argument errors -> ValueError (std::invalid_argument), evaluator.cpp:238-249,781-796,1872-1887."""
     import gemini_seal_b200 as g

@@ -26,3 +26,8 @@ def test_sim_exports_every_declared_symbol(simlib):
     from gemini_seal_b200 import _lib
     for sym in _lib.PROTOTYPES:
         assert hasattr(simlib, sym) or sym in _lib.CUDA_ONLY
+
+
+def test_sim_thin_evaluator_ops(simlib, oracle):
+    from common import check_thin_ops
+    check_thin_ops(simlib, oracle, logn=11)
