@@ -234,6 +234,37 @@ def bfv_config1(torch, g, lib, np, timed, batch=256):
     return out
 
 
+def ntt_sweep(torch, g, lib, timed, limbs=16, target_bytes=1 << 29):
+    """BASELINE config #2: strict forward + inverse limb-NTTs per second for N = 2^12..2^16 over `limbs` 59-bit
+    primes, batch sized to ~512 MiB (> L2).  Reported with the two rooflines of SURVEY 8(d): HBM (16 N bytes per
+    limb-NTT against the measured copy peak) and integer (butterflies/s)."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from common import ntt_primes
+    peak, _ = measured_peaks()
+    out = {}
+    for logn in (12, 13, 14, 15, 16):
+        n = 1 << logn
+        mods = ntt_primes(logn, 59, limbs)
+        ctx = g.Context(n, mods + ntt_primes(logn, 58, 1), 1, device=torch.cuda.current_device(), lib=lib)
+        polys = max(1, target_bytes // (limbs * n * 8))
+        cols = [torch.randint(0, q, (polys, n), dtype=torch.int64, device="cuda") for q in mods]
+        x = torch.stack(cols, dim=1).contiguous()
+        ref = x.clone()
+        stream = torch.cuda.current_stream().cuda_stream
+
+        def step():
+            lib.gsb_ntt_forward_dev(ctx.handle, x.data_ptr(), polys, limbs, 0, 0, stream)
+            lib.gsb_ntt_inverse_dev(ctx.handle, x.data_ptr(), polys, limbs, 0, 0, stream)
+        step()
+        per_s = 2 * polys * limbs * 3 / (timed(step, 3) / 1e3)
+        assert torch.equal(x, ref), "NTT round trip failed at N=2^%d" % logn
+        out["n%d" % n] = {"limb_ntt_per_s": per_s, "hbm_frac": per_s * 16 * n / 1e9 / peak,
+                          "butterflies_per_s": per_s * (n // 2) * logn, "polys": polys, "limbs": limbs}
+        ctx.close()
+        del x, ref, cols
+    return out
+
+
 def run_ours(args):
     import numpy as np
     import torch
@@ -347,6 +378,7 @@ def run_ours(args):
     del work, rot_out
     if rank == 0:
         extra["bfv_n4096"] = bfv_config1(torch, g, lib, np, timed)
+        extra["ntt_sweep"] = ntt_sweep(torch, g, lib, timed)
 
     # ---- per-kernel CUDA-event timing of one more step -> roofline of the dominant kernel
     roofline, kernels = None, {}
