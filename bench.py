@@ -279,7 +279,19 @@ def run_ours(args):
         raise SystemExit("bench.py: no CUDA device (there is no CPU fallback; use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
     if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        # stdout carries exactly one JSON line: NCCL prints its version banner to stdout while the
+        # communicator is created, so fd 1 points at stderr until that has happened
+        sys.stdout.flush()
+        saved = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+            dist.barrier()
+            torch.cuda.synchronize()
+        finally:
+            sys.stdout.flush()
+            os.dup2(saved, 1)
+            os.close(saved)
     lib = _lib.load()
     mods = moduli()
     B = args.batch
@@ -376,7 +388,7 @@ def run_ours(args):
     extra["limb_ntt_per_s"] = world * 2 * B * 2 * L * 3 / (timed(step_ntt, 3) / 1e3)
     assert torch.equal(work, a), "forward/inverse NTT round trip failed"
     del work, rot_out
-    if rank == 0:
+    if world == 1:  # `timed` synchronises all ranks, so single-rank extras only run in the 1-GPU bench
         extra["bfv_n4096"] = bfv_config1(torch, g, lib, np, timed)
         extra["ntt_sweep"] = ntt_sweep(torch, g, lib, timed)
 
