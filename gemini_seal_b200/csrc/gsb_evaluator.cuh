@@ -808,10 +808,21 @@ static int host_call(
         const size_t per_set = chunk * (w0 + w1 + wo);
         uint64_t *stage = static_cast<uint64_t *>(ctx->host_io.reserve(2 * per_set * sizeof(uint64_t)));
         cudaEvent_t *in_done = ctx->pipe_event, *run_done = ctx->pipe_event + 2, *out_done = ctx->pipe_event + 4;
-        size_t n = 0;
-        for (size_t b0 = 0; b0 < batch && rc == GSB_OK; b0 += chunk, n++)
+        // Chunk schedule: full chunks, then a halving tail.  The host->device copies run back to back
+        // and bound the call, so what matters is how little work is left once the last input byte has
+        // arrived: the last chunk's kernels and its copy-out.
+        std::vector<size_t> sizes;
+        size_t rem = batch;
+        for (; rem > chunk; rem -= chunk)
+            sizes.push_back(chunk);
+        for (; rem > 1; rem -= (rem + 1) / 2)
+            sizes.push_back((rem + 1) / 2);
+        if (rem)
+            sizes.push_back(rem);
+        size_t b0 = 0;
+        for (size_t n = 0; n < sizes.size() && rc == GSB_OK; b0 += sizes[n], n++)
         {
-            const size_t B = std::min(chunk, batch - b0);
+            const size_t B = sizes[n];
             const int set = static_cast<int>(n & 1);
             uint64_t *d0 = stage + set * per_set, *d1 = d0 + chunk * w0, *dout = d1 + chunk * w1;
             if (n >= 2) // the set's inputs are free once its previous kernels ran, its output once copied out
