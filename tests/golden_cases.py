@@ -36,6 +36,8 @@ EVAL = {
     "c4_n32768_default": (15, BFV_DEFAULT[32768], 1, 15, 1, 1),
     "n32768_k4_L12": (15, BFV_DEFAULT[32768], 4, 12, 1, 1),
     "n65536_k1_L2": (16, [59, 59, 59], 1, 2, 1, 1),
+    "n65536_k2_L3": (16, [50, 50, 50, 51, 51], 2, 3, 1, -1),
+    "n16384_k3_L5_ragged": (14, BFV_DEFAULT[16384], 3, 5, 1, 5),
 }
 # BFV branches (BASELINE config #1 = the first one): coefficient-form ciphertexts.
 # name -> (logn, moduli spec, k special, level L, batch, rotation step, plain modulus)
@@ -45,6 +47,8 @@ BFV = {
     "bfv_n1024_k1_L3": (10, [40, 40, 40, 41], 1, 3, 2, 3, 12289),
     "bfv_n8192_default": (13, BFV_DEFAULT[8192], 1, 4, 1, 1, 786433),
     "bfv_n16384_default": (14, BFV_DEFAULT[16384], 1, 8, 1, 1, 786433),
+    "bfv_n32768_default": (15, BFV_DEFAULT[32768], 1, 15, 1, 1, 786433),
+    "bfv_n4096_L1": (12, BFV_DEFAULT[4096], 1, 1, 1, 1, 65537),
 }
 
 # (logn, bits): 3 polys x 3 limbs, all four transforms
