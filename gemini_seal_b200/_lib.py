@@ -61,6 +61,8 @@ PROTOTYPES = {
     "gsb_bfv_multiply_dev": (i32, [vp, vp, u64, vp, vp, vp, sz, sz, vp]),
     "gsb_bfv_multiply_host": (i32, [vp, u64, vp, vp, vp, sz, sz]),
     "gsb_bfv_aux_base": (i32, [vp, sz, u64, u64p, sz, C.POINTER(sz)]),
+    "gsb_bfv_mod_switch_dev": (i32, [vp, vp, vp, sz, sz, sz, vp]),
+    "gsb_bfv_mod_switch_host": (i32, [vp, vp, vp, sz, sz, sz]),
     "gsb_bfv_relinearize_dev": (i32, [vp, vp, vp, vp, sz, sz, vp]),
     "gsb_bfv_apply_galois_dev": (i32, [vp, vp, u32, vp, vp, sz, sz, vp]),
     "gsb_bfv_relinearize_host": (i32, [vp, vp, vp, sz, sz]),

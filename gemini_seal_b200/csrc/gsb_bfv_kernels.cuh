@@ -131,4 +131,35 @@ namespace gsb
             }
         }
     }
+    // BFV mod_switch_to_next: RNSTool::divide_and_round_q_last_inplace (util/rns.cpp:731-775), coefficient
+    // form.  in = n_polys x [L][N] -> out = n_polys x [L-1][N]; one thread per output word.
+    struct BfvModSwitchArgs
+    {
+        const uint64_t *in;
+        uint64_t *out;
+        const LimbC *limb;          // [K]
+        const uint64_t *inv_qlast;  // [L-1] q_last^-1 mod q_i (rns.cpp:719-728)
+        uint32_t N, L;
+        size_t total; // n_polys * (L-1) * N
+    };
+
+    __global__ void __launch_bounds__(256) bfv_mod_switch_kernel(BfvModSwitchArgs p)
+    {
+        const size_t per = static_cast<size_t>(p.L - 1) * p.N;
+        const LimbC last = p.limb[p.L - 1];
+        const uint64_t half = last.q >> 1;
+        for (size_t t = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; t < p.total;
+             t += static_cast<size_t>(gridDim.x) * blockDim.x)
+        {
+            const size_t poly = t / per, rem = t - poly * per;
+            const uint32_t i = static_cast<uint32_t>(rem / p.N), d = static_cast<uint32_t>(rem - static_cast<size_t>(i) * p.N);
+            const uint64_t *src = p.in + poly * static_cast<size_t>(p.L) * p.N;
+            const LimbC m = p.limb[i];
+            const uint64_t l = barrett63(src[static_cast<size_t>(p.L - 1) * p.N + d] + half, last.q, last.cr1); // :747-751
+            uint64_t tmp = barrett63(l, m.q, m.cr1);                                                              // :758
+            tmp = sub_mod(tmp, barrett63(half, m.q, m.cr1), m.q);                                               // :760-764
+            const uint64_t v = sub_mod(src[static_cast<size_t>(i) * p.N + d], tmp, m.q);                        // :766-767
+            p.out[t] = mul_mod(v, __ldg(p.inv_qlast + i), m);                                                   // :770-772
+        }
+    }
 } // namespace gsb

@@ -686,6 +686,21 @@ int gsb_bfv_multiply_dev(
     });
 }
 
+int gsb_bfv_mod_switch_dev(gsb_ctx *ctx, const uint64_t *in, uint64_t *out, size_t batch, size_t size, size_t L, void *stream)
+{
+    return guarded([&] {
+        check_batch(ctx, batch, L, 2); // evaluator.cpp:1006-1009: needs a next level
+        require(in && out && size >= 1 && size <= 16, GSB_E_INVALID_ARG, "invalid ciphertext");
+        GSB_CUDA_CHECK(cudaSetDevice(ctx->device));
+        const KsLevelConsts &lc = ctx->consts_for(L);
+        BfvModSwitchArgs p{ in, out, ctx->d_limb, lc.d_inv_qlast, static_cast<uint32_t>(ctx->N), static_cast<uint32_t>(L),
+                            batch * size * (L - 1) * ctx->N };
+        GSB_LAUNCH("bfv_mod_switch", "", bfv_mod_switch_kernel, dim3(grid_for(p.total, 256)), dim3(256), 0,
+                   static_cast<cudaStream_t>(stream), p);
+        GSB_CUDA_CHECK(cudaGetLastError());
+    });
+}
+
 int gsb_bfv_apply_galois_dev(gsb_ctx *ctx, gsb_ws *ws, uint32_t galois_elt, const uint64_t *in, uint64_t *out, size_t batch, size_t L, void *stream)
 {
     return guarded([&] {
@@ -897,6 +912,14 @@ int gsb_bfv_aux_base(gsb_ctx *ctx, size_t L, uint64_t plain_modulus, uint64_t *m
         for (size_t i = 0; i < tool.bsk.size(); i++)
             moduli_out[i] = tool.bsk[i];
         *n_out = tool.bsk.size();
+    });
+}
+
+int gsb_bfv_mod_switch_host(gsb_ctx *ctx, const uint64_t *in, uint64_t *out, size_t batch, size_t size, size_t L)
+{
+    const size_t w = ctx ? size * ctx->N : 0;
+    return host_call(ctx, in, w * L, nullptr, 0, out, L ? w * (L - 1) : 0, batch, [&](gsb_ws *, uint64_t *di, uint64_t *, uint64_t *dout, size_t B, void *st) {
+        return gsb_bfv_mod_switch_dev(ctx, di, dout, B, size, L, st);
     });
 }
 

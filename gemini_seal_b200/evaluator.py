@@ -377,7 +377,19 @@ class BfvEvaluator(Evaluator):
         _check(self.lib, self.lib.gsb_bfv_aux_base(self.ctx.handle, L, self.plain_modulus, buf, 80, C.byref(n)))
         return [int(buf[i]) for i in range(n.value)]
 
+    def mod_switch_to_next(self, c):
+        """mod_switch_to_next, BFV: divide_and_round_q_last_inplace (util/rns.cpp:731-775)."""
+        B, size, L = self._shape(c)
+        if L < 2:
+            raise ValueError("end of modulus switching chain reached")
+        out = _empty_like(c, (B, size, L - 1, self.ctx.N))
+        if _is_torch(c):
+            _check(self.lib, self.lib.gsb_bfv_mod_switch_dev(self.ctx.handle, _ptr(c), _ptr(out), B, size, L, _stream()))
+        else:
+            _check(self.lib, self.lib.gsb_bfv_mod_switch_host(self.ctx.handle, _ptr(c), _ptr(out), B, size, L))
+        return out
+
     def _unsupported(self, *a, **k):
         raise NotImplementedError("not part of the BFV surface built so far (no CPU fallback)")
 
-    mul_relin_rescale = rescale_to_next = _unsupported
+    mul_relin_rescale = rescale_to_next = multiply_plain = _unsupported

@@ -177,6 +177,11 @@ int gsb_bfv_multiply_dev(gsb_ctx *ctx, gsb_ws *ws, uint64_t plain_modulus, const
 int gsb_bfv_multiply_host(gsb_ctx *ctx, uint64_t plain_modulus, const uint64_t *a, const uint64_t *b, uint64_t *out, size_t batch, size_t L);
 /* The moduli of Bsk = B u {m_sk} for (L, plain_modulus) (RNSTool::base_Bsk, util/rns.cpp:585-603). */
 int gsb_bfv_aux_base(gsb_ctx *ctx, size_t L, uint64_t plain_modulus, uint64_t *moduli_out, size_t cap, size_t *n_out);
+/* Evaluator::mod_switch_to_next, BFV branch: mod_switch_scale_to_next (evaluator.cpp:829-892) ->
+ * RNSTool::divide_and_round_q_last_inplace (util/rns.cpp:731-775): in = [batch][size][L][N] coefficient
+ * form -> out = [batch][size][L-1][N]. */
+int gsb_bfv_mod_switch_dev(gsb_ctx *ctx, const uint64_t *in, uint64_t *out, size_t batch, size_t size, size_t L, void *stream);
+int gsb_bfv_mod_switch_host(gsb_ctx *ctx, const uint64_t *in, uint64_t *out, size_t batch, size_t size, size_t L);
 int gsb_bfv_relinearize_host(gsb_ctx *ctx, const uint64_t *in, uint64_t *out, size_t batch, size_t L);
 int gsb_bfv_apply_galois_host(gsb_ctx *ctx, uint32_t galois_elt, const uint64_t *in, uint64_t *out, size_t batch, size_t L);
 

@@ -60,6 +60,7 @@ class Oracle:
         lib.so_apply_galois.argtypes = [vp, sz, u32, vp, vp, vp]
         lib.so_mul_relin_rescale.argtypes = [vp, sz, vp, vp, vp, vp]
         lib.so_relinearize_bfv.argtypes = [vp, sz, vp, vp, vp]
+        lib.so_bfv_mod_switch.argtypes = [vp, sz, sz, vp, vp]
         lib.so_bfv_multiply.argtypes = [i32, C.POINTER(u64), sz, u64, vp, vp, vp]
         lib.so_bfv_aux_base.argtypes = [i32, C.POINTER(u64), sz, u64, vp]
         lib.so_apply_galois_bfv.argtypes = [vp, sz, u32, vp, vp, vp]
@@ -197,6 +198,12 @@ class OracleCtx:
         assert self.lib.so_relinearize_bfv(self.h, L, _p(c3), _p(key), _p(out)) == 0
         return out
 
+    def mod_switch_bfv(self, c):
+        size, L = c.shape[0], c.shape[1]
+        out = np.empty((size, L - 1, self.N), dtype=np.uint64)
+        assert self.lib.so_bfv_mod_switch(self.h, L, size, _p(c), _p(out)) == 0
+        return out
+
     def apply_galois_bfv(self, c, elt, key):
         L = c.shape[1]
         out = np.empty((2, L, self.N), dtype=np.uint64)
@@ -234,6 +241,7 @@ class RefLib:
         lib.ref_relinearize.argtypes = [vp, sz, vp, vp]
         lib.ref_rescale.argtypes = [vp, sz, sz, vp, vp]
         lib.ref_apply_galois.argtypes = [vp, sz, u32, vp, vp]
+        lib.ref_mod_switch.argtypes = [vp, sz, sz, vp, vp]
         lib.ref_rotate.argtypes = [vp, sz, i32, vp, vp]
         lib.ref_mul_relin_rescale.argtypes = [vp, sz, vp, vp, vp]
         lib.ref_elt_from_step.argtypes = [vp, i32]
@@ -349,6 +357,12 @@ class RefCtx:
         size, L = c.shape[0], c.shape[1]
         out = np.empty((size, L - 1, self.N), dtype=np.uint64)
         self._run(self.lib.ref_rescale(self.h, L, size, _p(c), _p(out)))
+        return out
+
+    def mod_switch(self, c):
+        size, L = c.shape[0], c.shape[1]
+        out = np.empty((size, L - 1, self.N), dtype=np.uint64)
+        self._run(self.lib.ref_mod_switch(self.h, L, size, _p(c), _p(out)))
         return out
 
     def apply_galois(self, c, elt):

@@ -412,6 +412,17 @@ extern "C"
         });
     }
 
+    // mod_switch_to_next_inplace: in [size][L][N] -> out [size][L-1][N] (BFV: divide and round; CKKS: drop)
+    int ref_mod_switch(void *h, size_t L, size_t size, const uint64_t *in, uint64_t *out)
+    {
+        auto *c = static_cast<RefCtx *>(h);
+        return guarded([&] {
+            auto x = c->make_ct(in, size, L, std::pow(2.0, 20));
+            c->evaluator->mod_switch_to_next_inplace(x);
+            std::memcpy(out, x.data(), size * (L - 1) * c->N * 8);
+        });
+    }
+
     // apply_galois_inplace: in/out [2][L][N]
     int ref_apply_galois(void *h, size_t L, uint32_t elt, const uint64_t *in, uint64_t *out)
     {

@@ -756,6 +756,41 @@ int so_apply_galois_bfv(const so_ctx *c, size_t L, uint32_t elt, const uint64_t 
     return rc;
 }
 
+/* BFV mod_switch_to_next: mod_switch_scale_to_next (evaluator.cpp:829-892) ->
+ * RNSTool::divide_and_round_q_last_inplace (util/rns.cpp:731-775); coefficient form.
+ * in [size][L][N] -> out [size][L-1][N] */
+int so_bfv_mod_switch(const so_ctx *c, size_t L, size_t size, const uint64_t *in, uint64_t *out)
+{
+    if (L < 2 || L > c->L0)
+        return -1;
+    const size_t N = c->N;
+    const uint64_t qL = c->q[L - 1], half = qL >> 1;
+    uint64_t *last = (uint64_t *)malloc(N * 8);
+    for (size_t p = 0; p < size; p++)
+    {
+        const uint64_t *src = in + p * L * N;
+        uint64_t *dst = out + p * (L - 1) * N;
+        for (size_t d = 0; d < N; d++) /* :747-751 */
+            last[d] = so_barrett_reduce_63(src[(L - 1) * N + d] + half, qL, c->tab[L - 1].cr);
+        for (size_t i = 0; i + 1 < L; i++)
+        {
+            const uint64_t qi = c->q[i];
+            const uint64_t *cri = c->tab[i].cr;
+            const uint64_t half_mod = so_barrett_reduce_63(half, qi, cri); /* :760 */
+            uint64_t inv;
+            so_try_invert_uint_mod(qL, qi, &inv); /* rns.cpp:719-728 */
+            for (size_t d = 0; d < N; d++)
+            {
+                uint64_t t = so_barrett_reduce_63(last[d], qi, cri); /* modulo_poly_coeffs_63, :758 */
+                t = so_sub_uint_mod(t, half_mod, qi);                  /* :761-764 */
+                dst[i * N + d] = so_multiply_uint_mod(so_sub_uint_mod(src[i * N + d], t, qi), inv, qi, cri); /* :766-772 */
+            }
+        }
+    }
+    free(last);
+    return 0;
+}
+
 /* evaluator.cpp:772-827 (size 3 -> 2) */
 int so_relinearize(const so_ctx *c, size_t L, const uint64_t *in, const uint64_t *key, uint64_t *out)
 {

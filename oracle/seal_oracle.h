@@ -90,6 +90,8 @@ int so_apply_galois(const so_ctx *c, size_t L, uint32_t elt, const uint64_t *in,
 /* ---- BFV branches (coefficient-form ciphertexts) ----------------------- */
 int so_switch_key_bfv(const so_ctx *c, size_t L, uint64_t *enc, const uint64_t *target, const uint64_t *key);
 int so_relinearize_bfv(const so_ctx *c, size_t L, const uint64_t *in, const uint64_t *key, uint64_t *out);
+/* in [size][L][N] -> out [size][L-1][N] (util/rns.cpp:731-775) */
+int so_bfv_mod_switch(const so_ctx *c, size_t L, size_t size, const uint64_t *in, uint64_t *out);
 void so_apply_galois_coeff(int logn, uint32_t elt, uint64_t q, const uint64_t *in, uint64_t *out);
 int so_apply_galois_bfv(const so_ctx *c, size_t L, uint32_t elt, const uint64_t *in, const uint64_t *key, uint64_t *out);
 /* Evaluator::bfv_multiply (BEHZ, evaluator.cpp:274-445; seal_oracle_bfv.c): a, b [2][L][N] in

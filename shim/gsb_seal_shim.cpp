@@ -276,12 +276,27 @@ namespace gsb_seal
             throw invalid_argument("end of modulus switching chain reached");
         if (!pool)
             throw invalid_argument("pool is uninitialized");
-        if (bfv_)
-            throw logic_error("device mod_switch_to_next serves CKKS");
-        if (!encrypted.is_ntt_form())
-            throw invalid_argument("CKKS encrypted must be in NTT form");
         auto &context_data = *context_->get_context_data(encrypted.parms_id());
         auto &next = *context_data.next_context_data();
+        if (bfv_)
+        {
+            // mod_switch_scale_to_next (evaluator.cpp:829-892) -> divide_and_round_q_last_inplace
+            if (encrypted.is_ntt_form())
+                throw invalid_argument("BFV encrypted cannot be in NTT form");
+            const size_t Lb = level_limbs(encrypted), sz = encrypted.size();
+            vector<uint64_t> out(sz * (Lb - 1) * N_);
+            check(gsb_bfv_mod_switch_host(ctx_, encrypted.data(), out.data(), 1, sz, Lb));
+            encrypted.resize(context_, next.parms_id(), sz);
+            encrypted.is_ntt_form() = false;
+            memcpy(encrypted.data(), out.data(), out.size() * sizeof(uint64_t));
+#ifdef SEAL_THROW_ON_TRANSPARENT_CIPHERTEXT
+            if (encrypted.is_transparent())
+                throw logic_error("result ciphertext is transparent");
+#endif
+            return;
+        }
+        if (!encrypted.is_ntt_form())
+            throw invalid_argument("CKKS encrypted must be in NTT form");
         if (encrypted.scale() <= 0 || (static_cast<int>(log2(encrypted.scale())) >= next.total_coeff_modulus_bit_count()))
             throw invalid_argument("scale out of bounds");
         const size_t L = level_limbs(encrypted), size = encrypted.size();

@@ -261,6 +261,22 @@ static int run_bfv(size_t N)
         dev.multiply_inplace(d2, d2);
         same("BFV multiply_inplace(x, x) vs square", r2, d2);
     }
+    {
+        Ciphertext r2 = a, d2 = a;
+        ref.multiply_inplace(r2, b);
+        dev.multiply_inplace(d2, b);
+        ref.mod_switch_to_next_inplace(r2); // size 3
+        dev.mod_switch_to_next_inplace(d2);
+        same("BFV mod_switch_to_next_inplace", r2, d2);
+        Ciphertext r3 = a, d3 = a;
+        ref.add_inplace(r3, b);
+        dev.add_inplace(d3, b);
+        ref.sub_inplace(r3, a);
+        dev.sub_inplace(d3, a);
+        ref.negate_inplace(r3);
+        dev.negate_inplace(d3);
+        same("BFV add / sub / negate", r3, d3);
+    }
     expect_throw("BFV rotate_vector (CKKS only)", [&] { Ciphertext t = a; dev.rotate_vector_inplace(t, 1, glk); }, 1);
     return failures;
 }

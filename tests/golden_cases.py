@@ -111,6 +111,8 @@ def run_case(name, be):
         c3 = be.multiply(c["a"], c["b"])
         out["bfv_multiply"] = digest(c3)
         out["bfv_relinearize"] = digest(be.relinearize(c3))
+        if c["L"] >= 2:
+            out["bfv_mod_switch"] = digest(be.mod_switch(c3))
         out["bfv_rotate_rows"] = digest(be.apply_galois(c["a"], elt))
         out["bfv_rotate_columns"] = digest(be.apply_galois(c["b"], conj))
         return out
@@ -166,6 +168,9 @@ class OracleBackend(_PerCt):
     def rescale(self, c):
         return self.each(self.c.rescale, c)
 
+    def mod_switch(self, c):
+        return self.each(self.c.mod_switch_bfv, c)
+
     def mul_relin_rescale(self, a, b):
         return self.each(lambda x, y: self.c.mul_relin_rescale(x, y, self.relin), a, b)
 
@@ -208,6 +213,9 @@ class RefBackend(_PerCt):
 
     def rescale(self, c):
         return self.each(self.c.rescale, c)
+
+    def mod_switch(self, c):
+        return self.each(self.c.mod_switch, c)
 
     def mul_relin_rescale(self, a, b):
         return self.each(self.c.mul_relin_rescale, a, b)
@@ -261,6 +269,9 @@ class DeviceBackend:
 
     def rescale(self, c):
         return self.ev.rescale_to_next(c)
+
+    def mod_switch(self, c):
+        return self.ev.mod_switch_to_next(c)
 
     def mul_relin_rescale(self, a, b):
         return self.ev.mul_relin_rescale(a, b)
