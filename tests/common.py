@@ -101,3 +101,60 @@ def check_thin_ops(lib, oracle, logn=11, to_device=None):
     assert np.array_equal(back(ev.transform_from_ntt(da)), coef)
     assert np.array_equal(back(ev.transform_to_ntt(to_device(coef))), a)
     ctx.close()
+
+
+def fuzz_against_oracle(lib, oracle, seed, n_configs, max_logn=13):
+    """Random parameter sets (N, #primes, bit sizes incl. 57..59-bit ones that disable the lazy-range
+    shortcuts, k special primes, level L with ragged last bundle, batch, rotation step; CKKS and BFV)
+    through the C ABI against the oracle, array by array."""
+    import gemini_seal_b200 as g
+    rng = np.random.default_rng(seed)
+    for _ in range(n_configs):
+        logn = int(rng.integers(10, max_logn + 1))
+        N = 1 << logn
+        k = int(rng.integers(1, 4))
+        L0 = int(rng.integers(1, 7))
+        wide = bool(rng.integers(0, 4) == 0)
+        bits = [int(b) for b in rng.integers(57, 60, size=L0 + k)] if wide else [int(b) for b in rng.integers(30, 56, size=L0 + k)]
+        mods = mixed_moduli(logn, bits)
+        L = int(rng.integers(1, L0 + 1))
+        batch = int(rng.integers(1, 4))
+        step = int(rng.integers(1, N // 2)) * (1 if rng.integers(0, 2) else -1)
+        beta0 = (L0 + k - 1) // k
+        what = (logn, bits, k, L, batch, step)
+        ctx = g.Context(N, mods, k, lib=lib)
+        oc = oracle.context(logn, mods, k)
+        relin, gal = rand_key(rng, mods, beta0, N), rand_key(rng, mods, beta0, N)
+        ctx.set_relin_keys(relin)
+        elt = ctx.galois_elt_from_step(step)
+        assert elt == oracle.elt_from_step(logn, step), what
+        ctx.set_galois_key(elt, gal)
+        a, b = rand_poly(rng, mods[:L], (batch, 2), N), rand_poly(rng, mods[:L], (batch, 2), N)
+        ev = g.Evaluator(ctx)
+        c3 = ev.multiply(a, b)
+        for i in range(batch):
+            assert np.array_equal(c3[i], oc.multiply(a[i], b[i])), ("multiply", what)
+        c2 = ev.relinearize(c3)
+        rot = ev.apply_galois(a, elt)
+        for i in range(batch):
+            assert np.array_equal(c2[i], oc.relinearize(c3[i], relin)), ("relinearize", what)
+            assert np.array_equal(rot[i], oc.apply_galois(a[i], elt, gal)), ("apply_galois", what)
+        if L >= 2:
+            rs = ev.rescale_to_next(c3)
+            for i in range(batch):
+                assert np.array_equal(rs[i], oc.rescale(c3[i])), ("rescale", what)
+        # the BFV branches on the same context (plain modulus below every prime)
+        t = int(rng.choice([65537, 786433, 12289]))
+        bev = g.BfvEvaluator(ctx, t)
+        b3 = bev.multiply(a, b)
+        b2 = bev.relinearize(b3)
+        brot = bev.apply_galois(a, elt)
+        for i in range(batch):
+            assert np.array_equal(b3[i], oracle.bfv_multiply(logn, mods, t, a[i], b[i])), ("bfv multiply", what, t)
+            assert np.array_equal(b2[i], oc.relinearize_bfv(b3[i], relin)), ("bfv relinearize", what)
+            assert np.array_equal(brot[i], oc.apply_galois_bfv(a[i], elt, gal)), ("bfv apply_galois", what)
+        if L >= 2:
+            ms = bev.mod_switch_to_next(b3)
+            for i in range(batch):
+                assert np.array_equal(ms[i], oc.mod_switch_bfv(b3[i])), ("bfv mod_switch", what)
+        ctx.close()

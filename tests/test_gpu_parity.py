@@ -147,6 +147,13 @@ def test_thin_evaluator_ops(cudalib, oracle):
     check_thin_ops(cudalib, oracle, logn=12, to_device=lambda x: torch.from_numpy(x.view(np.int64)).cuda())
 
 
+@pytest.mark.parametrize("seed", [1, 2, 3])
+def test_fuzz_against_oracle(cudalib, oracle, seed):
+    """Random parameter sets (k = 1..3, ragged bundles, 30..60-bit primes, CKKS + BFV) vs the oracle."""
+    from common import fuzz_against_oracle
+    fuzz_against_oracle(cudalib, oracle, seed=seed, n_configs=12, max_logn=14)
+
+
 def test_error_convention(cudalib):
     """Argument errors -> ValueError (std::invalid_argument), evaluator.cpp:238-249,781-796,1872-1887."""
     import gemini_seal_b200 as g

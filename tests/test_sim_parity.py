@@ -31,3 +31,8 @@ def test_sim_exports_every_declared_symbol(simlib):
 def test_sim_thin_evaluator_ops(simlib, oracle):
     from common import check_thin_ops
     check_thin_ops(simlib, oracle, logn=11)
+
+
+def test_sim_fuzz_against_oracle(simlib, oracle):
+    from common import fuzz_against_oracle
+    fuzz_against_oracle(simlib, oracle, seed=2024, n_configs=24, max_logn=13)
