@@ -68,6 +68,7 @@ namespace gsb
         __syncthreads();
     }
     GSB_DEV void fence_proxy_async() {}
+    GSB_DEV void prefetch_l2(const void *) {}
 #else
     GSB_DEV uint32_t smem_u32(const void *p)
     {
@@ -92,6 +93,11 @@ namespace gsb
     GSB_DEV void fence_proxy_async()
     {
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    // pulls the line holding p towards L2 / L1 without a destination register
+    GSB_DEV void prefetch_l2(const void *p)
+    {
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
     }
     GSB_DEV void mbar_wait(uint64_t *bar, uint32_t parity)
     {

@@ -255,6 +255,12 @@ namespace gsb
             const uint64_t addend = s ? (table ? s[__ldg(table + d)] : s[d]) : 0;
             return add_mod(val, addend, q);
         }
+        GSB_DEV void prefetch(uint32_t d) const
+        {
+            prefetch_l2(r + d);
+            if (s && !table)
+                prefetch_l2(s + d);
+        }
         GSB_DEV uint64_t one(uint32_t d, uint64_t v) const { return fin(d, r[d] + v); }
         GSB_DEV void store(uint32_t d, uint64_t v, int) const { o[d] = one(d, v); }
         GSB_DEV void store2(uint32_t d, uint64_t a, uint64_t b, int) const
@@ -356,6 +362,7 @@ namespace gsb
             : in(a.in + (static_cast<size_t>(z) * a.L + y) * N), out(a.out + (static_cast<size_t>(z) * (a.L - 1) + y) * N),
               q(c.q), cr0(c.cr0), cr1(c.cr1), four_q(c.q << 2), inv(a.inv_qlast[y])
         {}
+        GSB_DEV void prefetch(uint32_t d) const { prefetch_l2(in + d); }
         GSB_DEV uint64_t one(uint64_t u, uint64_t v) const { return mul_mod(u + four_q - v, inv, q, cr0, cr1); }
         GSB_DEV void store(uint32_t d, uint64_t v, int) const { out[d] = one(in[d], v); }
         GSB_DEV void store2(uint32_t d, uint64_t a, uint64_t b, int) const

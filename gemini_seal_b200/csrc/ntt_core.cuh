@@ -17,6 +17,8 @@
 //   forward : W[m + group]                      (root_powers, bit-reversed order)
 //   inverse : V[N - 2m + 1 + group]             (inv_root_powers, re-ordered at ntt.cpp:85-96)
 #pragma once
+#include <type_traits>
+#include <utility>
 #include "modarith.cuh"
 
 namespace gsb
@@ -395,6 +397,34 @@ namespace gsb
         }
     }
 
+    // Epilogues that read extra operands may offer prefetch(d): called for the elements the thread will
+    // store, before its butterflies, so those operands are on their way while the integer pipe works.
+    template <class E, class = void>
+    struct has_prefetch : std::false_type
+    {};
+    template <class E>
+    struct has_prefetch<E, std::void_t<decltype(std::declval<const E &>().prefetch(0u))>> : std::true_type
+    {};
+
+    template <int TOP, int R, int T_LOG, class Map, class Epi>
+    GSB_DEV void tile_prefetch(uint32_t tid, uint32_t tile, const Map &map, const Epi &epi)
+    {
+        constexpr int low = TOP - R + 1;
+#pragma unroll
+        for (int sub = 0; sub < (8 >> R); sub++)
+        {
+            const uint32_t base = group_base<TOP, R, T_LOG>(tid, sub);
+            if (low == 0 && R == 3)
+                epi.prefetch(map.coeff(tile, base)); // 8 adjacent words: one 64-byte segment
+            else
+            {
+#pragma unroll
+                for (int i = 0; i < (1 << R); i++)
+                    epi.prefetch(map.coeff(tile, base + (static_cast<uint32_t>(i) << low)));
+            }
+        }
+    }
+
     // Loads / stores of a whole transform (first / last executed round's layout).
     template <int T_LOG, int G_HI, int G_LO, bool INVERSE, class Map, class Pro>
     GSB_DEV void xf_load_raw(uint64_t (&x)[8], uint32_t tid, uint32_t tile, const Map &map, const Pro &pro)
@@ -402,6 +432,13 @@ namespace gsb
         constexpr int NS = G_HI - G_LO + 1;
         constexpr int PI = RoundPlan<NS, INVERSE>::first;
         tile_load_raw<G_HI - plan_before(NS, PI), plan_size(NS, PI), T_LOG>(x, tid, tile, map, pro);
+    }
+    template <int T_LOG, int G_HI, int G_LO, bool INVERSE, class Map, class Epi>
+    GSB_DEV void xf_prefetch(uint32_t tid, uint32_t tile, const Map &map, const Epi &epi)
+    {
+        constexpr int NS = G_HI - G_LO + 1;
+        constexpr int PI = RoundPlan<NS, INVERSE>::last;
+        tile_prefetch<G_HI - plan_before(NS, PI), plan_size(NS, PI), T_LOG>(tid, tile, map, epi);
     }
     template <int T_LOG, int G_HI, int G_LO, bool INVERSE, class Map, class Epi>
     GSB_DEV void xf_store(const uint64_t (&x)[8], uint32_t tid, uint32_t tile, const Map &map, const Epi &epi)

@@ -160,11 +160,13 @@ namespace gsb
                     xf_load_raw<T_LOG, G_HI, G_LO, INVERSE>(xn, tid, tile, map, pro);
                 }
 #endif
+                const typename IO::Epi epi(io, y, z, mod, c, N);
+                if constexpr (has_prefetch<typename IO::Epi>::value)
+                    xf_prefetch<T_LOG, G_HI, G_LO, INVERSE>(tid, tile, map, epi);
                 if constexpr (INVERSE)
                     inv_compute<T_LOG, G_HI, G_LO, LAST, 0>(x, smem, tid, tw, c, parity);
                 else
                     fwd_compute<T_LOG, G_HI, G_LO, LAST, 0>(x, smem, tid, tw, c, parity);
-                const typename IO::Epi epi(io, y, z, mod, c, N);
                 xf_store<T_LOG, G_HI, G_LO, INVERSE>(x, tid, tile, map, epi);
 #if !GSB_PREFETCH
                 if (zn < z1)
