@@ -2,7 +2,7 @@
  *
  * This is the drop-in boundary: plain pointers and sizes, no C++ or torch types.  Each entry
  * point names the reference interface it replaces (paths relative to
- * /root/reference/native/src/seal/).  The C++ shim (gemini_seal_b200/shim) and the Python host
+ * /root/reference/native/src/seal/).  The C++ shim (shim/gsb_seal_shim.{h,cpp}) and the Python host
  * mirror (gemini_seal_b200/evaluator.py) are thin callers of exactly these functions.
  *
  * Conventions (modelled on the reference's own C layer, c/defines.h:27-56, c/evaluator.cpp:31-58):
@@ -17,6 +17,10 @@
  *   - a context is immutable after creation/key upload and may be shared by host threads as long
  *     as each thread uses its own stream AND its own workspace (gsb_ws_*); the built-in default
  *     workspace serialises callers that pass ws = NULL.
+ *   - ciphertext and key words must be canonical residues (word < its limb's modulus), which is what
+ *     the reference's is_buffer_valid (valcheck.cpp) demands before any Evaluator call; the shim and
+ *     gsb_key_upload check it, the device entry points do not scan their inputs.  On such inputs
+ *     every output word equals the reference's.
  *   - there is no CPU fallback: every compute entry point fails with GSB_E_CUDA if no CUDA
  *     device is usable.
  */
