@@ -135,6 +135,29 @@ class Context:
         return t
 
 
+class Workspace:
+    """Device scratch for the *_dev entry points: the stand-in for the MemoryPoolHandle argument of
+    the reference's Evaluator methods (evaluator.h:246).  One per host thread / CUDA stream; an
+    Evaluator built without one shares the context's default workspace (single stream only)."""
+
+    def __init__(self, context):
+        self.ctx = context
+        h = C.c_void_p()
+        _check(context.lib, context.lib.gsb_ws_create(context.handle, C.byref(h)))
+        self.handle = h
+
+    def close(self):
+        if getattr(self, "handle", None) and self.ctx.handle:
+            self.ctx.lib.gsb_ws_destroy(self.handle)
+        self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
 def _ntt(ctx, data, limb_offset, lazy, inverse):
     if data.ndim < 2 or data.shape[-1] != ctx.N:
         raise ValueError("data must be [..., n_limbs, N]")
@@ -191,9 +214,14 @@ def poly_op(ctx, op, a, b=None, scalars=None, limb_offset=0):
 class Evaluator:
     """Mirror of seal::Evaluator for the CKKS hot path (evaluator.h:246,344,565,984,1201,1269)."""
 
-    def __init__(self, context):
+    def __init__(self, context, workspace=None):
         self.ctx = context
         self.lib = context.lib
+        self.workspace = workspace  # keeps it alive; None = the context's default workspace
+
+    @property
+    def _ws(self):
+        return self.workspace.handle if self.workspace is not None else None
 
     def _shape(self, x, size=None):
         if x.ndim != 4 or x.shape[-1] != self.ctx.N or (size is not None and x.shape[1] != size):
@@ -217,7 +245,7 @@ class Evaluator:
         B, _, L = self._shape(c, 3)
         out = _empty_like(c, (B, 2, L, self.ctx.N))
         if _is_torch(c):
-            _check(self.lib, self.lib.gsb_relinearize_dev(self.ctx.handle, None, _ptr(c), _ptr(out), B, L, _stream()))
+            _check(self.lib, self.lib.gsb_relinearize_dev(self.ctx.handle, self._ws, _ptr(c), _ptr(out), B, L, _stream()))
         else:
             _check(self.lib, self.lib.gsb_relinearize_host(self.ctx.handle, _ptr(c), _ptr(out), B, L))
         return out
@@ -229,7 +257,7 @@ class Evaluator:
             raise ValueError("end of modulus switching chain reached")
         out = _empty_like(c, (B, size, L - 1, self.ctx.N))
         if _is_torch(c):
-            _check(self.lib, self.lib.gsb_rescale_dev(self.ctx.handle, None, _ptr(c), _ptr(out), B, size, L, _stream()))
+            _check(self.lib, self.lib.gsb_rescale_dev(self.ctx.handle, self._ws, _ptr(c), _ptr(out), B, size, L, _stream()))
         else:
             _check(self.lib, self.lib.gsb_rescale_host(self.ctx.handle, _ptr(c), _ptr(out), B, size, L))
         return out
@@ -239,7 +267,7 @@ class Evaluator:
         B, _, L = self._shape(c, 2)
         out = _empty_like(c, tuple(c.shape))
         if _is_torch(c):
-            _check(self.lib, self.lib.gsb_apply_galois_dev(self.ctx.handle, None, int(galois_elt), _ptr(c), _ptr(out), B, L, _stream()))
+            _check(self.lib, self.lib.gsb_apply_galois_dev(self.ctx.handle, self._ws, int(galois_elt), _ptr(c), _ptr(out), B, L, _stream()))
         else:
             _check(self.lib, self.lib.gsb_apply_galois_host(self.ctx.handle, int(galois_elt), _ptr(c), _ptr(out), B, L))
         return out
@@ -316,7 +344,7 @@ class Evaluator:
             raise ValueError("end of modulus switching chain reached")
         out = _empty_like(a, (B, 2, L - 1, self.ctx.N))
         if _is_torch(a):
-            _check(self.lib, self.lib.gsb_mul_relin_rescale_dev(self.ctx.handle, None, _ptr(a), _ptr(b), _ptr(out), B, L, _stream()))
+            _check(self.lib, self.lib.gsb_mul_relin_rescale_dev(self.ctx.handle, self._ws, _ptr(a), _ptr(b), _ptr(out), B, L, _stream()))
         else:
             _check(self.lib, self.lib.gsb_mul_relin_rescale_host(self.ctx.handle, _ptr(a), _ptr(b), _ptr(out), B, L))
         return out
@@ -331,7 +359,7 @@ class BfvEvaluator(Evaluator):
         B, _, L = self._shape(c, 3)
         out = _empty_like(c, (B, 2, L, self.ctx.N))
         if _is_torch(c):
-            _check(self.lib, self.lib.gsb_bfv_relinearize_dev(self.ctx.handle, None, _ptr(c), _ptr(out), B, L, _stream()))
+            _check(self.lib, self.lib.gsb_bfv_relinearize_dev(self.ctx.handle, self._ws, _ptr(c), _ptr(out), B, L, _stream()))
         else:
             _check(self.lib, self.lib.gsb_bfv_relinearize_host(self.ctx.handle, _ptr(c), _ptr(out), B, L))
         return out
@@ -340,7 +368,7 @@ class BfvEvaluator(Evaluator):
         B, _, L = self._shape(c, 2)
         out = _empty_like(c, tuple(c.shape))
         if _is_torch(c):
-            _check(self.lib, self.lib.gsb_bfv_apply_galois_dev(self.ctx.handle, None, int(galois_elt), _ptr(c), _ptr(out), B, L, _stream()))
+            _check(self.lib, self.lib.gsb_bfv_apply_galois_dev(self.ctx.handle, self._ws, int(galois_elt), _ptr(c), _ptr(out), B, L, _stream()))
         else:
             _check(self.lib, self.lib.gsb_bfv_apply_galois_host(self.ctx.handle, int(galois_elt), _ptr(c), _ptr(out), B, L))
         return out
@@ -353,8 +381,8 @@ class BfvEvaluator(Evaluator):
         """rotate_columns (evaluator.h:1147-1176): Galois element 2N-1."""
         return self.apply_galois(c, 2 * self.ctx.N - 1)
 
-    def __init__(self, context, plain_modulus):
-        super().__init__(context)
+    def __init__(self, context, plain_modulus, workspace=None):
+        super().__init__(context, workspace)
         self.plain_modulus = int(plain_modulus)
 
     def multiply(self, a, b):
@@ -364,7 +392,7 @@ class BfvEvaluator(Evaluator):
             raise ValueError("encrypted1 and encrypted2 parameter mismatch")
         out = _empty_like(a, (B, 3, L, self.ctx.N))
         if _is_torch(a):
-            _check(self.lib, self.lib.gsb_bfv_multiply_dev(self.ctx.handle, None, self.plain_modulus, _ptr(a), _ptr(b), _ptr(out), B, L, _stream()))
+            _check(self.lib, self.lib.gsb_bfv_multiply_dev(self.ctx.handle, self._ws, self.plain_modulus, _ptr(a), _ptr(b), _ptr(out), B, L, _stream()))
         else:
             _check(self.lib, self.lib.gsb_bfv_multiply_host(self.ctx.handle, self.plain_modulus, _ptr(a), _ptr(b), _ptr(out), B, L))
         return out

@@ -15,8 +15,9 @@
  *     stream) without synchronising; *_host functions take HOST pointers, copy in, run, copy out
  *     and synchronise before returning;
  *   - a context is immutable after creation/key upload and may be shared by host threads as long
- *     as each thread uses its own stream AND its own workspace (gsb_ws_*); the built-in default
- *     workspace serialises callers that pass ws = NULL.
+ *     as each thread uses its own stream AND its own workspace (gsb_ws_*).  Calls that pass
+ *     ws = NULL share the context's default workspace: they must all be enqueued on one stream
+ *     (or be serialised by the caller); the *_host entry points take a per-context lock.
  *   - ciphertext and key words must be canonical residues (word < its limb's modulus), which is what
  *     the reference's is_buffer_valid (valcheck.cpp) demands before any Evaluator call; the shim and
  *     gsb_key_upload check it, the device entry points do not scan their inputs.  On such inputs

@@ -182,3 +182,52 @@ def test_error_convention(cudalib):
     with pytest.raises(ValueError):
         g.Context(1024, [97, 193], 1, lib=cudalib)  # 97 is not 1 mod 2N
     ctx.close()
+
+
+def test_concurrent_host_threads(cudalib):
+    """Thread-safety contract of include/gseal_b200.h: one context shared by four host threads, each with
+    its own stream and workspace, running CKKS and BFV key switches at the same time (ctypes drops the
+    GIL inside the calls), must give exactly the words the same calls give one after another."""
+    import threading
+    import torch
+    import gemini_seal_b200 as g
+    mods = golden_cases.BFV_DEFAULT[8192]
+    N, L, B, t = 8192, len(mods) - 1, 6, 65537
+    ctx = g.Context(N, mods, 1, lib=cudalib)
+    rng = np.random.default_rng(21)
+    ctx.set_relin_keys(rand_key(rng, mods, L, N))
+    elt = ctx.galois_elt_from_step(3)
+    ctx.set_galois_key(elt, rand_key(rng, mods, L, N))
+    dev = lambda x: torch.from_numpy(x.view(np.int64)).cuda()
+    ins = [(dev(rand_poly(rng, mods[:L], (B, 2), N)), dev(rand_poly(rng, mods[:L], (B, 2), N))) for _ in range(4)]
+
+    def work(i, ev, bfv):
+        a, b = ins[i]
+        return [ev.mul_relin_rescale(a, b), ev.apply_galois(a, elt), bfv.relinearize(bfv.multiply(a, b)),
+                bfv.apply_galois(b, elt)]
+
+    ev0, bfv0 = g.Evaluator(ctx), g.BfvEvaluator(ctx, t)
+    want = [work(i, ev0, bfv0) for i in range(4)]
+    torch.cuda.synchronize()
+    got, errs = [None] * 4, []
+
+    def thread(i):
+        try:
+            ws, stream = g.Workspace(ctx), torch.cuda.Stream()
+            ev, bfv = g.Evaluator(ctx, ws), g.BfvEvaluator(ctx, t, ws)
+            with torch.cuda.stream(stream):
+                for _ in range(10):
+                    got[i] = work(i, ev, bfv)
+            stream.synchronize()
+            ws.close()
+        except Exception as e:  # surfaced below
+            errs.append(e)
+
+    ths = [threading.Thread(target=thread, args=(i,)) for i in range(4)]
+    [th.start() for th in ths]
+    [th.join() for th in ths]
+    assert not errs, errs
+    for i in range(4):
+        for x, y in zip(got[i], want[i]):
+            assert torch.equal(x, y)
+    ctx.close()
