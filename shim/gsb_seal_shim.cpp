@@ -435,6 +435,104 @@ namespace gsb_seal
         relinearize_inplace(destination, relin_keys, move(pool));
     }
 
+    // ---- multiply_many / exponentiate (evaluator.cpp:1180-1288) ----------------------------------------
+    void Evaluator::multiply_many(
+        const vector<Ciphertext> &encrypteds, const RelinKeys &relin_keys, Ciphertext &destination, MemoryPoolHandle pool)
+    {
+        if (encrypteds.size() == 0)
+            throw invalid_argument("encrypteds vector must not be empty");
+        if (!pool)
+            throw invalid_argument("pool is uninitialized");
+        for (size_t i = 0; i < encrypteds.size(); i++)
+            if (&encrypteds[i] == &destination)
+                throw invalid_argument("encrypteds must be different from destination");
+        auto context_data_ptr = context_->get_context_data(encrypteds[0].parms_id());
+        if (!context_data_ptr)
+            throw invalid_argument("encrypteds is not valid for encryption parameters");
+        if (!bfv_)
+            throw logic_error("unsupported scheme");
+        if (encrypteds.size() == 1)
+        {
+            destination = encrypteds[0];
+            return;
+        }
+        // what multiply / relinearize_inplace check per product (:235-272, :772-800)
+        for (auto &ct : encrypteds)
+        {
+            validate(ct, "encrypted1");
+            if (ct.parms_id() != encrypteds[0].parms_id())
+                throw invalid_argument("encrypted1 and encrypted2 parameter mismatch");
+            if (ct.is_ntt_form())
+                throw invalid_argument("encrypted1 or encrypted2 cannot be in NTT form");
+            if (ct.size() != 2)
+                throw logic_error("device multiply serves size-2 operands (relinearize first)");
+        }
+        if (relin_keys.parms_id() != context_->key_parms_id())
+            throw invalid_argument("relin_keys is not valid for encryption parameters");
+        if (relin_keys.size() < 1)
+            throw invalid_argument("not enough relinearization keys");
+        ensure_relin(relin_keys, RelinKeys::get_index(2));
+
+        // The reference's queue (:1224-1254): q = [e0*e1, e2*e3, ..., (e_last if odd)], then q.push(q[i]*q[i+1])
+        // for i = 0, 2, 4, ... until one product is left.  Entry j of the queue is a pair of earlier entries,
+        // so the pairs whose operands already exist form one batch.
+        const size_t L = level_limbs(encrypteds[0]), ct_words = 2 * L * N_;
+        const size_t n = encrypteds.size();
+        vector<vector<uint64_t>> q;                                       // queue entries, [2][L][N] each
+        q.reserve(n);
+        vector<uint64_t> a, b, c3, c2;
+        auto run_wave = [&](const vector<pair<const uint64_t *, const uint64_t *>> &pairs) {
+            const size_t w = pairs.size();
+            a.resize(w * ct_words), b.resize(w * ct_words), c3.resize(w * 3 * L * N_), c2.resize(w * ct_words);
+            for (size_t i = 0; i < w; i++)
+            {
+                memcpy(a.data() + i * ct_words, pairs[i].first, ct_words * sizeof(uint64_t));
+                memcpy(b.data() + i * ct_words, pairs[i].second, ct_words * sizeof(uint64_t));
+            }
+            check(gsb_bfv_multiply_host(ctx_, plain_modulus_, a.data(), b.data(), c3.data(), w, L));
+            check(gsb_bfv_relinearize_host(ctx_, c3.data(), c2.data(), w, L));
+            for (size_t i = 0; i < w; i++)
+                q.emplace_back(c2.begin() + i * ct_words, c2.begin() + (i + 1) * ct_words);
+        };
+        vector<pair<const uint64_t *, const uint64_t *>> pairs;
+        for (size_t i = 0; i + 1 < n; i += 2)
+            pairs.emplace_back(encrypteds[i].data(), encrypteds[i + 1].data());
+        run_wave(pairs);
+        if (n & 1)
+            q.emplace_back(encrypteds.back().data(), encrypteds.back().data() + ct_words);
+        for (size_t i = 0; i + 1 < q.size();)
+        {
+            pairs.clear();
+            const size_t avail = q.size();
+            for (; i + 1 < avail; i += 2)
+                pairs.emplace_back(q[i].data(), q[i + 1].data());
+            run_wave(pairs);
+        }
+        destination.resize(context_, context_data_ptr->parms_id(), 2);
+        destination.is_ntt_form() = false;
+        memcpy(destination.data(), q.back().data(), ct_words * sizeof(uint64_t));
+#ifdef SEAL_THROW_ON_TRANSPARENT_CIPHERTEXT
+        if (destination.is_transparent())
+            throw logic_error("result ciphertext is transparent");
+#endif
+    }
+
+    void Evaluator::exponentiate_inplace(Ciphertext &encrypted, uint64_t exponent, const RelinKeys &relin_keys, MemoryPoolHandle pool)
+    {
+        if (!context_->get_context_data(encrypted.parms_id()))
+            throw invalid_argument("encrypted is not valid for encryption parameters");
+        if (!context_->get_context_data(relin_keys.parms_id()))
+            throw invalid_argument("relin_keys is not valid for encryption parameters");
+        if (!pool)
+            throw invalid_argument("pool is uninitialized");
+        if (exponent == 0)
+            throw invalid_argument("exponent cannot be 0");
+        if (exponent == 1)
+            return;
+        vector<Ciphertext> exp_vector(static_cast<size_t>(exponent), encrypted);
+        multiply_many(exp_vector, relin_keys, encrypted, move(pool));
+    }
+
     // ---- rescale (evaluator.cpp:1090-1126, 829-892) ---------------------------------------------------
     void Evaluator::rescale_to_next(const Ciphertext &encrypted, Ciphertext &destination, MemoryPoolHandle pool)
     {

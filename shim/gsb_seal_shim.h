@@ -68,6 +68,17 @@ namespace gsb_seal
             const seal::Ciphertext &encrypted, const seal::RelinKeys &relin_keys, seal::Ciphertext &destination,
             seal::MemoryPoolHandle pool = seal::MemoryManager::GetPool());
 
+        // evaluator.h:480-520 / evaluator.cpp:1180-1288 (BFV only, as in the reference).  The reference's
+        // product queue is evaluated wave by wave: all products whose operands exist go to the device
+        // as ONE batched multiply + relinearize, so a product of n ciphertexts costs ceil(log2 n) + 1
+        // device passes instead of n - 1.
+        void multiply_many(
+            const std::vector<seal::Ciphertext> &encrypteds, const seal::RelinKeys &relin_keys, seal::Ciphertext &destination,
+            seal::MemoryPoolHandle pool = seal::MemoryManager::GetPool());
+        void exponentiate_inplace(
+            seal::Ciphertext &encrypted, std::uint64_t exponent, const seal::RelinKeys &relin_keys,
+            seal::MemoryPoolHandle pool = seal::MemoryManager::GetPool());
+
         // evaluator.h:565-600 / evaluator.cpp:1090-1126,829-892
         void rescale_to_next(
             const seal::Ciphertext &encrypted, seal::Ciphertext &destination,

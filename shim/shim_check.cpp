@@ -277,6 +277,29 @@ static int run_bfv(size_t N)
         dev.negate_inplace(d3);
         same("BFV add / sub / negate", r3, d3);
     }
+    {
+        // multiply_many (queue of 5 -> waves of 2, 1, 1 products) and exponentiate (x^3, x^4)
+        Ciphertext c;
+        ref.add(a, b, c);
+        vector<Ciphertext> v{ a, b, c, a, b };
+        Ciphertext r4, d4;
+        ref.multiply_many(v, rlk, r4);
+        dev.multiply_many(v, rlk, d4);
+        same("BFV multiply_many(5)", r4, d4);
+        v.resize(2);
+        ref.multiply_many(v, rlk, r4);
+        dev.multiply_many(v, rlk, d4);
+        same("BFV multiply_many(2)", r4, d4);
+        for (uint64_t e : { 3, 4 })
+        {
+            Ciphertext r5 = a, d5 = a;
+            ref.exponentiate_inplace(r5, e, rlk);
+            dev.exponentiate_inplace(d5, e, rlk);
+            same(e == 3 ? "BFV exponentiate_inplace(3)" : "BFV exponentiate_inplace(4)", r5, d5);
+        }
+        expect_throw("multiply_many(empty)", [&] { vector<Ciphertext> e; Ciphertext t; dev.multiply_many(e, rlk, t); }, 0);
+        expect_throw("exponentiate(0)", [&] { Ciphertext t = a; dev.exponentiate_inplace(t, 0, rlk); }, 0);
+    }
     expect_throw("BFV rotate_vector (CKKS only)", [&] { Ciphertext t = a; dev.rotate_vector_inplace(t, 1, glk); }, 1);
     return failures;
 }

@@ -34,3 +34,15 @@ def test_shim_compiles_against_reference_headers():
     build.build()
     subprocess.run(["make", "-s", "-C", os.path.join(ROOT, "oracle"), "shim"], check=True)
     assert os.path.exists(BIN)
+
+
+def test_shim_against_simulator(simlib):
+    """CPU-side: the same shim_check binary with the TEST-ONLY simulator build of the kernel sources
+    preloaded (its C-ABI symbols take precedence over libgseal_b200.so's), so the shim's host logic,
+    the C ABI and the kernels are compared with the unmodified reference without a GPU."""
+    if not os.path.exists(BIN):
+        pytest.skip("oracle/_ref/shim_check not built (needs /root/reference at build time)")
+    env = dict(os.environ, LD_PRELOAD=simlib._name)
+    p = subprocess.run([BIN], capture_output=True, text=True, timeout=900, env=env)
+    assert p.returncode == 0, p.stdout[-3000:] + p.stderr[-1000:]
+    assert "SHIM_CHECK PASS" in p.stdout and "MISMATCH" not in p.stdout
