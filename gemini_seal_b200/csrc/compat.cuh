@@ -30,6 +30,22 @@
 
 #define GSB_DEV __device__ __forceinline__
 
+// Range checks that only exist in the test-only simulator build (they compile to nothing for nvcc):
+// used to validate the no-wrap bounds of the wide-range butterflies on real inputs.
+#ifdef GSB_CUSIM
+#define GSB_SIM_ASSERT(cond)                                                              \
+    do                                                                                    \
+    {                                                                                     \
+        if (!(cond))                                                                      \
+        {                                                                                 \
+            fprintf(stderr, "GSB_SIM_ASSERT failed: %s (%s:%d)\n", #cond, __FILE__, __LINE__); \
+            abort();                                                                      \
+        }                                                                                 \
+    } while (0)
+#else
+#define GSB_SIM_ASSERT(cond) ((void)0)
+#endif
+
 namespace gsb
 {
     // Kernel launches issued by this library in this process (gsb_launch_count()).

@@ -239,10 +239,12 @@ int gsb_ctx_create(int device, int logn, const uint64_t *moduli, size_t K, size_
             uint64_t qmax = 0;
             for (size_t i = 0; i < K; i++)
                 qmax = std::max(qmax, moduli[i]);
-            const u128 growth = 2 * static_cast<u128>(logn) + 1;
+            // wide-range butterflies grow a word by < 5q per stage from an input < 2q (see fwd_round)
+            const u128 growth = 5 * static_cast<u128>(logn) + 2;
             const u128 beta0 = (ctx->L0 + ctx->k - 1) / ctx->k;
-            ctx->lazy_modup = static_cast<u128>(qmax) * growth < (static_cast<u128>(1) << 64);
-            ctx->lazy_mac = ctx->lazy_modup && static_cast<u128>(qmax) * qmax <= ~static_cast<u128>(0) / (beta0 * growth);
+            ctx->fast_ntt = static_cast<u128>(qmax) * growth < (static_cast<u128>(1) << 63);
+            ctx->lazy_modup = ctx->fast_ntt;
+            ctx->lazy_mac = ctx->fast_ntt && static_cast<u128>(qmax) * qmax <= ~static_cast<u128>(0) / (beta0 * growth);
         }
         ctx->d_WW = upload(ww);
         ctx->d_VV = upload(vv);

@@ -89,9 +89,12 @@ struct gsb_ctx
     int device = 0;
     int logn = 0;
     size_t N = 0, K = 0, k = 0, L0 = 0;
-    // no-wrap bounds over q_max = max modulus, n = log2 N, beta0 = ceil(L0 / k) (see KsDev):
-    //   lazy_modup: q_max (2n + 1) < 2^64             (a lazy forward NTT grows by < 2p per stage)
-    //   lazy_mac:   beta0 (2n + 1) q_max^2 < 2^128    (sum of beta0 products operand x key)
+    // no-wrap bounds over q_max = max modulus, n = log2 N, beta0 = ceil(L0 / k) (see KsDev, fwd_round):
+    //   fast_ntt:   q_max (5n + 2) < 2^63             (a wide-range forward NTT grows by < 5q per stage
+    //                                                  from an input < 2q; its multiply needs x < 2^63)
+    //   lazy_modup: = fast_ntt                        (single-limb bundle enters the NTT unreduced)
+    //   lazy_mac:   beta0 (5n + 2) q_max^2 < 2^128    (sum of beta0 products operand x key)
+    bool fast_ntt = false;
     bool lazy_modup = false, lazy_mac = false;
     std::vector<gsb::host::LimbTables> tables; // host copies (introspection + constants)
     gsb::Twiddle *d_WW = nullptr, *d_VV = nullptr;

@@ -308,7 +308,7 @@ namespace gsb
             if (K1 && ks.lazy_modup)
             {
                 IoPair<ModupLoadT<K1, K1>, PlainStore<OUT_RAW>> io{ ModupArgs{ ks, coef }, PlainStoreArgs{ ext1, E * N } };
-                launch_fwd_cols<LOGN>(io, tab, mup, iE, static_cast<int>(B * beta), st, "modup");
+                launch_fwd_cols<LOGN, true>(io, tab, mup, iE, static_cast<int>(B * beta), st, "modup");
             }
             else
             {
@@ -358,14 +358,25 @@ namespace gsb
         else if constexpr (two)
         {
             IoPair<MdLoadT<K1>, PlainStore<OUT_RAW>> io1{ la, PlainStoreArgs{ tmp, L * N } };
-            launch_fwd_cols<LOGN>(io1, tab, mm, iL, static_cast<int>(2 * B), st, "moddown");
             IoPair<PlainLoad, MdStore> io2{ PlainArgs{ tmp, L * N }, sa };
-            launch_fwd_contig<LOGN>(io2, tab, mm, iL, static_cast<int>(2 * B), st, "moddown");
+            if (ctx->fast_ntt)
+            {
+                launch_fwd_cols<LOGN, true>(io1, tab, mm, iL, static_cast<int>(2 * B), st, "moddown");
+                launch_fwd_contig<LOGN, true>(io2, tab, mm, iL, static_cast<int>(2 * B), st, "moddown");
+            }
+            else
+            {
+                launch_fwd_cols<LOGN>(io1, tab, mm, iL, static_cast<int>(2 * B), st, "moddown");
+                launch_fwd_contig<LOGN>(io2, tab, mm, iL, static_cast<int>(2 * B), st, "moddown");
+            }
         }
         else
         {
             IoPair<MdLoadT<K1>, MdStore> io{ la, sa };
-            launch_fwd_contig<LOGN>(io, tab, mm, iL, static_cast<int>(2 * B), st, "moddown");
+            if (ctx->fast_ntt)
+                launch_fwd_contig<LOGN, true>(io, tab, mm, iL, static_cast<int>(2 * B), st, "moddown");
+            else
+                launch_fwd_contig<LOGN>(io, tab, mm, iL, static_cast<int>(2 * B), st, "moddown");
         }
     }
 
@@ -411,14 +422,25 @@ namespace gsb
         {
             // `out` doubles as the buffer between the two passes (same element, same thread)
             IoPair<RsLoad, PlainStore<OUT_RAW>> io1{ la, PlainStoreArgs{ out, (L - 1) * N } };
-            launch_fwd_cols<LOGN>(io1, tab, mm, ny, nz, st, "rescale");
             IoPair<PlainLoad, RsStore> io2{ PlainArgs{ out, (L - 1) * N }, sa };
-            launch_fwd_contig<LOGN>(io2, tab, mm, ny, nz, st, "rescale");
+            if (ctx->fast_ntt)
+            {
+                launch_fwd_cols<LOGN, true>(io1, tab, mm, ny, nz, st, "rescale");
+                launch_fwd_contig<LOGN, true>(io2, tab, mm, ny, nz, st, "rescale");
+            }
+            else
+            {
+                launch_fwd_cols<LOGN>(io1, tab, mm, ny, nz, st, "rescale");
+                launch_fwd_contig<LOGN>(io2, tab, mm, ny, nz, st, "rescale");
+            }
         }
         else
         {
             IoPair<RsLoad, RsStore> io{ la, sa };
-            launch_fwd_contig<LOGN>(io, tab, mm, ny, nz, st, "rescale");
+            if (ctx->fast_ntt)
+                launch_fwd_contig<LOGN, true>(io, tab, mm, ny, nz, st, "rescale");
+            else
+                launch_fwd_contig<LOGN>(io, tab, mm, ny, nz, st, "rescale");
         }
     }
 

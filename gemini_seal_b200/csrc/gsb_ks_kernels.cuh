@@ -540,7 +540,7 @@ namespace gsb
                     x[r] = pro.xform(x[r]);
             }
             if (!direct)
-                fwd_compute<T, MP::G_HI, 0, !LAZY, 0>(x, smem, tid, tw, c, parity);
+                fwd_compute<T, MP::G_HI, 0, !LAZY, 0, LAZY>(x, smem, tid, tw, c, parity);
             const uint64_t *k0, *k1;
             if constexpr (MP::two_pass)
             {
@@ -558,10 +558,20 @@ namespace gsb
             {
                 const ulonglong2 u = reinterpret_cast<const ulonglong2 *>(k0)[r];
                 const ulonglong2 v = reinterpret_cast<const ulonglong2 *>(k1)[r];
-                mac128(lo[0][2 * r], hi[0][2 * r], x[2 * r], u.x);
-                mac128(lo[0][2 * r + 1], hi[0][2 * r + 1], x[2 * r + 1], u.y);
-                mac128(lo[1][2 * r], hi[1][2 * r], x[2 * r], v.x);
-                mac128(lo[1][2 * r + 1], hi[1][2 * r + 1], x[2 * r + 1], v.y);
+                if constexpr (LAZY) // operand and key words are < 2^63 (gsb_ctx::fast_ntt)
+                {
+                    mac128_mid(lo[0][2 * r], hi[0][2 * r], x[2 * r], u.x);
+                    mac128_mid(lo[0][2 * r + 1], hi[0][2 * r + 1], x[2 * r + 1], u.y);
+                    mac128_mid(lo[1][2 * r], hi[1][2 * r], x[2 * r], v.x);
+                    mac128_mid(lo[1][2 * r + 1], hi[1][2 * r + 1], x[2 * r + 1], v.y);
+                }
+                else
+                {
+                    mac128(lo[0][2 * r], hi[0][2 * r], x[2 * r], u.x);
+                    mac128(lo[0][2 * r + 1], hi[0][2 * r + 1], x[2 * r + 1], u.y);
+                    mac128(lo[1][2 * r], hi[1][2 * r], x[2 * r], v.x);
+                    mac128(lo[1][2 * r + 1], hi[1][2 * r + 1], x[2 * r + 1], v.y);
+                }
             }
         }
 #pragma unroll

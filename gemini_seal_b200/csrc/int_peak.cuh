@@ -57,7 +57,7 @@ namespace gsb
             x[i] = threadIdx.x * 8 + i;
         for (int it = 0; it < iters; it++)
         {
-            fwd_round<2, 3, 8, false>(x, threadIdx.x, tw, c); // 12 butterflies
+            fwd_round<2, 3, 8, false, false>(x, threadIdx.x, tw, c); // 12 butterflies
 #pragma unroll
             for (int i = 0; i < 8; i++) // keep values inside the lazy range (one Barrett per word per round)
                 x[i] = reduce_barrett_lazy(x[i], c.rdp, c.q);

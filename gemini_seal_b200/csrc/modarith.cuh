@@ -92,6 +92,56 @@ namespace gsb
         return mad_lo64_2(x, y, mulhi(x, ys), 0 - q, add);
     }
 
+    // Wide-range lazy multiply for transforms whose words never leave the library (see `FAST` in
+    // ntt_core.cuh): add + x*y - h*(2q) (mod 2^64) with h an UNDER-estimate of floor(x*y/(2q)) built
+    // from three 32x32 products instead of the four of an exact hi64 and with no carry instructions:
+    //     ysh = y' >> 1 = floor(y 2^63 / q) < 2^63,     x < 2^63   (bound kept by the caller)
+    //     t   = x0*ysh1 + x1*ysh0              (no 64-bit wrap: both products are < 2^63)
+    //     h   = x1*ysh1 + (t >> 32)            in { H, H-1 },  H = floor(x*ysh / 2^64)
+    // With Q = x*y/(2q):  Q - 1.5 < H <= Q  (x < 2^63), so Q - 2.5 < h <= Q and the product term
+    // x*y - 2q*h lies in [0, 5q): congruent to the reference's mulmodLazy word, in a wider range.
+    // 5 IMAD.WIDE + 4 IMAD and nothing else (the exact form is 6 IMAD.WIDE + 4 IMAD + 4 carry adds).
+    // `zero` is a run-time zero (LimbC::pad): as the high word of the third product's addend it keeps
+    // ptxas from splitting that multiply-add into a multiply plus a carry pair on the FMA-heavy pipe.
+    GSB_DEV uint64_t mulmod_wide_add(uint64_t x, uint64_t y, uint64_t ysh, uint64_t neg_two_q, uint64_t add, uint64_t zero)
+    {
+#ifdef GSB_CUSIM
+        GSB_SIM_ASSERT((x >> 63) == 0 && (ysh >> 63) == 0 && zero == 0);
+        const uint64_t x0 = static_cast<uint32_t>(x), x1 = x >> 32, s0 = static_cast<uint32_t>(ysh), s1 = ysh >> 32;
+        const uint64_t t = x0 * s1 + x1 * s0;
+        const uint64_t h = x1 * s1 + (t >> 32);
+        return x * y + h * neg_two_q + add;
+#else
+        uint64_t r;
+        asm("{\n\t"
+            ".reg .u32 x0, x1, y0, y1, s0, s1, h0, h1, n0, n1, lo, hi, z, z1;\n\t"
+            ".reg .u64 t, c;\n\t"
+            "mov.b64 {x0, x1}, %1;\n\t"
+            "mov.b64 {y0, y1}, %2;\n\t"
+            "mov.b64 {s0, s1}, %3;\n\t"
+            "mov.b64 {n0, n1}, %4;\n\t"
+            "mul.wide.u32 t, x0, s1;\n\t"
+            "mad.wide.u32 t, x1, s0, t;\n\t"
+            "mov.b64 {lo, hi}, t;\n\t"
+            "mov.b64 {z, z1}, %6;\n\t"
+            "mov.b64 c, {hi, z};\n\t"
+            "mad.wide.u32 t, x1, s1, c;\n\t"
+            "mov.b64 {h0, h1}, t;\n\t"
+            "mad.wide.u32 t, x0, y0, %5;\n\t"
+            "mad.wide.u32 t, h0, n0, t;\n\t"
+            "mov.b64 {lo, hi}, t;\n\t"
+            "mad.lo.u32 hi, x0, y1, hi;\n\t"
+            "mad.lo.u32 hi, x1, y0, hi;\n\t"
+            "mad.lo.u32 hi, h0, n1, hi;\n\t"
+            "mad.lo.u32 hi, h1, n0, hi;\n\t"
+            "mov.b64 %0, {lo, hi};\n\t"
+            "}"
+            : "=l"(r)
+            : "l"(x), "l"(y), "l"(ysh), "l"(neg_two_q), "l"(add), "l"(zero));
+        return r;
+#endif
+    }
+
     // SlothfulNTT::reduceBarrettLazy (util/ntt.cpp:237-241)
     GSB_DEV uint64_t reduce_barrett_lazy(uint64_t x, uint64_t rdp, uint64_t q)
     {
@@ -179,6 +229,41 @@ namespace gsb
             "addc.cc.u32 h0, h0, m1;\n"
             "addc.u32 h1, h1, 0;\n"
             "mul.wide.u32 p, a1, b0;\n"
+            "mov.b64 {m0, m1}, p;\n"
+            "add.cc.u32 l1, l1, m0;\n"
+            "addc.cc.u32 h0, h0, m1;\n"
+            "addc.u32 h1, h1, 0;\n"
+            "mov.b64 %0, {l0, l1};\n"
+            "mov.b64 %1, {h0, h1};\n"
+            "}"
+            : "+l"(lo), "+l"(hi)
+            : "l"(a), "l"(b));
+#endif
+    }
+
+    // mac128 for a < 2^63 and b < 2^63 (operand of a wide-range transform times a key word, both
+    // bounded by gsb_ctx::fast_ntt): the two middle products cannot wrap 64 bits when summed
+    // (a0*b1 < 2^63 and a1*b0 < 2^63), so they are added to each other inside the multiplier and
+    // enter the accumulator with one carry chain instead of two.  Same 128-bit result as mac128.
+    GSB_DEV void mac128_mid(uint64_t &lo, uint64_t &hi, uint64_t a, uint64_t b)
+    {
+#ifdef GSB_CUSIM
+        GSB_SIM_ASSERT((a >> 63) == 0 && (b >> 63) == 0);
+        mac128(lo, hi, a, b);
+#else
+        asm("{\n"
+            ".reg .u32 a0, a1, b0, b1, l0, l1, h0, h1, m0, m1;\n"
+            ".reg .u64 p;\n"
+            "mov.b64 {a0, a1}, %2;\n"
+            "mov.b64 {b0, b1}, %3;\n"
+            "mul.wide.u32 p, a0, b0;\n"
+            "add.cc.u64 %0, %0, p;\n"
+            "mul.wide.u32 p, a1, b1;\n"
+            "addc.u64 %1, %1, p;\n"
+            "mov.b64 {l0, l1}, %0;\n"
+            "mov.b64 {h0, h1}, %1;\n"
+            "mul.wide.u32 p, a0, b1;\n"
+            "mad.wide.u32 p, a1, b0, p;\n"
             "mov.b64 {m0, m1}, p;\n"
             "add.cc.u32 l1, l1, m0;\n"
             "addc.cc.u32 h0, h0, m1;\n"

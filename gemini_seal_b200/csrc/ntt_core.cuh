@@ -209,9 +209,19 @@ namespace gsb
     // ---- forward round: ForwardLazy / ForwardLazyLast (util/ntt.cpp:245-261) -------------------
     // LAST: this transform's gap-2^0 stage is the global last stage (h = 1), where x0 is first
     // reduced with reduceBarrettLazy.
-    template <int TOP, int R, int T_LOG, bool LAST, class TW>
+    //
+    // FAST (wide-range butterflies): only for transforms whose words stay inside the library and end
+    // in a canonical reduction, and only when gsb_ctx::fast_ntt proves no word can reach 2^63.  The
+    // twiddle product comes from mulmod_wide_add (one IMAD.WIDE and four carry adds fewer), which
+    // returns a word CONGRUENT to the reference's mulmodLazy in [0,5q) instead of [0,2q); the
+    // butterfly therefore uses u - v + 5q.  A word grows by < 5q per stage, so after s stages it is
+    // < in + 5qs.  The global last stage (LAST, g = 0) stays the literal ForwardLazyLast, whose
+    // reduceBarrettLazy / exact Shoup product accept any 64-bit word: its outputs are again in
+    // [0,4q), the range every epilogue of the reference expects.
+    template <int TOP, int R, int T_LOG, bool LAST, bool FAST, class TW>
     GSB_DEV void fwd_round(uint64_t (&x)[8], uint32_t tid, const TW &tw, const LimbC &c)
     {
+        const uint64_t five_q = c.two_q + c.two_q + c.q, neg_two_q = 0 - c.two_q;
 #pragma unroll
         for (int sub = 0; sub < (8 >> R); sub++)
         {
@@ -225,6 +235,8 @@ namespace gsb
                 for (int grp = 0; grp < (1 << s); grp++)
                 {
                     const Twiddle w = tw.fwd(g, base, grp);
+                    const bool wide = FAST && !(LAST && g == 0);
+                    const uint64_t wsh = w.y >> 1;
 #pragma unroll
                     for (int i = 0; i < half; i++)
                     {
@@ -236,9 +248,19 @@ namespace gsb
                         //      = (2u + 2q) - x[a]  (all mod 2^64, exactly the reference's words)
                         // (c.pad is a run-time zero: it keeps both sums three-input IADD3s on the ALU pipe
                         // instead of IMAD.X on the FMA-heavy pipe that bounds these kernels)
-                        const uint64_t s = mulmod_lazy_add(x[b], w.x, w.y, c.q, u);
-                        x[b] = (u + u + c.two_q) + (c.pad - s);
-                        x[a] = s;
+                        if (wide)
+                        {
+                            const uint64_t s = mulmod_wide_add(x[b], w.x, wsh, neg_two_q, u, c.pad);
+                            x[b] = (u + u + five_q) + (c.pad - s);
+                            x[a] = s;
+                            GSB_SIM_ASSERT((x[a] >> 63) == 0 && (x[b] >> 63) == 0);
+                        }
+                        else
+                        {
+                            const uint64_t s = mulmod_lazy_add(x[b], w.x, w.y, c.q, u);
+                            x[b] = (u + u + c.two_q) + (c.pad - s);
+                            x[a] = s;
+                        }
                     }
                 }
             }
@@ -449,7 +471,7 @@ namespace gsb
     }
 
     // All rounds of a forward transform; x enters in the first round's layout, leaves in the last's.
-    template <int T_LOG, int G_HI, int G_LO, bool LAST, int IDX, class TW>
+    template <int T_LOG, int G_HI, int G_LO, bool LAST, int IDX, bool FAST = false, class TW>
     GSB_DEV void fwd_compute(uint64_t (&x)[8], uint64_t *smem, uint32_t tid, const TW &tw, const LimbC &c, int &parity)
     {
         constexpr int NS = G_HI - G_LO + 1;
@@ -465,12 +487,12 @@ namespace gsb
                 __syncthreads();
                 tile_load<TOP, R, T_LOG>(buf, x, tid);
             }
-            fwd_round<TOP, R, T_LOG, LAST>(x, tid, tw, c);
+            fwd_round<TOP, R, T_LOG, LAST, FAST>(x, tid, tw, c);
             if constexpr (IDX < NR - 1)
             {
                 uint64_t *buf = smem + (static_cast<size_t>(parity) << (T_LOG + 3));
                 tile_store<TOP, R, T_LOG>(buf, x, tid);
-                fwd_compute<T_LOG, G_HI, G_LO, LAST, IDX + 1>(x, smem, tid, tw, c, parity);
+                fwd_compute<T_LOG, G_HI, G_LO, LAST, IDX + 1, FAST>(x, smem, tid, tw, c, parity);
             }
         }
     }

@@ -114,7 +114,8 @@ namespace gsb
         static constexpr size_t smem_bytes = exch_words * sizeof(uint64_t) + PAIRS * sizeof(Twiddle) + 16;
     };
 
-    template <bool INVERSE, int T_LOG, int G_HI, int G_LO, bool LAST, int A, class IO>
+    // FAST (forward only): wide-range butterflies, see fwd_round.
+    template <bool INVERSE, int T_LOG, int G_HI, int G_LO, bool LAST, int A, class IO, bool FAST = false>
     __global__ void __launch_bounds__(1 << T_LOG, T_LOG <= 8 ? GSB_TILE_MIN_CTAS : 1) ntt_tile_kernel(IO io, NttTables tab, ModMap mm, int nz, int zb)
     {
         typedef TilePlan<T_LOG, G_HI, A> TP;
@@ -166,7 +167,7 @@ namespace gsb
                 if constexpr (INVERSE)
                     inv_compute<T_LOG, G_HI, G_LO, LAST, 0>(x, smem, tid, tw, c, parity);
                 else
-                    fwd_compute<T_LOG, G_HI, G_LO, LAST, 0>(x, smem, tid, tw, c, parity);
+                    fwd_compute<T_LOG, G_HI, G_LO, LAST, 0, FAST>(x, smem, tid, tw, c, parity);
                 xf_store<T_LOG, G_HI, G_LO, INVERSE>(x, tid, tile, map, epi);
 #if !GSB_PREFETCH
                 if (zn < z1)
@@ -225,13 +226,13 @@ namespace gsb
         return static_cast<int>(zb);
     }
 
-    template <bool INVERSE, int T_LOG, int G_HI, int G_LO, bool LAST, int A, class IO>
+    template <bool INVERSE, int T_LOG, int G_HI, int G_LO, bool LAST, int A, bool FAST = false, class IO>
     inline void launch_tile(
         const char *pass, const char *tag, const IO &io, const NttTables &tab, const ModMap &mm, unsigned tiles, int ny, int nz,
         cudaStream_t st)
     {
         typedef TilePlan<T_LOG, G_HI, A> TP;
-        auto kfn = ntt_tile_kernel<INVERSE, T_LOG, G_HI, G_LO, LAST, A, IO>;
+        auto kfn = ntt_tile_kernel<INVERSE, T_LOG, G_HI, G_LO, LAST, A, IO, FAST>;
         allow_smem(kfn, TP::smem_bytes);
         const int zb = pick_zb(static_cast<size_t>(tiles) * ny, nz);
         dim3 grid(tiles, ny, (nz + zb - 1) / zb);
@@ -239,25 +240,25 @@ namespace gsb
     }
 
     // Forward pass 1 (columns) with arbitrary IO.  tiles = N / 2^C column groups.
-    template <int LOGN, class IO>
+    template <int LOGN, bool FAST = false, class IO>
     inline void launch_fwd_cols(
         const IO &io, const NttTables &tab, const ModMap &mm, int ny, int nz, cudaStream_t st, const char *tag = "plain")
     {
         using SP = Split<LOGN>;
         constexpr int A = SP::A, TC = SP::TC, C = TC + 3 - A;
-        launch_tile<false, TC, A + C - 1, C, false, A>("fwd_cols", tag, io, tab, mm, (1u << (LOGN - A)) >> C, ny, nz, st);
+        launch_tile<false, TC, A + C - 1, C, false, A, FAST>("fwd_cols", tag, io, tab, mm, (1u << (LOGN - A)) >> C, ny, nz, st);
     }
 
     // Forward pass 2 (contiguous blocks of N >> A) -- or the whole transform when !two_pass.
-    template <int LOGN, class IO>
+    template <int LOGN, bool FAST = false, class IO>
     inline void launch_fwd_contig(
         const IO &io, const NttTables &tab, const ModMap &mm, int ny, int nz, cudaStream_t st, const char *tag = "plain")
     {
         using SP = Split<LOGN>;
         if constexpr (SP::two_pass)
-            launch_tile<false, 8, LOGN - SP::A - 1, 0, true, 0>("fwd_contig", tag, io, tab, mm, 1u << (LOGN - 11), ny, nz, st);
+            launch_tile<false, 8, LOGN - SP::A - 1, 0, true, 0, FAST>("fwd_contig", tag, io, tab, mm, 1u << (LOGN - 11), ny, nz, st);
         else
-            launch_tile<false, SP::T1, LOGN - 1, 0, true, 0>("fwd_contig", tag, io, tab, mm, 1u, ny, nz, st);
+            launch_tile<false, SP::T1, LOGN - 1, 0, true, 0, FAST>("fwd_contig", tag, io, tab, mm, 1u, ny, nz, st);
     }
 
     // Inverse pass 1 (contiguous) -- or the whole transform when !two_pass.
