@@ -220,8 +220,10 @@ int gsb_ctx_create(int device, int logn, const uint64_t *moduli, size_t K, size_
             const host::LimbTables &t = ctx->tables[i];
             for (size_t d = 0; d < ctx->N; d++)
             {
-                ww[i * ctx->N + d] = make_ulonglong2(t.w[d], t.ws[d]);
-                vv[i * ctx->N + d] = make_ulonglong2(t.v[d], t.vs[d]);
+                // device layout: small-gap stages swizzled against bank conflicts (ntt_core.cuh)
+                const uint32_t n32 = static_cast<uint32_t>(ctx->N), d32 = static_cast<uint32_t>(d);
+                ww[i * ctx->N + fwd_tw_pos(d32, n32)] = make_ulonglong2(t.w[d], t.ws[d]);
+                vv[i * ctx->N + inv_tw_pos(d32, n32)] = make_ulonglong2(t.v[d], t.vs[d]);
             }
             LimbC c;
             c.q = t.mod.q;

@@ -152,8 +152,9 @@ const gsb::BfvTool &gsb_ctx::bfv_tool(size_t L, uint64_t plain_modulus)
         const host::LimbTables &t = i < L ? tables[i] : aux;
         for (size_t d = 0; d < N; d++)
         {
-            ww[i * N + d] = make_ulonglong2(t.w[d], t.ws[d]);
-            vv[i * N + d] = make_ulonglong2(t.v[d], t.vs[d]);
+            const uint32_t n32 = static_cast<uint32_t>(N), d32 = static_cast<uint32_t>(d);
+            ww[i * N + fwd_tw_pos(d32, n32)] = make_ulonglong2(t.w[d], t.ws[d]);
+            vv[i * N + inv_tw_pos(d32, n32)] = make_ulonglong2(t.v[d], t.vs[d]);
         }
         LimbC c;
         c.q = t.mod.q;
@@ -550,9 +551,18 @@ int gsb_key_upload(gsb_ctx *ctx, int kind, uint32_t galois_elt, const uint64_t *
                 for (size_t d = 0; d < ctx->N; d++)
                     require(p[d] < q, GSB_E_INVALID_ARG, "kswitch_keys is not valid for encryption parameters");
             }
+        // device layout: 16-byte units swizzled inside every 1 KiB block (key_word_pos, ntt_core.cuh)
+        std::vector<uint64_t> perm(words);
+        for (size_t row = 0; row < n_bundles * 2 * ctx->K; row++)
+        {
+            const uint64_t *src = key_host + row * ctx->N;
+            uint64_t *dst = perm.data() + row * ctx->N;
+            for (size_t w = 0; w < ctx->N; w++)
+                dst[key_word_pos(static_cast<uint32_t>(w))] = src[w];
+        }
         uint64_t *d = nullptr;
         GSB_CUDA_CHECK(cudaMalloc(reinterpret_cast<void **>(&d), words * sizeof(uint64_t)));
-        GSB_CUDA_CHECK(cudaMemcpy(d, key_host, words * sizeof(uint64_t), cudaMemcpyHostToDevice));
+        GSB_CUDA_CHECK(cudaMemcpy(d, perm.data(), words * sizeof(uint64_t), cudaMemcpyHostToDevice));
         std::lock_guard<std::mutex> lock(ctx->mu);
         SwitchKey &slot = kind == GSB_KEY_RELIN ? ctx->relin[galois_elt] : ctx->galois[galois_elt];
         if (slot.d)

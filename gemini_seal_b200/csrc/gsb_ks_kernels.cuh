@@ -541,23 +541,26 @@ namespace gsb
             }
             if (!direct)
                 fwd_compute<T, MP::G_HI, 0, !LAZY, 0, LAZY>(x, smem, tid, tw, c, parity);
-            const uint64_t *k0, *k1;
+            // key tiles are stored with their 16-byte units swizzled (key_word_pos): the thread's
+            // words 2r, 2r+1 are unit swz8(4 tid + r) of the tile -- conflict-free for a warp
+            const ulonglong2 *k0, *k1;
             if constexpr (MP::two_pass)
             {
                 mbar_wait(bar + 2, j & 1);
-                k0 = st_key + tid * 8;
-                k1 = k0 + MP::TILE;
+                k0 = reinterpret_cast<const ulonglong2 *>(st_key);
+                k1 = k0 + MP::TILE / 2;
             }
             else
             {
-                k0 = p.key + (static_cast<size_t>(j * 2) * p.K + mod) * N + d0;
-                k1 = k0 + static_cast<size_t>(p.K) * N;
+                k0 = reinterpret_cast<const ulonglong2 *>(p.key + (static_cast<size_t>(j * 2) * p.K + mod) * N + map.off(tile));
+                k1 = k0 + static_cast<size_t>(p.K) * N / 2;
             }
 #pragma unroll
             for (int r = 0; r < 4; r++)
             {
-                const ulonglong2 u = reinterpret_cast<const ulonglong2 *>(k0)[r];
-                const ulonglong2 v = reinterpret_cast<const ulonglong2 *>(k1)[r];
+                const uint32_t unit = swz8(tid * 4 + r);
+                const ulonglong2 u = k0[unit];
+                const ulonglong2 v = k1[unit];
                 if constexpr (LAZY) // operand and key words are < 2^63 (gsb_ctx::fast_ntt)
                 {
                     mac128_mid(lo[0][2 * r], hi[0][2 * r], x[2 * r], u.x);

@@ -31,6 +31,36 @@ namespace gsb
         return idx ^ (((idx >> 4) & 7u) << 1);
     }
 
+    // ---- bank-conflict-free layout of the small-gap twiddles and of the switching keys -----------
+    // In the stride-1 round a thread owns 8 adjacent coefficients, so lane l of a warp reads the
+    // twiddles of the gap-1 / gap-2 stages (and its key words) at a 64 / 32 byte stride: 4- / 2-way
+    // shared-memory bank conflicts on 128-bit loads.  The DEVICE copies of those arrays are therefore
+    // stored with their 16-byte units XOR-swizzled inside every block of 64 units (unit u of the block
+    // lives at u ^ ((u >> 3) & 7)): a linear bulk copy of any 64-unit-aligned range carries the
+    // permutation into shared memory, where 8 lanes at a 64- or 32-byte stride then hit 8 different
+    // 16-byte bank groups.  Only the device layout changes; every word read is the same word.
+    __host__ __device__ inline uint32_t swz8(uint32_t u)
+    {
+        return u ^ ((u >> 3) & 7u);
+    }
+    // Device position of forward twiddle `idx` (root_powers order): the entries of the three
+    // smallest-gap stages, idx >= N/8, are swizzled.
+    __host__ __device__ inline uint32_t fwd_tw_pos(uint32_t idx, uint32_t N)
+    {
+        return idx >= (N >> 3) ? swz8(idx) : idx;
+    }
+    // Device position of inverse twiddle `idx` (re-ordered table, entries 1 .. N-1): the three
+    // smallest-gap stages are idx - 1 < 7N/8; their blocks start at idx - 1 = multiple of 64.
+    __host__ __device__ inline uint32_t inv_tw_pos(uint32_t idx, uint32_t N)
+    {
+        return (idx >= 1 && idx - 1 < N - (N >> 3)) ? 1u + swz8(idx - 1) : idx;
+    }
+    // Device position of word d of a switching-key limb (16-byte unit = 2 words).
+    __host__ __device__ inline uint32_t key_word_pos(uint32_t d)
+    {
+        return (swz8(d >> 1) << 1) | (d & 1u);
+    }
+
     // ---- compile-time round plan ---------------------------------------------------------------
     // Split `ns` stages into rounds of <= 3 so that the round touching gap 2^0 has 3 stages.
     __host__ __device__ constexpr int plan_next(int left)
@@ -141,11 +171,11 @@ namespace gsb
         uint32_t S, off, N;
         GSB_DEV Twiddle fwd(int g, uint32_t local, int grp) const
         {
-            return __ldg(tab + (S >> (g + 1)) + ((off + local) >> (g + 1)) + grp);
+            return __ldg(tab + fwd_tw_pos((S >> (g + 1)) + ((off + local) >> (g + 1)) + grp, N));
         }
         GSB_DEV Twiddle inv(int g, uint32_t local, int grp) const
         {
-            return __ldg(tab + N - 2u * (S >> (g + 1)) + 1u + ((off + local) >> (g + 1)) + grp);
+            return __ldg(tab + inv_tw_pos(N - 2u * (S >> (g + 1)) + 1u + ((off + local) >> (g + 1)) + grp, N));
         }
     };
 
@@ -162,13 +192,16 @@ namespace gsb
         const Twiddle *sm;
         TwGlobal gl;
         GSB_DEV static uint32_t seg(int g) { return TILE - (TILE >> g); }
+        // stages g <= 2 arrive swizzled (fwd_tw_pos / inv_tw_pos): every staged range starts at a
+        // multiple of 64 entries, so the position inside the segment is swizzled the same way
+        GSB_DEV static uint32_t pos(int g, uint32_t rel) { return g <= 2 ? swz8(rel) : rel; }
         GSB_DEV Twiddle fwd(int g, uint32_t local, int grp) const
         {
-            return g <= G_SM ? sm[seg(g) + (local >> (g + 1)) + grp] : gl.fwd(g, local, grp);
+            return g <= G_SM ? sm[seg(g) + pos(g, (local >> (g + 1)) + grp)] : gl.fwd(g, local, grp);
         }
         GSB_DEV Twiddle inv(int g, uint32_t local, int grp) const
         {
-            return g <= G_SM ? sm[seg(g) + (local >> (g + 1)) + grp] : gl.inv(g, local, grp);
+            return g <= G_SM ? sm[seg(g) + pos(g, (local >> (g + 1)) + grp)] : gl.inv(g, local, grp);
         }
         // issued by ONE thread after mbar_init + a CTA barrier
         GSB_DEV static void stage(Twiddle *sm, const Twiddle *tab, uint32_t N, uint32_t off, bool inverse, uint64_t *bar)
