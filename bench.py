@@ -414,14 +414,39 @@ def run_ours(args):
         roofline = {"bound": "hbm", "kernel": top, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                     "traffic": ncu_traffic(top, B // kernels[top]["launches"]), "peak_source": how,
                     "kernel_share_of_step": kernels[top]["share"]}
-        # the binding limit of these kernels is the integer multiplier pipe, not HBM: report the
-        # butterfly rate of the dominant kernel against the register-resident butterfly peak measured now
-        bf = C.c_double()
-        if lib.gsb_int_peak(ctx.handle, 2, None, None, C.byref(bf)) == 0 and top in BUTTERFLY_STAGES:
-            per_s = B * (L * (L + K_SPECIAL) - L) * BUTTERFLY_STAGES[top] * (N // 2) / (kernels[top]["ms"] * 1e-3)
-            roofline["int_pipe"] = {"achieved": per_s / 1e9, "peak": bf.value / 1e9, "unit": "G butterflies/s",
-                                    "frac": per_s / bf.value,
-                                    "peak_source": "gsb_int_peak: register-resident Harvey butterflies, 2 CTAs x 256 threads per SM"}
+        # The binding limit of these kernels is the integer multiplier ("FMA-heavy") pipe, not HBM (DESIGN.md
+        # section 3).  int_pipe = the multiplies the kernel's ALGORITHM needs (butterflies and 64x64->128
+        # multiply-accumulates only; no address, carry or move instructions), each weighted by its measured
+        # register-resident issue rate (gsb_int_peak: IMAD.WIDE.U32/s and IMAD/s on this GPU, now), over the
+        # kernel's measured time.  Unit: IMAD.WIDE-equivalents/s; it is the same quantity ncu reports as
+        # sm__pipe_fmaheavy_cycles_active minus the non-multiply instructions ptxas places on that pipe.
+        imad, wide, bf, bfw = C.c_double(), C.c_double(), C.c_double(), C.c_double()
+        if (lib.gsb_int_peak(ctx.handle, 2, C.byref(imad), C.byref(wide), C.byref(bf)) == 0
+                and lib.gsb_int_peak_wide(ctx.handle, 2, C.byref(bfw)) == 0 and top in BUTTERFLY_STAGES):
+            fast = bool(lib.gsb_ctx_fast_ntt(ctx.handle))
+            pairs = L * (L + K_SPECIAL) - L          # (bundle, ext slot) pairs that go through the NTT
+            n_bf = B * pairs * BUTTERFLY_STAGES[top] * (N // 2)
+            w_per_bf, i_per_bf = (5, 4) if fast else (6, 4)
+            n_wide, n_imad = n_bf * w_per_bf, n_bf * i_per_bf
+            if top == "ks_mac":
+                n_wide += B * L * (L + K_SPECIAL) * N * 2 * 4      # two FMAU128 per (bundle, slot, coefficient)
+                if not fast:
+                    n_wide += B * pairs * N // 2 * 5               # reduceBarrettLazy of the last stage's x0
+                    n_imad += B * pairs * N // 2 * 2
+            secs = kernels[top]["ms"] * 1e-3
+            t_peak = n_wide / wide.value + n_imad / imad.value
+            roofline["int_pipe"] = {
+                "achieved": t_peak * wide.value / secs / 1e12, "peak": wide.value / 1e12,
+                "unit": "T IMAD.WIDE-equivalents/s", "frac": t_peak / secs,
+                "multiplies_per_launch": {"imad_wide": n_wide / kernels[top]["launches"], "imad": n_imad / kernels[top]["launches"]},
+                "butterfly": "wide-range (5 IMAD.WIDE + 4 IMAD)" if fast else "literal (6 IMAD.WIDE + 4 IMAD)",
+                "butterflies_per_s": n_bf / secs,
+                "peak_source": "gsb_int_peak: register-resident chains, 2 CTAs x 256 threads per SM: IMAD %.2f T/s, IMAD.WIDE %.2f T/s; "
+                               "register-resident butterflies %.0f G/s literal, %.0f G/s wide-range"
+                               % (imad.value / 1e12, wide.value / 1e12, bf.value / 1e9, bfw.value / 1e9)}
+            # the raw NTT sweep (literal butterflies, reference words) against the same multiplier-pipe peak
+            for e in extra.get("ntt_sweep", {}).values():
+                e["int_frac"] = e["butterflies_per_s"] * (6 / wide.value + 4 / imad.value)
 
     # ---- CPU baseline on this box's host cores (rank 0, N = 1 only)
     cpu = None

@@ -68,9 +68,11 @@ PROTOTYPES = {
     "gsb_bfv_relinearize_host": (i32, [vp, vp, vp, sz, sz]),
     "gsb_bfv_apply_galois_host": (i32, [vp, u32, vp, vp, sz, sz]),
     "gsb_int_peak": (i32, [vp, i32, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double)]),
+    "gsb_int_peak_wide": (i32, [vp, i32, C.POINTER(C.c_double)]),
+    "gsb_ctx_fast_ntt": (i32, [vp]),
 }
 # measurement aids that the test-only simulator build does not provide
-CUDA_ONLY = {"gsb_int_peak"}
+CUDA_ONLY = {"gsb_int_peak", "gsb_int_peak_wide"}
 
 
 def bind(lib):

@@ -512,6 +512,11 @@ int gsb_poly_op_dev(
     });
 }
 
+int gsb_ctx_fast_ntt(const gsb_ctx *ctx)
+{
+    return ctx != nullptr && ctx->fast_ntt ? 1 : 0;
+}
+
 } // extern "C"
 
 #include "gsb_evaluator.cuh"

@@ -2,7 +2,8 @@
 //   imad      : independent chains of 32-bit IMAD (mad.lo.u32)            -> 32-bit multiply-adds / s
 //   imad_wide : independent chains of IMAD.WIDE.U32 (mad.wide.u32)        -> 32x32+64 multiply-adds / s
 //   butterfly : the forward lazy Harvey butterfly of ntt_core.cuh (radix-8 rounds on 8 register words,
-//               twiddles in registers, no memory traffic)                 -> butterflies / s
+//               twiddles in registers, no memory traffic), in its literal form (the reference's words)
+//               and in the wide-range form of the library-internal transforms -> butterflies / s
 // Included at the end of gsb_api.cu.
 #pragma once
 #include "ntt_core.cuh"
@@ -44,6 +45,9 @@ namespace gsb
         GSB_DEV Twiddle fwd(int g, uint32_t, int grp) const { return w[(g == 2 ? 0 : g == 1 ? 1 : 3) + grp]; }
     };
 
+    // FAST = the wide-range butterfly of the library-internal transforms (fwd_round).  Values are not
+    // kept in range here: timing does not depend on them and nothing reads the result.
+    template <bool FAST>
     __global__ void __launch_bounds__(256) butterfly_peak_kernel(uint64_t *out, const LimbC *limb, const Twiddle *WW, int iters)
     {
         const LimbC c = limb[0];
@@ -56,12 +60,7 @@ namespace gsb
         for (int i = 0; i < 8; i++)
             x[i] = threadIdx.x * 8 + i;
         for (int it = 0; it < iters; it++)
-        {
-            fwd_round<2, 3, 8, false, false>(x, threadIdx.x, tw, c); // 12 butterflies
-#pragma unroll
-            for (int i = 0; i < 8; i++) // keep values inside the lazy range (one Barrett per word per round)
-                x[i] = reduce_barrett_lazy(x[i], c.rdp, c.q);
-        }
+            fwd_round<2, 3, 8, false, FAST>(x, threadIdx.x, tw, c); // 12 butterflies
         uint64_t acc = 0;
 #pragma unroll
         for (int i = 0; i < 8; i++)
@@ -70,7 +69,7 @@ namespace gsb
     }
 } // namespace gsb
 
-extern "C" int gsb_int_peak(gsb_ctx *ctx, int ctas_per_sm, double *imad_per_s, double *imad_wide_per_s, double *butterflies_per_s)
+static int int_peak_impl(gsb_ctx *ctx, int ctas_per_sm, double *imad_per_s, double *imad_wide_per_s, double *butterflies_per_s, double *wide_butterflies_per_s)
 {
     using namespace gsb;
     return guarded([&] {
@@ -95,17 +94,38 @@ extern "C" int gsb_int_peak(gsb_ctx *ctx, int ctas_per_sm, double *imad_per_s, d
             return static_cast<double>(ms);
         };
         const double threads = static_cast<double>(grid) * 256;
-        double ms = time_ms([&] { GSB_LAUNCH("int_peak", "imad", imad_peak_kernel<0>, dim3(grid), dim3(256), 0, nullptr, static_cast<uint32_t *>(buf), iters, 2654435761u); });
         if (imad_per_s)
+        {
+            const double ms = time_ms([&] { GSB_LAUNCH("int_peak", "imad", imad_peak_kernel<0>, dim3(grid), dim3(256), 0, nullptr, static_cast<uint32_t *>(buf), iters, 2654435761u); });
             *imad_per_s = threads * iters * 8 / (ms * 1e-3);
-        ms = time_ms([&] { GSB_LAUNCH("int_peak", "imad_wide", imad_peak_kernel<1>, dim3(grid), dim3(256), 0, nullptr, static_cast<uint32_t *>(buf), iters, 2654435761u); });
+        }
         if (imad_wide_per_s)
+        {
+            const double ms = time_ms([&] { GSB_LAUNCH("int_peak", "imad_wide", imad_peak_kernel<1>, dim3(grid), dim3(256), 0, nullptr, static_cast<uint32_t *>(buf), iters, 2654435761u); });
             *imad_wide_per_s = threads * iters * 8 / (ms * 1e-3);
-        ms = time_ms([&] { GSB_LAUNCH("int_peak", "butterfly", butterfly_peak_kernel, dim3(grid), dim3(256), 0, nullptr, static_cast<uint64_t *>(buf), ctx->d_limb, ctx->d_WW, iters); });
+        }
         if (butterflies_per_s)
+        {
+            const double ms = time_ms([&] { GSB_LAUNCH("int_peak", "butterfly", butterfly_peak_kernel<false>, dim3(grid), dim3(256), 0, nullptr, static_cast<uint64_t *>(buf), ctx->d_limb, ctx->d_WW, iters); });
             *butterflies_per_s = threads * iters * 12 / (ms * 1e-3);
+        }
+        if (wide_butterflies_per_s)
+        {
+            const double ms = time_ms([&] { GSB_LAUNCH("int_peak", "butterfly_wide", butterfly_peak_kernel<true>, dim3(grid), dim3(256), 0, nullptr, static_cast<uint64_t *>(buf), ctx->d_limb, ctx->d_WW, iters); });
+            *wide_butterflies_per_s = threads * iters * 12 / (ms * 1e-3);
+        }
         cudaEventDestroy(e0);
         cudaEventDestroy(e1);
         cudaFree(buf);
     });
+}
+
+extern "C" int gsb_int_peak(gsb_ctx *ctx, int ctas_per_sm, double *imad_per_s, double *imad_wide_per_s, double *butterflies_per_s)
+{
+    return int_peak_impl(ctx, ctas_per_sm, imad_per_s, imad_wide_per_s, butterflies_per_s, nullptr);
+}
+
+extern "C" int gsb_int_peak_wide(gsb_ctx *ctx, int ctas_per_sm, double *wide_butterflies_per_s)
+{
+    return int_peak_impl(ctx, ctas_per_sm, nullptr, nullptr, nullptr, wide_butterflies_per_s);
 }

@@ -203,6 +203,12 @@ int gsb_mul_relin_rescale_host(gsb_ctx *ctx, const uint64_t *a, const uint64_t *
  * 32-bit IMAD/s, IMAD.WIDE.U32/s and forward lazy Harvey butterflies/s (the exact butterfly of the
  * NTT kernels, twiddles in registers, no memory traffic).  Any output pointer may be NULL. */
 int gsb_int_peak(gsb_ctx *ctx, int ctas_per_sm, double *imad_per_s, double *imad_wide_per_s, double *butterflies_per_s);
+/* The same butterfly microbenchmark for the wide-range butterfly (5 instead of 6 IMAD.WIDE) that the
+ * library-internal transforms use when gsb_ctx_fast_ntt(ctx) is 1. */
+int gsb_int_peak_wide(gsb_ctx *ctx, int ctas_per_sm, double *wide_butterflies_per_s);
+/* 1 when the context's moduli satisfy q_max (5 log2 N + 2) < 2^63, i.e. the key-switch / rescale
+ * internals run the wide-range butterflies (identical outputs); else 0. */
+int gsb_ctx_fast_ntt(const gsb_ctx *ctx);
 
 #ifdef __cplusplus
 }
