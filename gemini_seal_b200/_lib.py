@@ -67,6 +67,11 @@ PROTOTYPES = {
     "gsb_bfv_apply_galois_dev": (i32, [vp, vp, u32, vp, vp, sz, sz, vp]),
     "gsb_bfv_relinearize_host": (i32, [vp, vp, vp, sz, sz]),
     "gsb_bfv_apply_galois_host": (i32, [vp, u32, vp, vp, sz, sz]),
+    "gsb_secret_key_set": (i32, [vp, vp]),
+    "gsb_dot_product_ct_sk_dev": (i32, [vp, vp, vp, vp, sz, sz, sz, i32, vp]),
+    "gsb_dot_product_ct_sk_host": (i32, [vp, vp, vp, sz, sz, sz, i32]),
+    "gsb_bfv_decrypt_dev": (i32, [vp, vp, u64, vp, vp, sz, sz, sz, vp]),
+    "gsb_bfv_decrypt_host": (i32, [vp, u64, vp, vp, sz, sz, sz]),
     "gsb_int_peak": (i32, [vp, i32, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "gsb_int_peak_wide": (i32, [vp, i32, C.POINTER(C.c_double)]),
     "gsb_ctx_fast_ntt": (i32, [vp]),

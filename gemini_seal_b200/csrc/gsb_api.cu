@@ -288,6 +288,9 @@ void gsb_ctx_destroy(gsb_ctx *ctx)
         cudaFree(kv.second.d_limb);
         cudaFree(kv.second.d_consts);
     }
+    cudaFree(ctx->d_sk);
+    for (uint64_t *p : ctx->sk_retired)
+        cudaFree(p);
     cudaFree(ctx->default_ws.buf);
     cudaFree(ctx->host_io.buf);
     if (ctx->pipe_ready)

@@ -162,4 +162,96 @@ namespace gsb
             p.out[t] = mul_mod(v, __ldg(p.inv_qlast + i), m);                                                   // :770-772
         }
     }
+
+    // ---- Decryptor --------------------------------------------------------------
+    // dot_product_ct_sk_array (decryptor.cpp:218-265): out[b][i][d] = c0 + sum_{p >= 1} c_p (.) s^p mod q_i.
+    // polys: polynomial p >= 1 of ciphertext b at polys + b*ct_stride + (p-1)*L*N (NTT form: the
+    // ciphertext's own c_1.. ; coefficient form: their lazy forward NTTs in scratch, any word < 2^64 --
+    // dyadic_product_coeffmod reduces the full 128-bit product).  c0 == nullptr: no final add (the BFV
+    // branch adds c0 after the inverse NTT).  skp = secret-key powers [size-1][K][N] at key level.
+    struct DotSkArgs
+    {
+        const uint64_t *polys;
+        size_t ct_stride;
+        const uint64_t *c0;
+        size_t c0_stride;
+        const uint64_t *skp;
+        uint64_t *out; // [B][L][N]
+        const LimbC *limb;
+        uint32_t N, L, K, n_pow;
+        size_t pairs; // B*L*N/2
+    };
+
+    __global__ void __launch_bounds__(256) dot_sk_kernel(DotSkArgs p)
+    {
+        const size_t LN = static_cast<size_t>(p.L) * p.N, KN = static_cast<size_t>(p.K) * p.N;
+        for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < p.pairs;
+             i += static_cast<size_t>(gridDim.x) * blockDim.x)
+        {
+            const size_t w = i << 1;
+            const size_t b = w / LN, rem = w - b * LN;
+            const LimbC c = p.limb[rem / p.N];
+            ulonglong2 acc = make_ulonglong2(0, 0); // set_zero_poly (:253), then add_poly_coeffmod per power
+            for (uint32_t pw = 0; pw < p.n_pow; pw++)
+            {
+                const ulonglong2 x = *reinterpret_cast<const ulonglong2 *>(p.polys + b * p.ct_stride + pw * LN + rem);
+                const ulonglong2 s = *reinterpret_cast<const ulonglong2 *>(p.skp + pw * KN + rem);
+                acc.x = add_mod(acc.x, mul_mod(x.x, s.x, c.q, c.cr0, c.cr1), c.q);
+                acc.y = add_mod(acc.y, mul_mod(x.y, s.y, c.q, c.cr0, c.cr1), c.q);
+            }
+            if (p.c0)
+            {
+                const ulonglong2 z = *reinterpret_cast<const ulonglong2 *>(p.c0 + b * p.c0_stride + rem);
+                acc.x = add_mod(acc.x, z.x, c.q);
+                acc.y = add_mod(acc.y, z.y, c.q);
+            }
+            *reinterpret_cast<ulonglong2 *>(p.out + w) = acc;
+        }
+    }
+
+    // RNSTool::decrypt_scale_and_round (util/rns.cpp:1070-1126): dot = [B][L][N] coefficient form ->
+    // out = [B][N] plaintext coefficients mod t.  One thread per coefficient across the L limbs.
+    struct DecryptRoundArgs
+    {
+        const uint64_t *dot;
+        uint64_t *out;
+        const LimbC *limb;             // [L] base q
+        const uint64_t *prod_tg_mod_q; // [L]
+        const uint64_t *inv_punct_q;   // [L]
+        const uint64_t *mat_tg;        // [2][L]
+        LimbC t, gamma;                // q / cr0 / cr1 of the two output moduli
+        uint64_t neg_inv_q_t, neg_inv_q_gamma, inv_gamma_mod_t;
+        uint32_t N, L;
+        size_t total; // B*N
+    };
+
+    __global__ void __launch_bounds__(256) decrypt_round_kernel(DecryptRoundArgs p)
+    {
+        for (size_t idx = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; idx < p.total;
+             idx += static_cast<size_t>(gridDim.x) * blockDim.x)
+        {
+            const size_t b = idx / p.N, d = idx - b * p.N;
+            const uint64_t *src = p.dot + b * static_cast<size_t>(p.L) * p.N + d;
+            uint64_t lo0 = 0, hi0 = 0, lo1 = 0, hi1 = 0;
+            for (uint32_t i = 0; i < p.L; i++)
+            {
+                const LimbC m = p.limb[i];
+                // |gamma t|_qi * ct(s) (:1077-1082), then fast_convert_array's multiply by the inverse
+                // punctured product (rns.cpp:478-488) and its dot products with the conversion matrix
+                const uint64_t v = mul_mod(mul_mod(src[static_cast<size_t>(i) * p.N], __ldg(p.prod_tg_mod_q + i), m), __ldg(p.inv_punct_q + i), m);
+                mac128(lo0, hi0, v, __ldg(p.mat_tg + i));
+                mac128(lo1, hi1, v, __ldg(p.mat_tg + p.L + i));
+            }
+            const uint64_t at = mul_mod(barrett128(lo0, hi0, p.t.q, p.t.cr0, p.t.cr1), p.neg_inv_q_t, p.t);          // :1091-1096
+            const uint64_t ag = mul_mod(barrett128(lo1, hi1, p.gamma.q, p.gamma.cr0, p.gamma.cr1), p.neg_inv_q_gamma, p.gamma);
+            uint64_t r;
+            if (ag > (p.gamma.q >> 1)) // :1107-1117
+                r = add_mod(at, (p.gamma.q - ag) % p.t.q, p.t.q);
+            else
+                r = sub_mod(at, ag % p.t.q, p.t.q);
+            if (r != 0)
+                r = mul_mod(r, p.inv_gamma_mod_t, p.t); // :1120-1124
+            p.out[idx] = r;
+        }
+    }
 } // namespace gsb

@@ -64,6 +64,7 @@ namespace gsb
         LimbC *d_limb = nullptr;
         uint64_t *d_consts = nullptr; // one allocation, carved up by `dev`
         BehzDev dev{};
+        DecryptRoundArgs dec{}; // constants of decrypt_scale_and_round (dot / out / total filled per call)
     };
 
     struct SwitchKey
@@ -104,6 +105,11 @@ struct gsb_ctx
     std::map<uint32_t, gsb::SwitchKey> galois;
     std::map<uint32_t, uint32_t *> galois_tables; // device permutation tables per element
     std::map<std::pair<size_t, uint64_t>, gsb::BfvTool> bfv_tools; // (L, plain modulus) -> BEHZ tool
+    // Decryptor::secret_key_array_ (decryptor.cpp:46-57, 151-216): NTT-form powers s^1.. at key level,
+    // [sk_powers][K][N] on the device; extended on demand by dyadic products, never shrunk
+    uint64_t *d_sk = nullptr;
+    size_t sk_powers = 0;
+    std::vector<uint64_t *> sk_retired; // superseded power arrays (kernels in flight may still read them)
     std::mutex mu;      // guards the lazily built maps below
     std::mutex host_mu; // serialises the *_host entry points (they share host_io / default_ws)
     gsb_ws default_ws;  // compute scratch for callers that pass ws = NULL

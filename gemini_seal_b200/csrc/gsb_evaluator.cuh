@@ -185,8 +185,23 @@ const gsb::BfvTool &gsb_ctx::bfv_tool(size_t L, uint64_t plain_modulus)
         return off;
     };
     const size_t o1 = put(bc.inv_punct_q), o2 = put(bc.mat_q), o3 = put(bc.inv_punct_b), o4 = put(bc.mat_b),
-                 o5 = put(bc.prod_q_mod_bsk), o6 = put(bc.inv_prod_q_mod_bsk), o7 = put(bc.inv_mtilde_mod_bsk), o8 = put(bc.prod_b_mod_q);
+                 o5 = put(bc.prod_q_mod_bsk), o6 = put(bc.inv_prod_q_mod_bsk), o7 = put(bc.inv_mtilde_mod_bsk), o8 = put(bc.prod_b_mod_q),
+                 o9 = put(bc.prod_tg_mod_q), o10 = put(bc.mat_tg);
     tool.d_consts = upload_words(all);
+    {
+        auto as_limb = [](uint64_t m) {
+            const host::ModConst mc = host::make_mod(m);
+            LimbC c{};
+            c.q = mc.q;
+            c.two_q = mc.q << 1;
+            c.cr0 = mc.cr0;
+            c.cr1 = mc.cr1;
+            return c;
+        };
+        tool.dec = DecryptRoundArgs{ nullptr, nullptr, tool.d_limb, tool.d_consts + o9, tool.d_consts + o1, tool.d_consts + o10,
+                                     as_limb(plain_modulus), as_limb(bc.gamma), bc.neg_inv_q_mod_tg[0], bc.neg_inv_q_mod_tg[1],
+                                     bc.inv_gamma_mod_t, static_cast<uint32_t>(N), static_cast<uint32_t>(L), 0 };
+    }
     tool.dev = BehzDev{ tool.d_limb, tool.d_consts + o1, tool.d_consts + o2, tool.d_consts + o3, tool.d_consts + o4,
                         tool.d_consts + o5, tool.d_consts + o6, tool.d_consts + o7, tool.d_consts + o8,
                         bc.inv_prod_q_mod_mtilde, bc.inv_prod_b_mod_msk, plain_modulus,
@@ -489,6 +504,90 @@ namespace gsb
     {
         require(ws == nullptr || ws->ctx == ctx, GSB_E_INVALID_ARG, "workspace belongs to another context");
         return ws ? ws : &ctx->default_ws;
+    }
+
+    // Decryptor::compute_secret_key_array (decryptor.cpp:151-216): make sure s^1 .. s^n_pow exist on the
+    // device; new powers are dyadic products of the previous power with s over all K key-level limbs.
+    static const uint64_t *secret_key_powers(gsb_ctx *ctx, size_t n_pow, cudaStream_t st)
+    {
+        std::lock_guard<std::mutex> lock(ctx->mu);
+        require(ctx->d_sk != nullptr, GSB_E_LOGIC, "secret key is not set");
+        if (ctx->sk_powers >= n_pow)
+            return ctx->d_sk;
+        const size_t KN = ctx->K * ctx->N;
+        uint64_t *d = nullptr;
+        GSB_CUDA_CHECK(cudaMalloc(reinterpret_cast<void **>(&d), n_pow * KN * sizeof(uint64_t)));
+        GSB_CUDA_CHECK(cudaMemcpyAsync(d, ctx->d_sk, ctx->sk_powers * KN * sizeof(uint64_t), cudaMemcpyDeviceToDevice, st));
+        for (size_t p = ctx->sk_powers; p < n_pow; p++)
+        {
+            PolyOpArgs a{};
+            a.a = d + (p - 1) * KN;
+            a.b = d;
+            a.out = d + p * KN;
+            a.limb = ctx->d_limb;
+            a.N = static_cast<uint32_t>(ctx->N);
+            a.n_limbs = static_cast<uint32_t>(ctx->K);
+            a.limb_offset = 0;
+            a.total = KN;
+            launch_poly_op(GSB_OP_DYADIC, a, st);
+        }
+        GSB_CUDA_CHECK(cudaStreamSynchronize(st)); // published to every stream from here on
+        ctx->sk_retired.push_back(ctx->d_sk);
+        ctx->d_sk = d;
+        ctx->sk_powers = n_pow;
+        return d;
+    }
+
+    // dot_product_ct_sk_array for B ciphertexts; scratch (coefficient form only) = B*(size-1)*L*N words.
+    template <int LOGN>
+    static void dot_sk_core(
+        gsb_ctx *ctx, uint64_t *scratch, const uint64_t *in, uint64_t *out, size_t B, size_t size, size_t L, bool ntt_form,
+        cudaStream_t st)
+    {
+        const size_t N = ctx->N, LN = L * N;
+        const uint64_t *skp = secret_key_powers(ctx, size - 1, st);
+        DotSkArgs p{};
+        p.skp = skp;
+        p.out = out;
+        p.limb = ctx->d_limb;
+        p.N = static_cast<uint32_t>(N);
+        p.L = static_cast<uint32_t>(L);
+        p.K = static_cast<uint32_t>(ctx->K);
+        p.n_pow = static_cast<uint32_t>(size - 1);
+        p.pairs = B * LN / 2;
+        const NttTables tab = ctx->ntt_tables();
+        const ModMap mm{ 1 << 30, 0, 0 };
+        if (ntt_form)
+        {
+            p.polys = in + LN;
+            p.ct_stride = size * LN;
+            p.c0 = in;
+            p.c0_stride = size * LN;
+            GSB_LAUNCH("dot_sk", "ntt", dot_sk_kernel, dim3(grid_for(p.pairs, 256)), dim3(256), 0, st, p);
+            return;
+        }
+        // coefficient form (:241-262): lazy forward NTT of c_1.., dot product, strict inverse NTT, + c_0
+        for (size_t pw = 0; pw + 1 < size; pw++)
+            ntt_forward_plain<LOGN>(tab, mm, in + (pw + 1) * LN, size * LN, scratch + pw * LN, (size - 1) * LN, static_cast<int>(L),
+                                    static_cast<int>(B), true, st, "dot_sk");
+        p.polys = scratch;
+        p.ct_stride = (size - 1) * LN;
+        p.c0 = nullptr;
+        GSB_LAUNCH("dot_sk", "coeff", dot_sk_kernel, dim3(grid_for(p.pairs, 256)), dim3(256), 0, st, p);
+        ntt_inverse_plain<LOGN>(tab, mm, out, LN, out, LN, static_cast<int>(L), static_cast<int>(B), false, st, "dot_sk");
+        // add_poly_coeffmod(destination, c_0) (:265): c_0 of ciphertext b sits at in + b*size*LN
+        for (size_t b = 0; b < B; b++)
+        {
+            PolyOpArgs a{};
+            a.a = out + b * LN;
+            a.b = in + b * size * LN;
+            a.out = out + b * LN;
+            a.limb = ctx->d_limb;
+            a.N = static_cast<uint32_t>(N);
+            a.n_limbs = static_cast<uint32_t>(L);
+            a.total = LN;
+            launch_poly_op(GSB_OP_ADD, a, st);
+        }
     }
 
     static void check_batch(const gsb_ctx *ctx, size_t batch, size_t L, size_t min_L)
@@ -968,6 +1067,96 @@ int gsb_bfv_apply_galois_host(gsb_ctx *ctx, uint32_t galois_elt, const uint64_t 
     const size_t w = ctx ? L * ctx->N : 0;
     return host_call(ctx, in, 2 * w, nullptr, 0, out, 2 * w, batch, [&](gsb_ws *ws, uint64_t *di, uint64_t *, uint64_t *dout, size_t B, void *st) {
         return gsb_bfv_apply_galois_dev(ctx, ws, galois_elt, di, dout, B, L, st);
+    });
+}
+
+// ---- Decryptor ---------------------------------------------------------------
+int gsb_secret_key_set(gsb_ctx *ctx, const uint64_t *sk_host)
+{
+    return guarded([&] {
+        require(ctx != nullptr && sk_host != nullptr, GSB_E_INVALID_ARG, "null argument");
+        // Decryptor::Decryptor (decryptor.cpp:34-37) -> is_valid_for(SecretKey): canonical residues at key level
+        for (size_t i = 0; i < ctx->K; i++)
+        {
+            const uint64_t q = ctx->tables[i].mod.q;
+            for (size_t d = 0; d < ctx->N; d++)
+                require(sk_host[i * ctx->N + d] < q, GSB_E_INVALID_ARG, "secret key is not valid for encryption parameters");
+        }
+        GSB_CUDA_CHECK(cudaSetDevice(ctx->device));
+        uint64_t *d = nullptr;
+        const size_t bytes = ctx->K * ctx->N * sizeof(uint64_t);
+        GSB_CUDA_CHECK(cudaMalloc(reinterpret_cast<void **>(&d), bytes));
+        GSB_CUDA_CHECK(cudaMemcpy(d, sk_host, bytes, cudaMemcpyHostToDevice));
+        std::lock_guard<std::mutex> lock(ctx->mu);
+        if (ctx->d_sk)
+            ctx->sk_retired.push_back(ctx->d_sk);
+        ctx->d_sk = d;
+        ctx->sk_powers = 1;
+    });
+}
+
+int gsb_dot_product_ct_sk_dev(
+    gsb_ctx *ctx, gsb_ws *ws, const uint64_t *in, uint64_t *out, size_t batch, size_t size, size_t L, int ntt_form, void *stream)
+{
+    return guarded([&] {
+        check_batch(ctx, batch, L, 1);
+        require(in && out && size >= 2 && size <= 16, GSB_E_INVALID_ARG, "invalid ciphertext");
+        GSB_CUDA_CHECK(cudaSetDevice(ctx->device));
+        gsb_ws *w = pick_ws(ctx, ws);
+        cudaStream_t st = static_cast<cudaStream_t>(stream);
+        const size_t LN = L * ctx->N, per = ntt_form ? 0 : (size - 1) * LN;
+        const size_t chunk = ntt_form ? batch : chunk_for(per, batch);
+        uint64_t *scratch = per ? static_cast<uint64_t *>(w->reserve((chunk * per + 1024) * sizeof(uint64_t))) : nullptr;
+        for (size_t b0 = 0; b0 < batch; b0 += chunk)
+        {
+            const size_t B = std::min(chunk, batch - b0);
+            GSB_DISPATCH_LOGN(ctx->logn, dot_sk_core<LOGN>(ctx, scratch, in + b0 * size * LN, out + b0 * LN, B, size, L, ntt_form != 0, st));
+        }
+        GSB_CUDA_CHECK(cudaGetLastError());
+    });
+}
+
+int gsb_bfv_decrypt_dev(
+    gsb_ctx *ctx, gsb_ws *ws, uint64_t plain_modulus, const uint64_t *in, uint64_t *out, size_t batch, size_t size, size_t L, void *stream)
+{
+    return guarded([&] {
+        check_batch(ctx, batch, L, 1);
+        require(in && out && size >= 2 && size <= 16, GSB_E_INVALID_ARG, "invalid ciphertext");
+        require(plain_modulus >= 2 && (plain_modulus >> 60) == 0, GSB_E_INVALID_ARG, "plain_modulus out of range");
+        GSB_CUDA_CHECK(cudaSetDevice(ctx->device));
+        const BfvTool &tool = ctx->bfv_tool(L, plain_modulus);
+        gsb_ws *w = pick_ws(ctx, ws);
+        cudaStream_t st = static_cast<cudaStream_t>(stream);
+        const size_t N = ctx->N, LN = L * N, per = (size - 1) * LN + LN, chunk = chunk_for(per, batch);
+        uint64_t *scratch = static_cast<uint64_t *>(w->reserve((chunk * per + 1024) * sizeof(uint64_t)));
+        for (size_t b0 = 0; b0 < batch; b0 += chunk)
+        {
+            const size_t B = std::min(chunk, batch - b0);
+            uint64_t *dot = scratch + B * (size - 1) * LN;
+            GSB_DISPATCH_LOGN(ctx->logn, dot_sk_core<LOGN>(ctx, scratch, in + b0 * size * LN, dot, B, size, L, false, st));
+            DecryptRoundArgs p = tool.dec;
+            p.dot = dot;
+            p.out = out + b0 * N;
+            p.total = B * N;
+            GSB_LAUNCH("bfv_decrypt", "", decrypt_round_kernel, dim3(grid_for(p.total, 256)), dim3(256), 0, st, p);
+        }
+        GSB_CUDA_CHECK(cudaGetLastError());
+    });
+}
+
+int gsb_dot_product_ct_sk_host(gsb_ctx *ctx, const uint64_t *in, uint64_t *out, size_t batch, size_t size, size_t L, int ntt_form)
+{
+    const size_t w = ctx ? L * ctx->N : 0;
+    return host_call(ctx, in, size * w, nullptr, 0, out, w, batch, [&](gsb_ws *ws, uint64_t *di, uint64_t *, uint64_t *dout, size_t B, void *st) {
+        return gsb_dot_product_ct_sk_dev(ctx, ws, di, dout, B, size, L, ntt_form, st);
+    });
+}
+
+int gsb_bfv_decrypt_host(gsb_ctx *ctx, uint64_t plain_modulus, const uint64_t *in, uint64_t *out, size_t batch, size_t size, size_t L)
+{
+    const size_t w = ctx ? L * ctx->N : 0;
+    return host_call(ctx, in, size * w, nullptr, 0, out, ctx ? ctx->N : 0, batch, [&](gsb_ws *ws, uint64_t *di, uint64_t *, uint64_t *dout, size_t B, void *st) {
+        return gsb_bfv_decrypt_dev(ctx, ws, plain_modulus, di, dout, B, size, L, st);
     });
 }
 

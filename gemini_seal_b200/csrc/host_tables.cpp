@@ -320,8 +320,26 @@ namespace gsb
             o.prod_b_mod_q.resize(L);
             for (size_t i = 0; i < L; i++)
                 o.prod_b_mod_q[i] = punctured(B, o.nB, q[i]);
-            return inv_mod(punctured(B, o.nB, o.m_sk), o.m_sk, o.inv_prod_b_mod_msk) &&
-                   inv_mod(punctured(Q, L, m_tilde), m_tilde, o.inv_prod_q_mod_mtilde);
+            if (!inv_mod(punctured(B, o.nB, o.m_sk), o.m_sk, o.inv_prod_b_mod_msk) ||
+                !inv_mod(punctured(Q, L, m_tilde), m_tilde, o.inv_prod_q_mod_mtilde))
+                return false;
+            // {t, gamma} side (rns.cpp:603-608, 690-717); gamma is the second sampled prime (:590)
+            o.gamma = primes[1];
+            const uint64_t tg[2] = { t, o.gamma };
+            o.prod_tg_mod_q.resize(L);
+            for (size_t i = 0; i < L; i++)
+                o.prod_tg_mod_q[i] = mul_mod(t % q[i], o.gamma % q[i], make_mod(q[i]));
+            o.mat_tg.resize(2 * L);
+            for (size_t j = 0; j < 2; j++)
+            {
+                for (size_t i = 0; i < L; i++)
+                    o.mat_tg[j * L + i] = punctured(Q, i, tg[j]);
+                uint64_t inv = 0;
+                if (!inv_mod(punctured(Q, L, tg[j]), tg[j], inv))
+                    return false;
+                o.neg_inv_q_mod_tg[j] = inv ? tg[j] - inv : 0;
+            }
+            return inv_mod(o.gamma % t, t, o.inv_gamma_mod_t);
         }
     } // namespace host
 } // namespace gsb

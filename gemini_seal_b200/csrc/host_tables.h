@@ -51,6 +51,11 @@ namespace gsb
             std::vector<uint64_t> prod_q_mod_bsk, inv_prod_q_mod_bsk, inv_mtilde_mod_bsk; // [nBsk]
             std::vector<uint64_t> prod_b_mod_q;   // [L]
             uint64_t inv_prod_q_mod_mtilde = 0, inv_prod_b_mod_msk = 0;
+            // decrypt_scale_and_round (util/rns.cpp:585-590, 603-608, 690-717, 1070-1126); t > 0 only
+            uint64_t gamma = 0, inv_gamma_mod_t = 0;
+            std::vector<uint64_t> prod_tg_mod_q;  // [L]    t * gamma mod q_i
+            std::vector<uint64_t> mat_tg;         // [2][L] prod_{l != i} q_l mod {t, gamma}
+            uint64_t neg_inv_q_mod_tg[2] = { 0, 0 }; // -(prod q)^-1 mod {t, gamma}
         };
         // false when the auxiliary base cannot be built (not enough primes / not invertible)
         bool build_behz(int logn, const uint64_t *q, size_t L, uint64_t t, BehzConsts &out);

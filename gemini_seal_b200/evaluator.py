@@ -421,3 +421,48 @@ class BfvEvaluator(Evaluator):
         raise NotImplementedError("not part of the BFV surface built so far (no CPU fallback)")
 
     mul_relin_rescale = rescale_to_next = multiply_plain = _unsupported
+
+
+class Decryptor:
+    """Mirror of seal::Decryptor (decryptor.h / decryptor.cpp; SURVEY 8(f) row f4) on raw limb buffers.
+
+    `secret_key` is SecretKey::data() as the reference stores it: NTT form at key level, uint64 [K][N].
+    CKKS (plain_modulus None): decrypt(c) = dot_product_ct_sk_array(c) (decryptor.cpp:115-149, 218-265),
+    [B][size][L][N] NTT form -> plaintexts [B][L][N].  BFV: decrypt(c) = bfv_decrypt (decryptor.cpp:76-113):
+    coefficient-form ciphertexts -> [B][N] plaintext coefficients mod t (leading zeros not trimmed)."""
+
+    def __init__(self, context, secret_key, plain_modulus=None, workspace=None):
+        self.ctx, self.lib, self.workspace = context, context.lib, workspace
+        self.plain_modulus = None if plain_modulus is None else int(plain_modulus)
+        sk = np.ascontiguousarray(secret_key, dtype=np.uint64)
+        if sk.shape != (context.K, context.N):
+            raise ValueError("secret key is not valid for encryption parameters")
+        _check(self.lib, self.lib.gsb_secret_key_set(context.handle, _ptr(sk)))
+
+    @property
+    def _ws(self):
+        return self.workspace.handle if self.workspace is not None else None
+
+    def dot_product_ct_sk_array(self, c, ntt_form):
+        if c.ndim != 4 or c.shape[-1] != self.ctx.N or c.shape[1] < 2:
+            raise ValueError("encrypted is not valid for encryption parameters")
+        B, size, L = c.shape[0], c.shape[1], c.shape[2]
+        out = _empty_like(c, (B, L, self.ctx.N))
+        if _is_torch(c):
+            _check(self.lib, self.lib.gsb_dot_product_ct_sk_dev(self.ctx.handle, self._ws, _ptr(c), _ptr(out), B, size, L, 1 if ntt_form else 0, _stream()))
+        else:
+            _check(self.lib, self.lib.gsb_dot_product_ct_sk_host(self.ctx.handle, _ptr(c), _ptr(out), B, size, L, 1 if ntt_form else 0))
+        return out
+
+    def decrypt(self, c):
+        if self.plain_modulus is None:
+            return self.dot_product_ct_sk_array(c, True)
+        if c.ndim != 4 or c.shape[-1] != self.ctx.N or c.shape[1] < 2:
+            raise ValueError("encrypted is not valid for encryption parameters")
+        B, size, L = c.shape[0], c.shape[1], c.shape[2]
+        out = _empty_like(c, (B, self.ctx.N))
+        if _is_torch(c):
+            _check(self.lib, self.lib.gsb_bfv_decrypt_dev(self.ctx.handle, self._ws, self.plain_modulus, _ptr(c), _ptr(out), B, size, L, _stream()))
+        else:
+            _check(self.lib, self.lib.gsb_bfv_decrypt_host(self.ctx.handle, self.plain_modulus, _ptr(c), _ptr(out), B, size, L))
+        return out

@@ -198,6 +198,23 @@ int gsb_rescale_host(gsb_ctx *ctx, const uint64_t *in, uint64_t *out, size_t bat
 int gsb_apply_galois_host(gsb_ctx *ctx, uint32_t galois_elt, const uint64_t *in, uint64_t *out, size_t batch, size_t L);
 int gsb_mul_relin_rescale_host(gsb_ctx *ctx, const uint64_t *a, const uint64_t *b, uint64_t *out, size_t batch, size_t L);
 
+/* ---- Decryptor (seal::Decryptor, decryptor.cpp) --------------------------------
+ * gsb_secret_key_set: SecretKey::data() in NTT form at key level, sk_host = [K][N] canonical residues
+ * (Decryptor::Decryptor, decryptor.cpp:21-58; rejects what is_valid_for(SecretKey) rejects).  Powers
+ * s^2.. are computed on the device on demand (compute_secret_key_array, decryptor.cpp:151-216).
+ * gsb_dot_product_ct_sk_*: Decryptor::dot_product_ct_sk_array (decryptor.cpp:218-265):
+ *   in = [batch][size][L][N] -> out = [batch][L][N] = c_0 + c_1 s + ... + c_{size-1} s^{size-1} mod q_i;
+ *   ntt_form = Ciphertext::is_ntt_form(): 1 (CKKS; this IS Decryptor::ckks_decrypt's plaintext,
+ *   decryptor.cpp:115-149), 0 (BFV: lazy NTT, dyadic products, inverse NTT, + c_0).
+ * gsb_bfv_decrypt_*: Decryptor::bfv_decrypt (decryptor.cpp:76-113) = the dot product followed by
+ *   RNSTool::decrypt_scale_and_round (util/rns.cpp:1070-1126); out = [batch][N] plaintext coefficients
+ *   mod plain_modulus (the caller trims leading zeros as the reference does at :107-111). */
+int gsb_secret_key_set(gsb_ctx *ctx, const uint64_t *sk_host);
+int gsb_dot_product_ct_sk_dev(gsb_ctx *ctx, gsb_ws *ws, const uint64_t *in, uint64_t *out, size_t batch, size_t size, size_t L, int ntt_form, void *stream);
+int gsb_dot_product_ct_sk_host(gsb_ctx *ctx, const uint64_t *in, uint64_t *out, size_t batch, size_t size, size_t L, int ntt_form);
+int gsb_bfv_decrypt_dev(gsb_ctx *ctx, gsb_ws *ws, uint64_t plain_modulus, const uint64_t *in, uint64_t *out, size_t batch, size_t size, size_t L, void *stream);
+int gsb_bfv_decrypt_host(gsb_ctx *ctx, uint64_t plain_modulus, const uint64_t *in, uint64_t *out, size_t batch, size_t size, size_t L);
+
 /* ---- integer-pipe roofline (measurement aid, not part of the reference's interface) -------------
  * Register-resident microbenchmarks on ctx's device with `ctas_per_sm` x 256 threads per SM:
  * 32-bit IMAD/s, IMAD.WIDE.U32/s and forward lazy Harvey butterflies/s (the exact butterfly of the

@@ -65,6 +65,8 @@ class Oracle:
         lib.so_bfv_aux_base.argtypes = [i32, C.POINTER(u64), sz, u64, vp]
         lib.so_apply_galois_bfv.argtypes = [vp, sz, u32, vp, vp, vp]
         lib.so_apply_galois_coeff.argtypes = [i32, u32, u64, vp, vp]
+        lib.so_dot_product_ct_sk.argtypes = [vp, sz, sz, vp, vp, i32, vp]
+        lib.so_bfv_decrypt.argtypes = [vp, sz, sz, u64, vp, vp, vp]
         lib.so_const_ratio.argtypes = [u64, C.POINTER(u64)]
         lib.so_barrett_reduce_128.argtypes = [u64, u64, u64, C.POINTER(u64)]
         lib.so_barrett_reduce_128.restype = u64
@@ -211,6 +213,20 @@ class OracleCtx:
         return out
 
 
+    # -- Decryptor (row f4): ct [size][L][N], sk [K][N] NTT form at key level
+    def dot_product_ct_sk(self, ct, sk, ntt_form):
+        size, L = ct.shape[0], ct.shape[1]
+        out = np.empty((L, self.N), dtype=np.uint64)
+        assert self.lib.so_dot_product_ct_sk(self.h, L, size, _p(ct), _p(sk), 1 if ntt_form else 0, _p(out)) == 0
+        return out
+
+    def bfv_decrypt(self, ct, sk, plain_modulus):
+        size, L = ct.shape[0], ct.shape[1]
+        out = np.empty((self.N,), dtype=np.uint64)
+        assert self.lib.so_bfv_decrypt(self.h, L, size, plain_modulus, _p(ct), _p(sk), _p(out)) == 0
+        return out
+
+
 class RefLib:
     """The unmodified reference behind oracle/ref_harness.cpp.  Raises FileNotFoundError when the
     harness has not been built (it can only be built where /root/reference exists)."""
@@ -248,6 +264,7 @@ class RefLib:
         lib.ref_elt_from_step.restype = u32
         lib.ref_time_ops.argtypes = [vp, i32, sz, sz, i32, u64]
         lib.ref_time_ops.restype = C.c_double
+        lib.ref_decrypt.argtypes = [vp, vp, sz, sz, vp, vp]
 
     def err(self):
         return (self.lib.ref_last_error() or b"").decode()
@@ -385,6 +402,13 @@ class RefCtx:
 
     def elt_from_step(self, step):
         return self.lib.ref_elt_from_step(self.h, step)
+
+    def decrypt(self, ct, sk, bfv=False):
+        """Decryptor::decrypt with the secret key given as NTT-form limbs [K][N]: CKKS -> [L][N], BFV -> [N]."""
+        size, L = ct.shape[0], ct.shape[1]
+        out = np.empty((self.N,) if bfv else (L, self.N), dtype=np.uint64)
+        self._run(self.lib.ref_decrypt(self.h, _p(np.ascontiguousarray(sk)), L, size, _p(ct), _p(out)))
+        return out
 
     def time_ops(self, what, L, ops, n_threads, seed=1):
         s = self.lib.ref_time_ops(self.h, what, L, ops, n_threads, seed)

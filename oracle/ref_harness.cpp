@@ -466,6 +466,32 @@ extern "C"
     }
 
     // ---- CPU baseline timing (bench.py cpu_baseline / --impl reference) ---------------------------
+    // Decryptor::decrypt (decryptor.cpp:60-151) with the secret key given as raw NTT-form limbs at key
+    // level, sk_limbs = [K][N] (any canonical residues pass is_valid_for).  in = [size][L][N].
+    // CKKS: out = [L][N], the plaintext = dot_product_ct_sk_array's result.  BFV: out = [N] plaintext
+    // coefficients mod t (zero-padded past Plaintext::coeff_count()).
+    int ref_decrypt(void *h, const uint64_t *sk_limbs, size_t L, size_t size, const uint64_t *in, uint64_t *out)
+    {
+        auto *c = static_cast<RefCtx *>(h);
+        return guarded([&] {
+            SecretKey sk;
+            sk.data().resize(c->K * c->N);
+            std::memcpy(sk.data().data(), sk_limbs, c->K * c->N * sizeof(uint64_t));
+            sk.parms_id() = c->context->key_parms_id();
+            Decryptor dec(c->context, sk);
+            auto x = c->make_ct(in, size, L, std::pow(2.0, 40));
+            Plaintext p;
+            dec.decrypt(x, p);
+            if (c->bfv)
+            {
+                std::memset(out, 0, c->N * sizeof(uint64_t));
+                std::memcpy(out, p.data(), p.coeff_count() * sizeof(uint64_t));
+            }
+            else
+                std::memcpy(out, p.data(), L * c->N * sizeof(uint64_t));
+        });
+    }
+
     // Runs `ops` units of work spread over n_threads host threads sharing one Evaluator (const
     // re-entrant) and returns wall seconds, or a negative error code.
     // what: 0 = mul+relin+rescale, 1 = rotate_vector(ct, 1), 2 = strict fwd limb-NTT, 3 = strict inv limb-NTT

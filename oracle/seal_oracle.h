@@ -99,6 +99,12 @@ int so_apply_galois_bfv(const so_ctx *c, size_t L, uint32_t elt, const uint64_t 
 int so_bfv_multiply(int logn, const uint64_t *q, size_t L, uint64_t plain_modulus, const uint64_t *a, const uint64_t *b, uint64_t *out);
 /* out[0] = |B|, out[1..] = the |B|+1 moduli of Bsk (rns.cpp:585-603) */
 int so_bfv_aux_base(int logn, const uint64_t *q, size_t L, uint64_t plain_modulus, uint64_t *out);
+/* ---- Decryptor (seal_oracle_bfv.c) -------------------------------------- */
+/* dot_product_ct_sk_array (decryptor.cpp:218-265): ct [size][L][N], sk [K][N] (NTT form, key level) ->
+ * out [L][N] = c0 + c1 s + ... ; this is also Decryptor::ckks_decrypt's plaintext (ntt_form = 1) */
+int so_dot_product_ct_sk(const so_ctx *c, size_t L, size_t size, const uint64_t *ct, const uint64_t *sk, int ntt_form, uint64_t *out);
+/* Decryptor::bfv_decrypt (decryptor.cpp:76-113, util/rns.cpp:1070-1126) -> out [N] coefficients mod t */
+int so_bfv_decrypt(const so_ctx *c, size_t L, size_t size, uint64_t plain_modulus, const uint64_t *ct, const uint64_t *sk, uint64_t *out);
 /* a,b [2][L][N] -> out [2][L-1][N] */
 int so_mul_relin_rescale(const so_ctx *c, size_t L, const uint64_t *a, const uint64_t *b, const uint64_t *key, uint64_t *out);
 

@@ -465,3 +465,136 @@ int so_bfv_aux_base(int logn, const uint64_t *q, size_t L, uint64_t plain_modulu
     free(z);
     return 0;
 }
+
+/* ---- Decryptor ---------------------------------------------------------------
+ * dot_product_ct_sk_array (decryptor.cpp:218-265), compute_secret_key_array (:151-216), bfv_decrypt
+ * (:76-113) and RNSTool::decrypt_scale_and_round (util/rns.cpp:1070-1126) with the {t, gamma}
+ * constants of RNSTool::initialize (:585-590, :603-608, :634-638, :690-717).  Pinned against the
+ * unmodified reference's Decryptor::decrypt (tests/test_oracle_pins.py). */
+
+/* ct [size][L][N] at level L; sk = NTT-form secret key at key level [K][N]; out [L][N].
+ * ntt_form = Ciphertext::is_ntt_form (1 CKKS, 0 BFV). */
+int so_dot_product_ct_sk(const so_ctx *c, size_t L, size_t size, const uint64_t *ct, const uint64_t *sk, int ntt_form, uint64_t *out)
+{
+    const size_t N = c->N, K = c->K;
+    if (size < 2 || L < 1 || L > c->L0)
+        return -1;
+    /* secret key powers s^1 .. s^(size-1) at key level (:191-199) */
+    uint64_t *pw = (uint64_t *)malloc((size - 1) * K * N * 8);
+    memcpy(pw, sk, K * N * 8);
+    for (size_t p = 1; p + 1 < size; p++)
+        for (size_t i = 0; i < K; i++)
+            so_poly_op(0, c->q[i], pw + ((p - 1) * K + i) * N, pw + i * N, 0, N, pw + (p * K + i) * N);
+    uint64_t *copy = (uint64_t *)malloc((size - 1) * L * N * 8);
+    memcpy(copy, ct + L * N, (size - 1) * L * N * 8); /* :237-238 */
+    for (size_t p = 0; p + 1 < size; p++)
+        for (size_t i = 0; i < L; i++)
+        {
+            uint64_t *x = copy + (p * L + i) * N;
+            if (!ntt_form)
+                so_ntt_fwd_lazy(x, &c->tab[i]);                                   /* :241-244 */
+            so_poly_op(0, c->q[i], x, pw + (p * K + i) * N, 0, N, x);             /* :247-250 */
+        }
+    memset(out, 0, L * N * 8); /* :253 */
+    for (size_t p = 0; p + 1 < size; p++)
+        for (size_t i = 0; i < L; i++)
+            so_poly_op(1, c->q[i], out + i * N, copy + (p * L + i) * N, 0, N, out + i * N); /* :254-256 */
+    for (size_t i = 0; i < L; i++)
+    {
+        if (!ntt_form)
+            so_ntt_inv(out + i * N, &c->tab[i]);                                  /* :258-262 */
+        so_poly_op(1, c->q[i], out + i * N, ct + i * N, 0, N, out + i * N);       /* :265 */
+    }
+    free(copy);
+    free(pw);
+    return 0;
+}
+
+/* out [N] = plaintext coefficients mod t (the reference then trims leading zeros, :107-111) */
+int so_bfv_decrypt(const so_ctx *c, size_t L, size_t size, uint64_t plain_modulus, const uint64_t *ct, const uint64_t *sk, uint64_t *out)
+{
+    const size_t N = c->N;
+    if (L + 3 > MAXB)
+        return -1;
+    uint64_t *dot = (uint64_t *)malloc(L * N * 8);
+    if (so_dot_product_ct_sk(c, L, size, ct, sk, 0, dot))
+    {
+        free(dot);
+        return -1;
+    }
+    /* constants (rns.cpp:585-590: the second sampled prime is gamma) */
+    uint64_t primes[MAXB];
+    {
+        int t_bits = 0;
+        for (uint64_t x = plain_modulus; x; x >>= 1)
+            t_bits++;
+        size_t nB = L;
+        if (32 + t_bits + product_bit_count(c->q, L) >= 61 * (int)L + 61)
+            nB++;
+        if (get_primes(N, 60, nB + 2, primes))
+        {
+            free(dot);
+            return -1;
+        }
+    }
+    mod_t t, gamma, q[MAXB];
+    mod_set(&t, plain_modulus);
+    mod_set(&gamma, primes[1]);
+    const uint64_t tg[2] = { plain_modulus, primes[1] };
+    conv_t *cv = (conv_t *)malloc(sizeof(conv_t));
+    if (conv_init(cv, c->q, L, tg, 2))
+    {
+        free(cv);
+        free(dot);
+        return -1;
+    }
+    uint64_t inv_gamma_mod_t, neg_inv_q[2], prod_tg_mod_q[MAXB];
+    int ok = so_try_invert_uint_mod(gamma.v % t.v, t.v, &inv_gamma_mod_t);          /* :693 */
+    for (size_t i = 0; i < L; i++)
+    {
+        mod_set(&q[i], c->q[i]);
+        prod_tg_mod_q[i] = mm(t.v, gamma.v, &q[i]);                                  /* :699-704 */
+    }
+    for (size_t j = 0; j < 2; j++)                                                    /* :706-716 */
+    {
+        uint64_t p = 1 % tg[j];
+        for (size_t l = 0; l < L; l++)
+            p = mulmod(p, c->q[l] % tg[j], tg[j]);
+        ok = ok && so_try_invert_uint_mod(p, tg[j], &neg_inv_q[j]);
+        neg_inv_q[j] = so_negate_uint_mod(neg_inv_q[j], tg[j]);
+    }
+    if (!ok)
+    {
+        free(cv);
+        free(dot);
+        return -1;
+    }
+    /* decrypt_scale_and_round (:1070-1126) */
+    uint64_t *temp = (uint64_t *)malloc(L * N * 8), *ttg = (uint64_t *)malloc(2 * N * 8);
+    for (size_t i = 0; i < L; i++)
+        for (size_t d = 0; d < N; d++)
+            temp[i * N + d] = mm(dot[i * N + d], prod_tg_mod_q[i], &q[i]);           /* :1077-1082 */
+    conv_array(cv, temp, N, ttg);                                                    /* :1088 */
+    for (size_t d = 0; d < N; d++)                                                   /* :1091-1096 */
+    {
+        ttg[d] = mm(ttg[d], neg_inv_q[0], &t);
+        ttg[N + d] = mm(ttg[N + d], neg_inv_q[1], &gamma);
+    }
+    const uint64_t gamma_div_2 = gamma.v >> 1;
+    for (size_t d = 0; d < N; d++)                                                   /* :1104-1125 */
+    {
+        uint64_t v;
+        if (ttg[N + d] > gamma_div_2)
+            v = so_add_uint_mod(ttg[d], (gamma.v - ttg[N + d]) % t.v, t.v);
+        else
+            v = so_sub_uint_mod(ttg[d], ttg[N + d] % t.v, t.v);
+        if (v != 0)
+            v = mm(v, inv_gamma_mod_t, &t);
+        out[d] = v;
+    }
+    free(temp);
+    free(ttg);
+    free(cv);
+    free(dot);
+    return 0;
+}

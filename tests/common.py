@@ -4,6 +4,7 @@ the test-only simulator build of the same kernel sources (CPU)."""
 import hashlib
 
 import numpy as np
+import pytest
 
 
 def is_prime(n):
@@ -157,4 +158,35 @@ def fuzz_against_oracle(lib, oracle, seed, n_configs, max_logn=13):
             ms = bev.mod_switch_to_next(b3)
             for i in range(batch):
                 assert np.array_equal(ms[i], oc.mod_switch_bfv(b3[i])), ("bfv mod_switch", what)
+        ctx.close()
+
+
+def check_decrypt(lib, oracle, logn=11, to_device=None):
+    """Decryptor mirror (CKKS dot product, BFV dot product + decrypt_scale_and_round)
+    against the oracle on every level, sizes 2..4 (secret-key powers up to s^3), batch 3."""
+    import gemini_seal_b200 as g
+    to_device = to_device or (lambda x: x)
+    back = lambda x: x if isinstance(x, np.ndarray) else x.cpu().numpy().view(np.uint64)
+    N = 1 << logn
+    for bits, k, t in [([50, 40, 45, 51], 1, 65537), ([36, 36, 37, 58, 59], 2, 786433)]:
+        mods = mixed_moduli(logn, bits)
+        ctx = g.Context(N, mods, k, lib=lib)
+        oc = oracle.context(logn, mods, k)
+        rng = np.random.default_rng(logn * 7 + k)
+        sk = rand_poly(rng, mods, (), N)
+        ckks, bfv = g.Decryptor(ctx, sk), g.Decryptor(ctx, sk, plain_modulus=t)
+        for size in (3, 2, 4):  # 3 first: the power array is extended, then reused, then extended again
+            for L in range(1, len(mods) - k + 1):
+                c = rand_poly(rng, mods[:L], (3, size), N)
+                got = back(ckks.decrypt(to_device(c)))
+                coef = back(bfv.dot_product_ct_sk_array(to_device(c), False))
+                plain = back(bfv.decrypt(to_device(c)))
+                for i in range(3):
+                    assert np.array_equal(got[i], oc.dot_product_ct_sk(c[i], sk, True)), ("ckks", bits, size, L)
+                    assert np.array_equal(coef[i], oc.dot_product_ct_sk(c[i], sk, False)), ("bfv dot", bits, size, L)
+                    assert np.array_equal(plain[i], oc.bfv_decrypt(c[i], sk, t)), ("bfv decrypt", bits, size, L)
+        with pytest.raises(ValueError):  # is_valid_for(SecretKey): non-canonical residue
+            bad = sk.copy()
+            bad[0, 0] = mods[0]
+            g.Decryptor(ctx, bad)
         ctx.close()

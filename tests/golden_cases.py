@@ -74,7 +74,8 @@ def eval_inputs(name):
     return dict(
         logn=logn, N=N, mods=mods, k=k, L=L, batch=batch, step=step,
         a=rand_poly(rng, mods[:L], (batch, 2), N), b=rand_poly(rng, mods[:L], (batch, 2), N),
-        relin=rand_key(rng, mods, nb, N), galois=rand_key(rng, mods, nb, N))
+        relin=rand_key(rng, mods, nb, N), galois=rand_key(rng, mods, nb, N),
+        sk=rand_poly(rng, mods, (), N))  # drawn last: a synthetic NTT-form secret key at key level (row f4)
 
 
 def bfv_inputs(name):
@@ -86,7 +87,8 @@ def bfv_inputs(name):
     return dict(
         logn=logn, N=N, mods=mods, k=k, L=L, batch=batch, step=step, t=t,
         a=rand_poly(rng, mods[:L], (batch, 2), N), b=rand_poly(rng, mods[:L], (batch, 2), N),
-        relin=rand_key(rng, mods, nb, N), galois=rand_key(rng, mods, nb, N), conj=rand_key(rng, mods, nb, N))
+        relin=rand_key(rng, mods, nb, N), galois=rand_key(rng, mods, nb, N), conj=rand_key(rng, mods, nb, N),
+        sk=rand_poly(rng, mods, (), N))
 
 
 def ntt_inputs(name):
@@ -115,6 +117,8 @@ def run_case(name, be):
             out["bfv_mod_switch"] = digest(be.mod_switch(c3))
         out["bfv_rotate_rows"] = digest(be.apply_galois(c["a"], elt))
         out["bfv_rotate_columns"] = digest(be.apply_galois(c["b"], conj))
+        out["bfv_decrypt"] = digest(be.decrypt(c["a"], c["sk"]))    # Decryptor::bfv_decrypt, size 2
+        out["bfv_decrypt3"] = digest(be.decrypt(c3, c["sk"]))       # size 3: uses s^2
         return out
     c = eval_inputs(name)
     be.setup(c["logn"], c["mods"], c["k"])
@@ -128,6 +132,8 @@ def run_case(name, be):
         out["rescale"] = digest(be.rescale(c2))
         out["mul_relin_rescale"] = digest(be.mul_relin_rescale(c["a"], c["b"]))
     out["rotate"] = digest(be.apply_galois(c["a"], elt))
+    out["decrypt"] = digest(be.decrypt(c["a"], c["sk"]))            # Decryptor::ckks_decrypt, size 2
+    out["decrypt3"] = digest(be.decrypt(c3, c["sk"]))               # size 3: uses s^2
     return out
 
 
@@ -180,6 +186,12 @@ class OracleBackend(_PerCt):
         return self.each(lambda x: self.c.apply_galois(x, elt, self.gal[elt]), c)
 
 
+    def decrypt(self, c, sk):
+        if self.t is not None:
+            return self.each(lambda x: self.c.bfv_decrypt(x, sk, self.t), c)
+        return self.each(lambda x: self.c.dot_product_ct_sk(x, sk, True), c)
+
+
 class RefBackend(_PerCt):
     """The unmodified reference (oracle/_ref); used by make_golden.py only."""
 
@@ -193,7 +205,11 @@ class RefBackend(_PerCt):
         return out
 
     def setup(self, logn, mods, k, bfv_t=None):
+        self.bfv = bfv_t is not None
         self.c = self.r.context(1 << logn, mods, k, bfv_plain_modulus=bfv_t)
+
+    def decrypt(self, c, sk):
+        return self.each(lambda x: self.c.decrypt(x, sk, bfv=self.bfv), c)
 
     def elt_from_step(self, logn, step):
         return self.c.elt_from_step(step)
@@ -251,6 +267,7 @@ class DeviceBackend:
             self.ctx.close()
         self.ctx = self._ctx(logn, mods, k)
         self.ev = Evaluator(self.ctx) if bfv_t is None else BfvEvaluator(self.ctx, bfv_t)
+        self.t = bfv_t
 
     def elt_from_step(self, logn, step):
         return self.ctx.galois_elt_from_step(step)
@@ -278,3 +295,7 @@ class DeviceBackend:
 
     def apply_galois(self, c, elt):
         return self.ev.apply_galois(c, elt)
+
+    def decrypt(self, c, sk):
+        from gemini_seal_b200 import Decryptor
+        return Decryptor(self.ctx, sk, plain_modulus=self.t).decrypt(c)

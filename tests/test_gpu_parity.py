@@ -147,6 +147,14 @@ def test_thin_evaluator_ops(cudalib, oracle):
     check_thin_ops(cudalib, oracle, logn=12, to_device=lambda x: torch.from_numpy(x.view(np.int64)).cuda())
 
 
+def test_decryptor(cudalib, oracle):
+    """Row f4 on host buffers (N = 2^13, two-pass NTT) and on device buffers (N = 2^11)."""
+    import torch
+    from common import check_decrypt
+    check_decrypt(cudalib, oracle, logn=13)
+    check_decrypt(cudalib, oracle, logn=11, to_device=lambda x: torch.from_numpy(x.view(np.int64)).cuda())
+
+
 @pytest.mark.parametrize("seed", [1, 2, 3])
 def test_fuzz_against_oracle(cudalib, oracle, seed):
     """Random parameter sets (k = 1..3, ragged bundles, 30..60-bit primes, CKKS + BFV) vs the oracle."""

@@ -207,6 +207,23 @@ def test_bfv_branches_vs_reference(oracle, reflib):
             assert np.array_equal(oc.apply_galois_bfv(a, e, rc.get_key(1, e)), rc.apply_galois(a, e))
 
 
+def test_decryptor_vs_reference(oracle, reflib):
+    """Row f4: the restated dot_product_ct_sk_array / bfv_decrypt against seal::Decryptor::decrypt of the
+    unmodified reference, every level, ciphertext sizes 2 and 3, k = 1 and 2, synthetic secret key limbs."""
+    from common import mixed_moduli, rand_poly
+    for logn, bits, k, t in [(10, [40, 40, 41, 42], 1, 65537), (11, [50, 50, 50, 51, 51], 2, 65537), (12, [36, 36, 37], 1, 786433)]:
+        N, mods = 1 << logn, mixed_moduli(logn, bits)
+        rc, rb = reflib.context(N, mods, k), reflib.context(N, mods, k, bfv_plain_modulus=t)
+        oc = oracle.context(logn, mods, k)
+        rng = np.random.default_rng(logn)
+        sk = rand_poly(rng, mods, (), N)
+        for size in (2, 3):
+            for L in range(1, len(mods) - k + 1):
+                c = rand_poly(rng, mods[:L], (size,), N)
+                assert np.array_equal(oc.dot_product_ct_sk(c, sk, True), rc.decrypt(c, sk)), (logn, size, L)
+                assert np.array_equal(oc.bfv_decrypt(c, sk, t), rb.decrypt(c, sk, bfv=True)), (logn, size, L)
+
+
 # ---- (c) golden digests produced by the reference ---------------------------------------------------
 def test_golden_digests(oracle):
     path = os.path.join(os.path.dirname(__file__), "golden", "evaluator_digests.json")

@@ -36,3 +36,8 @@ def test_sim_thin_evaluator_ops(simlib, oracle):
 def test_sim_fuzz_against_oracle(simlib, oracle):
     from common import fuzz_against_oracle
     fuzz_against_oracle(simlib, oracle, seed=2024, n_configs=24, max_logn=13)
+
+
+def test_sim_decryptor(simlib, oracle):
+    from common import check_decrypt
+    check_decrypt(simlib, oracle, logn=10)
