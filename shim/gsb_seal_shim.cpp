@@ -2,6 +2,7 @@
 // polynomial arithmetic through the C ABI of the B200 library.  No CPU arithmetic fallback.
 #include "gsb_seal_shim.h"
 #include "seal/util/numth.h"
+#include "seal/util/uintcore.h"
 #include "seal/valcheck.h"
 #include <cmath>
 #include <cstring>
@@ -726,6 +727,77 @@ namespace gsb_seal
         gsb_free_host(hb);
         gsb_free_host(ho);
         check(rc);
+    }
+
+    // ---- Decryptor (decryptor.cpp:21-149) ------------------------------------------------------------------
+    Decryptor::Decryptor(shared_ptr<SEALContext> context, const SecretKey &secret_key, int device) : context_(move(context))
+    {
+        // decryptor.cpp:24-37
+        if (!context_)
+            throw invalid_argument("invalid context");
+        if (!context_->parameters_set())
+            throw invalid_argument("encryption parameters are not set correctly");
+        if (!is_valid_for(secret_key, context_))
+            throw invalid_argument("secret key is not valid for encryption parameters");
+        auto &key_parms = context_->key_context_data()->parms();
+        if (key_parms.scheme() != scheme_type::CKKS && key_parms.scheme() != scheme_type::BFV)
+            throw invalid_argument("unsupported scheme");
+        bfv_ = key_parms.scheme() == scheme_type::BFV;
+        plain_modulus_ = bfv_ ? key_parms.plain_modulus().value() : 0;
+        N_ = key_parms.poly_modulus_degree();
+        const size_t K = key_parms.coeff_modulus().size();
+        size_t k = K - context_->first_context_data()->parms().coeff_modulus().size();
+        if (K == 1)
+            k = 1;
+        vector<uint64_t> moduli;
+        for (auto &m : key_parms.coeff_modulus())
+            moduli.push_back(m.value());
+        int logn = 0;
+        while ((size_t(1) << logn) < N_)
+            logn++;
+        check(gsb_ctx_create(device, logn, moduli.data(), K, k, &ctx_));
+        const int rc = gsb_secret_key_set(ctx_, secret_key.data().data()); // decryptor.cpp:46-57
+        if (rc != GSB_OK)
+        {
+            gsb_ctx_destroy(ctx_);
+            ctx_ = nullptr;
+            raise(rc);
+        }
+    }
+
+    Decryptor::~Decryptor()
+    {
+        gsb_ctx_destroy(ctx_);
+    }
+
+    void Decryptor::decrypt(const Ciphertext &encrypted, Plaintext &destination)
+    {
+        // decryptor.cpp:60-75
+        if (!is_valid_for(encrypted, context_))
+            throw invalid_argument("encrypted is not valid for encryption parameters");
+        auto &context_data = *context_->get_context_data(encrypted.parms_id());
+        const size_t L = context_data.parms().coeff_modulus().size();
+        if (bfv_)
+        {
+            if (encrypted.is_ntt_form()) // :78-81
+                throw invalid_argument("encrypted cannot be in NTT form");
+            vector<uint64_t> tmp(N_);
+            check(gsb_bfv_decrypt_host(ctx_, plain_modulus_, encrypted.data(), tmp.data(), 1, encrypted.size(), L));
+            destination.parms_id() = parms_id_zero;
+            destination.resize(N_); // :101
+            memcpy(destination.data(), tmp.data(), N_ * sizeof(uint64_t));
+            const size_t plain_coeff_count = seal::util::get_significant_uint64_count_uint(destination.data(), N_); // :107
+            destination.resize(max(plain_coeff_count, size_t(1)));                                               // :110
+            destination.parms_id() = parms_id_zero;
+            return;
+        }
+        if (!encrypted.is_ntt_form()) // :117-120
+            throw invalid_argument("encrypted must be in NTT form");
+        destination.parms_id() = parms_id_zero; // :139
+        destination.resize(L * N_);             // :142
+        check(gsb_dot_product_ct_sk_host(ctx_, encrypted.data(), destination.data(), 1, encrypted.size(), L, 1));
+        destination.parms_id() = encrypted.parms_id(); // :148-149
+        destination.scale() = encrypted.scale();
     }
 
     // ---- util::ntt_* over NTTTables (util/ntt.h:189-368) -------------------------------------------------

@@ -143,6 +143,27 @@ namespace gsb_seal
         std::map<std::uint32_t, const void *> relin_loaded_, galois_loaded_;
     };
 
+    // seal::Decryptor (decryptor.h:62-120 / decryptor.cpp:21-149, 218-265): the secret
+    // key's NTT-form limbs live on the device, decrypt() runs the dot product c_0 + c_1 s + ... there
+    // (and, for BFV, RNSTool::decrypt_scale_and_round) and fills the same seal::Plaintext the reference
+    // would.  invariant_noise_budget is not served.
+    class Decryptor
+    {
+    public:
+        Decryptor(std::shared_ptr<seal::SEALContext> context, const seal::SecretKey &secret_key, int device = 0);
+        ~Decryptor();
+        Decryptor(const Decryptor &) = delete;
+        Decryptor &operator=(const Decryptor &) = delete;
+        void decrypt(const seal::Ciphertext &encrypted, seal::Plaintext &destination);
+
+    private:
+        std::shared_ptr<seal::SEALContext> context_;
+        gsb_ctx *ctx_ = nullptr;
+        std::size_t N_ = 0;
+        bool bfv_ = false;
+        std::uint64_t plain_modulus_ = 0;
+    };
+
     namespace util
     {
         // util/ntt.h:189-368 over one limb (CoeffIter) or an RNS polynomial (RNSIter + tables array);

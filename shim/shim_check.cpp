@@ -25,6 +25,17 @@ static void same(const char *what, const Ciphertext &r, const Ciphertext &d)
     failures += !ok;
 }
 
+static void same_plain(const char *what, Decryptor &ref, gsb_seal::Decryptor &dev, const Ciphertext &ct)
+{
+    Plaintext r, d;
+    ref.decrypt(ct, r);
+    dev.decrypt(ct, d);
+    bool ok = r.coeff_count() == d.coeff_count() && r.parms_id() == d.parms_id() && r.scale() == d.scale() &&
+              memcmp(r.data(), d.data(), r.coeff_count() * sizeof(uint64_t)) == 0;
+    printf("%-34s %s\n", what, ok ? "bit-exact" : "MISMATCH");
+    failures += !ok;
+}
+
 template <class F>
 static void expect_throw(const char *what, F &&f, int kind) // 0 invalid_argument, 1 logic_error
 {
@@ -94,6 +105,19 @@ static int run(size_t N, vector<int> bits, int k_special)
     dev.rescale_to_next_inplace(d);
     same("rescale_to_next_inplace", r, d);
     Ciphertext prod = d;
+    {
+        // row f4: gsb_seal::Decryptor against seal::Decryptor on the same objects
+        gsb_seal::Decryptor ddec(context, sk);
+        Ciphertext sq = a;
+        ref.multiply_inplace(sq, b); // size 3: needs s^2
+        same_plain("Decryptor::decrypt (fresh)", dec, ddec, a);
+        same_plain("Decryptor::decrypt (size 3)", dec, ddec, sq);
+        same_plain("Decryptor::decrypt (rescaled)", dec, ddec, prod);
+        Plaintext bad_sk_plain;
+        SecretKey bad = sk;
+        bad.data().data()[0] = parms.coeff_modulus()[0].value();
+        expect_throw("Decryptor(invalid secret key)", [&] { gsb_seal::Decryptor x(context, bad); }, 0);
+    }
     ref.rotate_vector_inplace(r, 1, glk);
     dev.rotate_vector_inplace(d, 1, glk);
     same("rotate_vector_inplace(+1)", r, d);
@@ -223,9 +247,12 @@ static int run_bfv(size_t N)
     auto context = SEALContext::Create(parms, true, sec_level_type::none);
     KeyGenerator keygen(context);
     auto pk = keygen.public_key();
+    auto sk = keygen.secret_key();
     RelinKeys rlk = keygen.relin_keys_local();
     GaloisKeys glk = keygen.galois_keys_local();
     Encryptor enc(context, pk);
+    Decryptor dec(context, sk);
+    gsb_seal::Decryptor ddec(context, sk);
     BatchEncoder encoder(context);
     Evaluator ref(context);
     gsb_seal::Evaluator dev(context);
@@ -243,6 +270,17 @@ static int run_bfv(size_t N)
     ref.multiply_inplace(r, b);
     dev.multiply_inplace(d, b);
     same("BFV multiply_inplace", r, d);
+    same_plain("BFV Decryptor::decrypt (fresh)", dec, ddec, a);
+    same_plain("BFV Decryptor::decrypt (size 3)", dec, ddec, d);
+    {
+        Plaintext p;
+        ddec.decrypt(a, p);
+        vector<uint64_t> back;
+        encoder.decode(p, back);
+        const bool ok = back == va;
+        printf("%-34s %s\n", "BFV decrypt(encrypt(m)) == m", ok ? "yes" : "NO");
+        failures += !ok;
+    }
     ref.relinearize_inplace(r, rlk);
     dev.relinearize_inplace(d, rlk);
     same("BFV relinearize_inplace", r, d);
