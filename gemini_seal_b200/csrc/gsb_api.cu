@@ -288,9 +288,17 @@ void gsb_ctx_destroy(gsb_ctx *ctx)
         cudaFree(kv.second.d_limb);
         cudaFree(kv.second.d_consts);
     }
+    // secret-key material is wiped before its memory goes back to the allocator (the reference keeps
+    // SecretKey in a clear-on-destruction pool, secretkey.h:48-57); retired arrays hold at most as many
+    // powers as the current one
+    if (ctx->d_sk)
+        cudaMemset(ctx->d_sk, 0, ctx->sk_powers * ctx->K * ctx->N * sizeof(uint64_t));
     cudaFree(ctx->d_sk);
-    for (uint64_t *p : ctx->sk_retired)
-        cudaFree(p);
+    for (auto &r : ctx->sk_retired)
+    {
+        cudaMemset(r.first, 0, r.second);
+        cudaFree(r.first);
+    }
     cudaFree(ctx->default_ws.buf);
     cudaFree(ctx->host_io.buf);
     if (ctx->pipe_ready)

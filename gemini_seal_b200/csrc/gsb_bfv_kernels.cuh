@@ -138,7 +138,7 @@ namespace gsb
         const uint64_t *in;
         uint64_t *out;
         const LimbC *limb;          // [K]
-        const uint64_t *inv_qlast;  // [L-1] q_last^-1 mod q_i (rns.cpp:719-728)
+        const uint64_t *inv_qlast;  // [L-1][2] q_last^-1 mod q_i (rns.cpp:719-728) and its Shoup scaling
         uint32_t N, L;
         size_t total; // n_polys * (L-1) * N
     };
@@ -159,7 +159,7 @@ namespace gsb
             uint64_t tmp = barrett63(l, m.q, m.cr1);                                                              // :758
             tmp = sub_mod(tmp, barrett63(half, m.q, m.cr1), m.q);                                               // :760-764
             const uint64_t v = sub_mod(src[static_cast<size_t>(i) * p.N + d], tmp, m.q);                        // :766-767
-            p.out[t] = mul_mod(v, __ldg(p.inv_qlast + i), m);                                                   // :770-772
+            p.out[t] = mul_mod(v, __ldg(p.inv_qlast + 2 * i), m);                                                   // :770-772
         }
     }
 

@@ -50,7 +50,7 @@ namespace gsb
         uint64_t *d_neg_hat = nullptr;  // [L][k]  -(prod_{j'!=j} p_j') mod q_i
         uint64_t *d_inv_p = nullptr;    // [L][2]  (prod_j p_j)^-1 mod q_i (+ Shoup)
         // rescale (util/rns.cpp:719-728, 824): q_last^-1 mod q_i ; q_i - (half mod q_i)
-        uint64_t *d_inv_qlast = nullptr; // [L-1]
+        uint64_t *d_inv_qlast = nullptr; // [L-1][2] (+ Shoup)
         uint64_t *d_neg_half = nullptr;  // [L-1]
     };
 
@@ -109,7 +109,7 @@ struct gsb_ctx
     // [sk_powers][K][N] on the device; extended on demand by dyadic products, never shrunk
     uint64_t *d_sk = nullptr;
     size_t sk_powers = 0;
-    std::vector<uint64_t *> sk_retired; // superseded power arrays (kernels in flight may still read them)
+    std::vector<std::pair<uint64_t *, size_t>> sk_retired; // superseded power arrays + bytes (kernels in flight may still read them)
     std::mutex mu;      // guards the lazily built maps below
     std::mutex host_mu; // serialises the *_host entry points (they share host_io / default_ws)
     gsb_ws default_ws;  // compute scratch for callers that pass ws = NULL

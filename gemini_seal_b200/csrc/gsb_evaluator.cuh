@@ -109,6 +109,7 @@ const gsb::KsLevelConsts &gsb_ctx::consts_for(size_t L)
             uint64_t inv = 0;
             require(host::inv_mod(qL, modc(i).q, inv), GSB_E_LOGIC, "invalid rns bases");
             inv_qlast.push_back(inv);
+            inv_qlast.push_back(host::shoup(inv, modc(i).q));
             neg_half.push_back(modc(i).q - host::barrett63(half, modc(i)));
         }
     }
@@ -532,7 +533,7 @@ namespace gsb
             launch_poly_op(GSB_OP_DYADIC, a, st);
         }
         GSB_CUDA_CHECK(cudaStreamSynchronize(st)); // published to every stream from here on
-        ctx->sk_retired.push_back(ctx->d_sk);
+        ctx->sk_retired.emplace_back(ctx->d_sk, ctx->sk_powers * KN * sizeof(uint64_t));
         ctx->d_sk = d;
         ctx->sk_powers = n_pow;
         return d;
@@ -1089,7 +1090,7 @@ int gsb_secret_key_set(gsb_ctx *ctx, const uint64_t *sk_host)
         GSB_CUDA_CHECK(cudaMemcpy(d, sk_host, bytes, cudaMemcpyHostToDevice));
         std::lock_guard<std::mutex> lock(ctx->mu);
         if (ctx->d_sk)
-            ctx->sk_retired.push_back(ctx->d_sk);
+            ctx->sk_retired.emplace_back(ctx->d_sk, ctx->sk_powers * bytes);
         ctx->d_sk = d;
         ctx->sk_powers = 1;
     });

@@ -345,11 +345,14 @@ namespace gsb
     };
 
     // Stage 2 epilogue (:836-848): out = multiply_uint_mod(in + 4q - ntt_lazy, q_last^-1 mod q_i).
+    // The constant factor comes with its Shoup scaling: x*c - floor(x*c'/2^64)*q lies in [0, 2q) for any
+    // 64-bit x, so one conditional subtraction yields the same canonical residue as the reference's
+    // Barrett-128 of the full product, with 6 instead of 18 wide multiplies.
     struct RsStoreArgs
     {
         const uint64_t *in; // [n_polys][L][N]
         uint64_t *out;      // [n_polys][L-1][N]
-        const uint64_t *inv_qlast;
+        const uint64_t *inv_qlast; // [L-1][2]
         uint32_t L;
     };
     struct RsStore
@@ -357,13 +360,13 @@ namespace gsb
         typedef RsStoreArgs Args;
         const uint64_t *in;
         uint64_t *out;
-        uint64_t q, cr0, cr1, four_q, inv;
+        uint64_t q, four_q, inv, inv_s;
         GSB_DEV RsStore(const Args &a, int y, int z, int, const LimbC &c, uint32_t N)
             : in(a.in + (static_cast<size_t>(z) * a.L + y) * N), out(a.out + (static_cast<size_t>(z) * (a.L - 1) + y) * N),
-              q(c.q), cr0(c.cr0), cr1(c.cr1), four_q(c.q << 2), inv(a.inv_qlast[y])
+              q(c.q), four_q(c.q << 2), inv(a.inv_qlast[2 * y]), inv_s(a.inv_qlast[2 * y + 1])
         {}
         GSB_DEV void prefetch(uint32_t d) const { prefetch_l2(in + d); }
-        GSB_DEV uint64_t one(uint64_t u, uint64_t v) const { return mul_mod(u + four_q - v, inv, q, cr0, cr1); }
+        GSB_DEV uint64_t one(uint64_t u, uint64_t v) const { return mulmod_shoup(u + four_q - v, inv, inv_s, q); }
         GSB_DEV void store(uint32_t d, uint64_t v, int) const { out[d] = one(in[d], v); }
         GSB_DEV void store2(uint32_t d, uint64_t a, uint64_t b, int) const
         {
@@ -629,6 +632,13 @@ namespace gsb
         size_t pairs; // B*L*N/2
     };
 
+    GSB_DEV uint64_t cross_mod(uint64_t a, uint64_t b, uint64_t x, uint64_t y, const LimbC &c)
+    {
+        uint64_t lo = a * b, hi = mulhi(a, b);
+        mac128(lo, hi, x, y);
+        return barrett128(lo, hi, c.q, c.cr0, c.cr1);
+    }
+
     __global__ void __launch_bounds__(256) ckks_multiply_kernel(CkksMulArgs p)
     {
         const size_t LN = static_cast<size_t>(p.L) * p.N;
@@ -645,8 +655,11 @@ namespace gsb
             ulonglong2 c0, c1, c2;
             c0.x = mul_mod(a0.x, b0.x, c.q, c.cr0, c.cr1);
             c0.y = mul_mod(a0.y, b0.y, c.q, c.cr0, c.cr1);
-            c1.x = add_mod(mul_mod(a1.x, b0.x, c.q, c.cr0, c.cr1), mul_mod(a0.x, b1.x, c.q, c.cr0, c.cr1), c.q);
-            c1.y = add_mod(mul_mod(a1.y, b0.y, c.q, c.cr0, c.cr1), mul_mod(a0.y, b1.y, c.q, c.cr0, c.cr1), c.q);
+            // c1 = a1*b0 + a0*b1 (:503-512): the reference reduces both products and adds mod q; the
+            // canonical residue of the exact 128-bit sum (< 2^123 for 61-bit moduli) is the same word,
+            // with one Barrett-128 instead of two
+            c1.x = cross_mod(a1.x, b0.x, a0.x, b1.x, c);
+            c1.y = cross_mod(a1.y, b0.y, a0.y, b1.y, c);
             c2.x = mul_mod(a1.x, b1.x, c.q, c.cr0, c.cr1);
             c2.y = mul_mod(a1.y, b1.y, c.q, c.cr0, c.cr1);
             *reinterpret_cast<ulonglong2 *>(po) = c0;
