@@ -234,6 +234,7 @@ int gsb_ctx_create(int device, int logn, const uint64_t *moduli, size_t K, size_
             c.inv_n = t.inv_n;
             c.inv_n_s = t.inv_n_s;
             c.pad = 0;
+            limb_mu(c.q, c.mu, c.sh);
             limb[i] = c;
         }
         {

@@ -166,6 +166,7 @@ const gsb::BfvTool &gsb_ctx::bfv_tool(size_t L, uint64_t plain_modulus)
         c.inv_n = t.inv_n;
         c.inv_n_s = t.inv_n_s;
         c.pad = 0;
+        limb_mu(c.q, c.mu, c.sh);
         limb[i] = c;
     }
     BfvTool tool;
@@ -197,6 +198,7 @@ const gsb::BfvTool &gsb_ctx::bfv_tool(size_t L, uint64_t plain_modulus)
             c.two_q = mc.q << 1;
             c.cr0 = mc.cr0;
             c.cr1 = mc.cr1;
+            limb_mu(c.q, c.mu, c.sh);
             return c;
         };
         tool.dec = DecryptRoundArgs{ nullptr, nullptr, tool.d_limb, tool.d_consts + o9, tool.d_consts + o1, tool.d_consts + o10,
@@ -464,7 +466,7 @@ namespace gsb
     static void ckks_multiply_core(gsb_ctx *ctx, const uint64_t *a, const uint64_t *b, uint64_t *out, size_t B, size_t L, cudaStream_t st)
     {
         CkksMulArgs p{ a, b, out, ctx->d_limb, static_cast<uint32_t>(ctx->N), static_cast<uint32_t>(L), B * L * ctx->N / 2 };
-        GSB_LAUNCH("ckks_multiply", "", ckks_multiply_kernel, dim3(grid_for(p.pairs, 256)), dim3(256), 0, st, p);
+        GSB_LAUNCH("ckks_multiply", "", ckks_multiply_kernel<true>, dim3(grid_for(p.pairs, 256)), dim3(256), 0, st, p);
     }
 
     static void gather_core(
@@ -807,7 +809,7 @@ int gsb_bfv_multiply_dev(
             GSB_DISPATCH_LOGN(ctx->logn, ntt_forward_plain<LOGN>(tab, mm, ext, MN, ext, MN, static_cast<int>(M), static_cast<int>(4 * B), true, st, "bfv"));
             // (4): the size-2 x size-2 tensor product over all M limbs (same dyadic + add arithmetic as CKKS)
             CkksMulArgs p{ ext, ext + 2 * B * MN, dest, tool.d_limb, static_cast<uint32_t>(N), static_cast<uint32_t>(M), B * MN / 2 };
-            GSB_LAUNCH("bfv_tensor", "", ckks_multiply_kernel, dim3(grid_for(p.pairs, 256)), dim3(256), 0, st, p);
+            GSB_LAUNCH("bfv_tensor", "", ckks_multiply_kernel<false>, dim3(grid_for(p.pairs, 256)), dim3(256), 0, st, p);
             // (5): strict inverse NTT
             GSB_DISPATCH_LOGN(ctx->logn, ntt_inverse_plain<LOGN>(tab, mm, dest, MN, dest, MN, static_cast<int>(M), static_cast<int>(3 * B), false, st, "bfv"));
             // (6)-(8): times t, divide by q and floor into Bsk, Shenoy-Kumaresan back to q

@@ -632,13 +632,26 @@ namespace gsb
         size_t pairs; // B*L*N/2
     };
 
+    // FASTRED: operands are canonical residues and the limb has c.mu (every modulus of <= 60 bits): the
+    // products are reduced with reduce_2k; otherwise (BFV tensor product over lazy NTT words, 61-bit
+    // moduli) with the literal barrett_reduce_128.  Same canonical words either way.
+    template <bool FASTRED>
+    GSB_DEV uint64_t prod_mod(uint64_t a, uint64_t b, const LimbC &c)
+    {
+        const uint64_t lo = a * b, hi = mulhi(a, b);
+        return (FASTRED && c.mu) ? reduce_2k(lo, hi, c) : barrett128(lo, hi, c.q, c.cr0, c.cr1);
+    }
+    // a*b + x*y mod q: the reference reduces both products and adds mod q (evaluator.cpp:503-512); the
+    // canonical residue of the exact 128-bit sum (< 2^123 for 61-bit moduli) is the same word
+    template <bool FASTRED>
     GSB_DEV uint64_t cross_mod(uint64_t a, uint64_t b, uint64_t x, uint64_t y, const LimbC &c)
     {
         uint64_t lo = a * b, hi = mulhi(a, b);
         mac128(lo, hi, x, y);
-        return barrett128(lo, hi, c.q, c.cr0, c.cr1);
+        return (FASTRED && c.mu) ? reduce_2k(lo, hi, c) : barrett128(lo, hi, c.q, c.cr0, c.cr1);
     }
 
+    template <bool FASTRED>
     __global__ void __launch_bounds__(256) ckks_multiply_kernel(CkksMulArgs p)
     {
         const size_t LN = static_cast<size_t>(p.L) * p.N;
@@ -653,15 +666,12 @@ namespace gsb
             const ulonglong2 a0 = *reinterpret_cast<const ulonglong2 *>(pa), a1 = *reinterpret_cast<const ulonglong2 *>(pa + LN);
             const ulonglong2 b0 = *reinterpret_cast<const ulonglong2 *>(pb), b1 = *reinterpret_cast<const ulonglong2 *>(pb + LN);
             ulonglong2 c0, c1, c2;
-            c0.x = mul_mod(a0.x, b0.x, c.q, c.cr0, c.cr1);
-            c0.y = mul_mod(a0.y, b0.y, c.q, c.cr0, c.cr1);
-            // c1 = a1*b0 + a0*b1 (:503-512): the reference reduces both products and adds mod q; the
-            // canonical residue of the exact 128-bit sum (< 2^123 for 61-bit moduli) is the same word,
-            // with one Barrett-128 instead of two
-            c1.x = cross_mod(a1.x, b0.x, a0.x, b1.x, c);
-            c1.y = cross_mod(a1.y, b0.y, a0.y, b1.y, c);
-            c2.x = mul_mod(a1.x, b1.x, c.q, c.cr0, c.cr1);
-            c2.y = mul_mod(a1.y, b1.y, c.q, c.cr0, c.cr1);
+            c0.x = prod_mod<FASTRED>(a0.x, b0.x, c);
+            c0.y = prod_mod<FASTRED>(a0.y, b0.y, c);
+            c1.x = cross_mod<FASTRED>(a1.x, b0.x, a0.x, b1.x, c);
+            c1.y = cross_mod<FASTRED>(a1.y, b0.y, a0.y, b1.y, c);
+            c2.x = prod_mod<FASTRED>(a1.x, b1.x, c);
+            c2.y = prod_mod<FASTRED>(a1.y, b1.y, c);
             *reinterpret_cast<ulonglong2 *>(po) = c0;
             *reinterpret_cast<ulonglong2 *>(po + LN) = c1;
             *reinterpret_cast<ulonglong2 *>(po + 2 * LN) = c2;

@@ -16,8 +16,22 @@ namespace gsb
         uint64_t cr1;     // const_ratio[1]
         uint64_t inv_n;   // n^-1 mod q     (util/ntt.cpp:69-73)
         uint64_t inv_n_s; // floor(inv_n * 2^64 / q)
-        uint64_t pad;
+        uint64_t pad;     // run-time zero (see fwd_round)
+        // reduce_2k: k = bit length of q; mu = floor(2^(k+63) / q) (< 2^64), sh = k - 1; mu = 0 when k > 60
+        uint64_t mu, sh;
     };
+
+    // (mu, sh) of LimbC for modulus q (host side of reduce_2k)
+    inline void limb_mu(uint64_t q, uint64_t &mu, uint64_t &sh)
+    {
+        int k = 0;
+        for (uint64_t x = q; x; x >>= 1)
+            k++;
+        mu = 0;
+        sh = static_cast<uint64_t>(k - 1);
+        if (k >= 2 && k <= 60)
+            mu = static_cast<uint64_t>((static_cast<unsigned __int128>(1) << (k + 63)) / q);
+    }
 
     GSB_DEV uint64_t mulhi(uint64_t a, uint64_t b)
     {
@@ -176,6 +190,22 @@ namespace gsb
     {
         uint64_t r = mad_lo64_1(mulhi(x, cr1), 0 - q, x);
         return r - (r >= q ? q : 0);
+    }
+
+    // Canonical residue of z = (z1:z0) < 2^(2k+1), k = bit length of q <= 60 (c.mu != 0): generalized
+    // Barrett with one 64x64 high product.  zt = floor(z / 2^(k-1)) < 2^(k+2); h = floor(zt mu / 2^64)
+    // satisfies floor(z/q) - 2 <= h <= floor(z/q)  (zt > z/2^(k-1) - 1, mu > 2^(k+63)/q - 1 and
+    // z / 2^(k+63) <= 1/4), so z - h q is in [0, 3q): two conditional subtractions.  The result is the
+    // same word as barrett_reduce_128's (both are THE residue in [0, q)), with 5 instead of 14 wide
+    // multiplies.  Only for products of canonical operands (a b < q^2, a b + c d < 2 q^2).
+    GSB_DEV uint64_t reduce_2k(uint64_t z0, uint64_t z1, const LimbC &c)
+    {
+        const uint32_t sh = static_cast<uint32_t>(c.sh);
+        const uint64_t zt = (z0 >> sh) | (z1 << (64u - sh));
+        uint64_t r = mad_lo64_1(mulhi(zt, c.mu), 0 - c.q, z0);
+        GSB_SIM_ASSERT(sh >= 1 && (z1 >> sh) == 0 && r < c.q + c.two_q);
+        r -= (r >= c.two_q) ? c.two_q : 0;
+        return r - (r >= c.q ? c.q : 0);
     }
 
     // multiply_uint_mod (util/uintarithsmallmod.h:209-221); also the body of dyadic_product_coeffmod /

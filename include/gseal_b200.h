@@ -133,7 +133,10 @@ int gsb_galois_table(const gsb_ctx *ctx, uint32_t galois_elt, uint32_t *table_ou
 
 /* ---- Evaluator hot path, batched: every pointer is a batch of `batch` ciphertexts stored back to
  * back; L = number of limbs of the ciphertexts' level (2 <= L <= K-k for rescale, 1 <= L otherwise).
- * All ciphertexts are CKKS, NTT form.  ws = NULL uses the context's default workspace. ----------- */
+ * All ciphertexts are CKKS, NTT form.  ws = NULL uses the context's default workspace.
+ * Every input word must be a canonical residue (< q_i), i.e. the buffers must pass the reference's
+ * is_buffer_valid (valcheck.cpp), which the C++ shim checks as seal::Evaluator does; the *_dev entry
+ * points do not re-scan device buffers, and their internal no-wrap bounds assume it. -------------- */
 
 /* Evaluator::multiply_inplace -> ckks_multiply (evaluator.cpp:235-272,447-527) for two size-2
  * operands: a, b = [batch][2][L][N] -> out = [batch][3][L][N]. */
