@@ -380,7 +380,8 @@ namespace gsb
             IoPair<PlainLoad, MdStore> io2{ PlainArgs{ tmp, L * N }, sa };
             if (ctx->fast_ntt)
             {
-                launch_fwd_cols<LOGN, true>(io1, tab, mm, iL, static_cast<int>(2 * B), st, "moddown");
+                IoPair<MdLoadT<K1, true>, PlainStore<OUT_RAW>> io1f{ la, PlainStoreArgs{ tmp, L * N } };
+                launch_fwd_cols<LOGN, true>(io1f, tab, mm, iL, static_cast<int>(2 * B), st, "moddown");
                 launch_fwd_contig<LOGN, true>(io2, tab, mm, iL, static_cast<int>(2 * B), st, "moddown");
             }
             else
@@ -393,7 +394,7 @@ namespace gsb
         {
             IoPair<MdLoadT<K1>, MdStore> io{ la, sa };
             if (ctx->fast_ntt)
-                launch_fwd_contig<LOGN, true>(io, tab, mm, iL, static_cast<int>(2 * B), st, "moddown");
+                launch_fwd_contig<LOGN, true>(IoPair<MdLoadT<K1, true>, MdStore>{ la, sa }, tab, mm, iL, static_cast<int>(2 * B), st, "moddown");
             else
                 launch_fwd_contig<LOGN>(io, tab, mm, iL, static_cast<int>(2 * B), st, "moddown");
         }
@@ -444,7 +445,8 @@ namespace gsb
             IoPair<PlainLoad, RsStore> io2{ PlainArgs{ out, (L - 1) * N }, sa };
             if (ctx->fast_ntt)
             {
-                launch_fwd_cols<LOGN, true>(io1, tab, mm, ny, nz, st, "rescale");
+                IoPair<RsLoadT<true>, PlainStore<OUT_RAW>> io1f{ la, PlainStoreArgs{ out, (L - 1) * N } };
+                launch_fwd_cols<LOGN, true>(io1f, tab, mm, ny, nz, st, "rescale");
                 launch_fwd_contig<LOGN, true>(io2, tab, mm, ny, nz, st, "rescale");
             }
             else
@@ -457,7 +459,7 @@ namespace gsb
         {
             IoPair<RsLoad, RsStore> io{ la, sa };
             if (ctx->fast_ntt)
-                launch_fwd_contig<LOGN, true>(io, tab, mm, ny, nz, st, "rescale");
+                launch_fwd_contig<LOGN, true>(IoPair<RsLoadT<true>, RsStore>{ la, sa }, tab, mm, ny, nz, st, "rescale");
             else
                 launch_fwd_contig<LOGN>(io, tab, mm, ny, nz, st, "rescale");
         }

@@ -163,7 +163,11 @@ namespace gsb
         const uint64_t *red;
         GSB_DEV bool skip(int, int) const { return false; }
     };
-    template <bool K1>
+    // FAST (k = 1 contexts under gsb_ctx::fast_ntt): the wide-range transform that follows accepts any
+    // word < 2 q_max, so -[c]_p, an integer in [0, p), enters the NTT mod q_i as it is; and the special
+    // slot's lazy inverse NTT word is < 2p, so its barrett_reduce_63 is one conditional subtraction.
+    // Both are congruent to the reference's words and cost no multiply.
+    template <bool K1, bool FAST = false>
     struct MdLoadT
     {
         typedef MdLoadArgs Args;
@@ -208,6 +212,11 @@ namespace gsb
         {
             if (!K1 && k != 1)
                 return v;
+            if (K1 && FAST)
+            {
+                GSB_SIM_ASSERT(v < 2 * p0);
+                return neg_mod(v - (v >= p0 ? p0 : 0), p0);
+            }
             // :268-275: negate(barrett_reduce_63(c_p)) then barrett_reduce_128 of (v, 0)
             const uint64_t t = neg_mod(barrett63(v, p0, p0cr1), p0);
             return barrett128(t, 0, q, cr0, cr1);
@@ -325,14 +334,17 @@ namespace gsb
         uint64_t q_last;
         GSB_DEV bool skip(int, int) const { return false; }
     };
-    struct RsLoad
+    // FAST: t < q_last and the wide-range transform accepts any word < 2 q_max, so the reduction
+    // modulo q_i is skipped (congruent word).
+    template <bool FAST>
+    struct RsLoadT
     {
         typedef RsLoadArgs Args;
         const uint64_t *t;
         uint64_t q, cr1, nh;
         bool reduce;
-        GSB_DEV RsLoad(const Args &a, int y, int z, int, const LimbC &c, uint32_t N)
-            : t(a.t + static_cast<size_t>(z) * N), q(c.q), cr1(c.cr1), nh(a.neg_half[y]), reduce(c.q < a.q_last)
+        GSB_DEV RsLoadT(const Args &a, int y, int z, int, const LimbC &c, uint32_t N)
+            : t(a.t + static_cast<size_t>(z) * N), q(c.q), cr1(c.cr1), nh(a.neg_half[y]), reduce(!FAST && c.q < a.q_last)
         {}
         GSB_DEV uint64_t xform(uint64_t v) const { return (reduce ? barrett63(v, q, cr1) : v) + nh; }
         GSB_DEV uint64_t raw(uint32_t d) const { return t[d]; }
@@ -343,6 +355,8 @@ namespace gsb
             y = v.y;
         }
     };
+
+    typedef RsLoadT<false> RsLoad;
 
     // Stage 2 epilogue (:836-848): out = multiply_uint_mod(in + 4q - ntt_lazy, q_last^-1 mod q_i).
     // The constant factor comes with its Shoup scaling: x*c - floor(x*c'/2^64)*q lies in [0, 2q) for any
