@@ -504,6 +504,14 @@ namespace gsb
         for (int r = 0; r < 8; r++)
             lo[0][r] = hi[0][r] = lo[1][r] = hi[1][r] = 0;
         mbar_wait(bar, 0);
+        if constexpr (LAZY)
+        {
+            // every stage of this kernel's transform is a wide-range stage: shift the staged Shoup halves
+            // once per CTA instead of once per use (15 bundles x 36 butterflies per thread)
+            for (uint32_t i = tid; i < TP::PAIRS; i += (1u << T))
+                tws[i].y >>= 1;
+            __syncthreads();
+        }
         int parity = 0;
         for (int j = 0; j < nb; j++)
         {
@@ -557,7 +565,12 @@ namespace gsb
                     x[r] = pro.xform(x[r]);
             }
             if (!direct)
-                fwd_compute<T, MP::G_HI, 0, !LAZY, 0, LAZY>(x, smem, tid, tw, c, parity);
+            {
+                if constexpr (LAZY)
+                    fwd_compute<T, MP::G_HI, 0, false, 0, true>(x, smem, tid, TwPreshifted<typename TP::TwC>{ tw }, c, parity);
+                else
+                    fwd_compute<T, MP::G_HI, 0, true, 0, false>(x, smem, tid, tw, c, parity);
+            }
             // key tiles are stored with their 16-byte units swizzled (key_word_pos): the thread's
             // words 2r, 2r+1 are unit swz8(4 tid + r) of the tile -- conflict-free for a warp
             const ulonglong2 *k0, *k1;

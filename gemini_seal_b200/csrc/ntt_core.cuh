@@ -239,6 +239,23 @@ namespace gsb
         }
     };
 
+    // A twiddle source whose Shoup halves were already shifted right by one in shared memory (what
+    // mulmod_wide_add wants): saves the two funnel shifts per twiddle in kernels that reuse a staged
+    // table many times.  Only valid when every stage of the transform is a wide-range stage.
+    template <class TW>
+    struct TwPreshifted
+    {
+        TW tw;
+        static constexpr bool kPreshifted = true;
+        GSB_DEV Twiddle fwd(int g, uint32_t local, int grp) const { return tw.fwd(g, local, grp); }
+    };
+    template <class T, class = void>
+    struct tw_preshifted : std::false_type
+    {};
+    template <class T>
+    struct tw_preshifted<T, std::void_t<decltype(T::kPreshifted)>> : std::true_type
+    {};
+
     // ---- forward round: ForwardLazy / ForwardLazyLast (util/ntt.cpp:245-261) -------------------
     // LAST: this transform's gap-2^0 stage is the global last stage (h = 1), where x0 is first
     // reduced with reduceBarrettLazy.
@@ -269,7 +286,7 @@ namespace gsb
                 {
                     const Twiddle w = tw.fwd(g, base, grp);
                     const bool wide = FAST && !(LAST && g == 0);
-                    const uint64_t wsh = w.y >> 1;
+                    const uint64_t wsh = tw_preshifted<TW>::value ? w.y : (w.y >> 1);
 #pragma unroll
                     for (int i = 0; i < half; i++)
                     {
