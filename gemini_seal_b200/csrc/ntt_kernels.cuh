@@ -141,6 +141,16 @@ namespace gsb
                 xf_load_raw<T_LOG, G_HI, G_LO, INVERSE>(xn, tid, tile, map, pro);
             }
             mbar_wait(bar, 0); // twiddles have landed (every thread waits, also before an early exit)
+            if constexpr (FAST && !INVERSE)
+            {
+                // wide-range stages want w' >> 1 (mulmod_wide_add): shift the staged Shoup halves once per
+                // CTA.  The literal last stage of a contiguous transform (LAST: gap 2^0, segment 0 = the
+                // first TILE/2 pairs) keeps its exact w'.
+                constexpr uint32_t first = (LAST && !TP::COLS && G_LO == 0) ? (1u << (TP::TILE_LOG - 1)) : 0u;
+                for (uint32_t i = first + tid; i < TP::PAIRS; i += (1u << T_LOG))
+                    tws[i].y >>= 1;
+                __syncthreads();
+            }
             int parity = 0;
             while (z < z1)
             {
@@ -166,8 +176,10 @@ namespace gsb
                     xf_prefetch<T_LOG, G_HI, G_LO, INVERSE>(tid, tile, map, epi);
                 if constexpr (INVERSE)
                     inv_compute<T_LOG, G_HI, G_LO, LAST, 0>(x, smem, tid, tw, c, parity);
+                else if constexpr (FAST)
+                    fwd_compute<T_LOG, G_HI, G_LO, LAST, 0, true>(x, smem, tid, TwPreshifted<std::decay_t<decltype(tw)>>{ tw }, c, parity);
                 else
-                    fwd_compute<T_LOG, G_HI, G_LO, LAST, 0, FAST>(x, smem, tid, tw, c, parity);
+                    fwd_compute<T_LOG, G_HI, G_LO, LAST, 0, false>(x, smem, tid, tw, c, parity);
                 xf_store<T_LOG, G_HI, G_LO, INVERSE>(x, tid, tile, map, epi);
 #if !GSB_PREFETCH
                 if (zn < z1)
