@@ -2,6 +2,7 @@
 // points.  Key switching / multiply / rescale / Galois live in gsb_evaluator.cuh, included below.
 #include "gsb_context.cuh"
 #include "elementwise.cuh"
+#include <cstdlib>
 #include <cstdio>
 #include <cstring>
 #include <memory>
@@ -248,6 +249,16 @@ int gsb_ctx_create(int device, int logn, const uint64_t *moduli, size_t K, size_
             ctx->fast_ntt = static_cast<u128>(qmax) * growth < (static_cast<u128>(1) << 63);
             ctx->lazy_modup = ctx->fast_ntt;
             ctx->lazy_mac = ctx->fast_ntt && static_cast<u128>(qmax) * qmax <= ~static_cast<u128>(0) / (beta0 * growth);
+            // GSB_LITERAL=1 (read at context creation; a testing aid): every congruent-word shortcut off, the
+            // kernels carry the reference's own intermediate words.  tests/test_gpu_parity.py runs the full
+            // size both ways and requires identical outputs.
+            const char *lit = std::getenv("GSB_LITERAL");
+            if (lit && lit[0] == '1')
+            {
+                ctx->fast_ntt = ctx->lazy_modup = ctx->lazy_mac = false;
+                for (auto &c : limb)
+                    c.mu = 0;
+            }
         }
         ctx->d_WW = upload(ww);
         ctx->d_VV = upload(vv);

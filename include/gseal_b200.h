@@ -229,6 +229,8 @@ int gsb_int_peak_wide(gsb_ctx *ctx, int ctas_per_sm, double *wide_butterflies_pe
 /* 1 when the context's moduli satisfy q_max (5 log2 N + 2) < 2^63, i.e. the key-switch / rescale
  * internals run the wide-range butterflies (identical outputs); else 0. */
 int gsb_ctx_fast_ntt(const gsb_ctx *ctx);
+/* Testing aid: a context created while the environment variable GSB_LITERAL is "1" takes none of those
+ * shortcuts (gsb_ctx_fast_ntt returns 0); outputs are identical either way. */
 
 #ifdef __cplusplus
 }

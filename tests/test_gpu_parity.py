@@ -115,6 +115,36 @@ def test_full_size_properties(cudalib):
     ctx.close()
 
 
+def test_full_size_shortcuts_equal_literal(cudalib):
+    """N = 2^15, K = 16: the context with every congruent-word shortcut (wide-range butterflies, skipped
+    range reductions, single-high-product Barrett, ...) and a GSB_LITERAL=1 context that carries the
+    reference's own intermediate words must produce identical output words."""
+    import gemini_seal_b200 as g
+    mods = golden_cases.BFV_DEFAULT[32768]
+    N, L, B = 32768, 15, 3
+    rng = np.random.default_rng(23)
+    relin, gal = rand_key(rng, mods, 15, N), rand_key(rng, mods, 15, N)
+    a, b = rand_poly(rng, mods[:L], (B, 2), N), rand_poly(rng, mods[:L], (B, 2), N)
+    outs = []
+    for literal in (False, True):
+        if literal:
+            os.environ["GSB_LITERAL"] = "1"
+        try:
+            ctx = g.Context(N, mods, 1, lib=cudalib)
+        finally:
+            os.environ.pop("GSB_LITERAL", None)
+        assert cudalib.gsb_ctx_fast_ntt(ctx.handle) == (0 if literal else 1)
+        ctx.set_relin_keys(relin)
+        elt = ctx.galois_elt_from_step(1)
+        ctx.set_galois_key(elt, gal)
+        ev = g.Evaluator(ctx)
+        c3 = ev.multiply(a, b)
+        outs.append((c3, ev.relinearize(c3), ev.mul_relin_rescale(a, b), ev.apply_galois(a, elt)))
+        ctx.close()
+    for x, y in zip(*outs):
+        assert np.array_equal(x, y)
+
+
 @pytest.mark.parametrize("B", [3, 8])
 def test_full_size_repeatability(cudalib, B):
     """Race detector for the staged (bulk-copy) key-switch kernel: the same N = 2^15 key switch run 60

@@ -41,3 +41,33 @@ def test_sim_fuzz_against_oracle(simlib, oracle):
 def test_sim_decryptor(simlib, oracle):
     from common import check_decrypt
     check_decrypt(simlib, oracle, logn=10)
+
+
+def test_sim_fast_flag_and_literal_mode(simlib, oracle):
+    """gsb_ctx_fast_ntt follows q_max (5 log2 N + 2) < 2^63, and GSB_LITERAL=1 turns the shortcuts off
+    without changing any output word (small case; the GPU suite repeats it at N = 2^15)."""
+    import numpy as np
+    import gemini_seal_b200 as g
+    from common import mixed_moduli, rand_key, rand_poly
+    logn, N = 11, 2048
+    for bits, want in (([56, 55, 56, 56], 1), ([57, 55, 56, 56], 1), ([58, 55, 56, 56], 0), ([59, 58, 59, 59], 0)):
+        ctx = g.Context(N, mixed_moduli(logn, bits), 1, lib=simlib)
+        assert simlib.gsb_ctx_fast_ntt(ctx.handle) == want, bits
+        ctx.close()
+    mods = mixed_moduli(logn, [50, 40, 45, 51])
+    rng = np.random.default_rng(3)
+    relin = rand_key(rng, mods, 3, N)
+    a, b = rand_poly(rng, mods[:3], (2, 2), N), rand_poly(rng, mods[:3], (2, 2), N)
+    outs = []
+    for literal in (False, True):
+        if literal:
+            os.environ["GSB_LITERAL"] = "1"
+        try:
+            ctx = g.Context(N, mods, 1, lib=simlib)
+        finally:
+            os.environ.pop("GSB_LITERAL", None)
+        assert simlib.gsb_ctx_fast_ntt(ctx.handle) == (0 if literal else 1)
+        ctx.set_relin_keys(relin)
+        outs.append(g.Evaluator(ctx).mul_relin_rescale(a, b))
+        ctx.close()
+    assert np.array_equal(outs[0], outs[1])
