@@ -478,10 +478,13 @@ namespace gsb
         GSB_LAUNCH("galois_gather", "", galois_gather_kernel, dim3(grid_for(p.total, 256)), dim3(256), 0, st, p);
     }
 
-    // How many ciphertexts to push through one pass of the pipeline: bounded scratch (<= ~6 GiB).
+#ifndef GSB_SCRATCH_GIB
+#define GSB_SCRATCH_GIB 16
+#endif
+    // How many ciphertexts to push through one pass of the pipeline: bounded scratch (<= GSB_SCRATCH_GIB, 16 GiB: 64 ciphertexts per pass at N = 2^15, K = 16).
     static size_t chunk_for(size_t words_per_ct, size_t B)
     {
-        const size_t budget = (size_t(6) << 30) / sizeof(uint64_t);
+        const size_t budget = (size_t(GSB_SCRATCH_GIB) << 30) / sizeof(uint64_t);
         size_t c = budget / (words_per_ct + 64);
         c = c < 1 ? 1 : c;
         if (c >= B)

@@ -58,8 +58,8 @@ for row in rows[2:]:
         "issue_active_pct": float(row[hdr.index("smsp__issue_active.avg.pct_of_peak_sustained_active")]),
         "registers": int(float(row[hdr.index("launch__registers_per_thread")])),
     }
-doc = {"source": os.path.basename(rep), "command": "ncu --set full --clock-control none -s 78 -c 13 "
-       "python bench.py --no-cpu-baseline --steps 1 --warmup 3  (13 launches = one 32-ciphertext chunk of the step)", "kernels": out}
+doc = {"source": os.path.basename(rep), "command": "ncu --set full --clock-control none -s 105 -c 13 "
+       "python bench.py --no-cpu-baseline --steps 1 --warmup 3  (launches 105..117 = the 13 kernels of the 64-ciphertext timed step)", "kernels": out}
 path = os.path.join(ROOT, "profiles", "r1_ncu_traffic.json")
 with open(path, "w") as f:
     json.dump(doc, f, indent=1)
