@@ -1,6 +1,8 @@
 // 64-bit modular arithmetic on the 32-bit integer pipes, mirroring the reference word for word so
 // every intermediate u64 equals the CPU's.  Reference paths are relative to
-// /root/reference/native/src/seal/.
+// /root/reference/native/src/seal/.  Three helpers are NOT literal mirrors: mulmod_wide_add (congruent
+// word in a wider range), mac128_mid and reduce_2k (same results as FMAU128 / barrett_reduce_128 under
+// stated operand bounds); each says where it may be used.
 #pragma once
 #include "compat.cuh"
 

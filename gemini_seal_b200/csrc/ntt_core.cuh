@@ -3,6 +3,10 @@
 // (SlothfulNTT, util/ntt.cpp:213-282) while regrouping its radix-2 stages into rounds of up to
 // three stages held in registers.  Regrouping does not change any butterfly's inputs, so every
 // intermediate word -- lazy ranges and mod-2^64 wraps included -- equals the CPU's.
+// That literal form serves the public util::ntt_* entry points, every inverse transform and every
+// context whose moduli fail gsb_ctx::fast_ntt.  Forward transforms that stay inside the library and
+// end in a canonical reduction may instead run the wide-range butterfly (`FAST`, see fwd_round):
+// congruent words, one wide multiply less, identical outputs.
 //
 // Geometry.  A CTA of T = 2^T_LOG threads owns a tile of 8T words; each thread keeps 8 words in
 // registers per round.  A "round" (TOP, R) runs the R stages whose butterfly gaps, measured in
