@@ -116,9 +116,11 @@ namespace gsb
     //     h   = x1*ysh1 + (t >> 32)            in { H, H-1 },  H = floor(x*ysh / 2^64)
     // With Q = x*y/(2q):  Q - 1.5 < H <= Q  (x < 2^63), so Q - 2.5 < h <= Q and the product term
     // x*y - 2q*h lies in [0, 5q): congruent to the reference's mulmodLazy word, in a wider range.
-    // 5 IMAD.WIDE + 4 IMAD and nothing else (the exact form is 6 IMAD.WIDE + 4 IMAD + 4 carry adds).
-    // `zero` is a run-time zero (LimbC::pad): as the high word of the third product's addend it keeps
-    // ptxas from splitting that multiply-add into a multiply plus a carry pair on the FMA-heavy pipe.
+    // 5 wide multiplies + 4 IMAD (the exact form is 6 + 4 and four more carry adds).  In SASS (sm_100a,
+    // CUDA 12.9) ptxas issues the wide products without addends (IMAD.WIDE / IMAD.HI) and joins them with
+    // three-input IADD3 pairs on the ALU pipe.  `zero` is a run-time zero (LimbC::pad) used as the high
+    // word of the third product's addend: with a literal 0 there the carry word became an IMAD.X on the
+    // multiplier pipe, with a register operand it stays an IADD3.X.
     GSB_DEV uint64_t mulmod_wide_add(uint64_t x, uint64_t y, uint64_t ysh, uint64_t neg_two_q, uint64_t add, uint64_t zero)
     {
 #ifdef GSB_CUSIM
