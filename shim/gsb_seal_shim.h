@@ -121,6 +121,8 @@ namespace gsb_seal
             const seal::RelinKeys &relin_keys);
 
         gsb_ctx *device_context() const { return ctx_; }
+        // what the C layer's Evaluator_ContextUsingKeyswitching reports (c/evaluator.cpp:23-29)
+        bool using_keyswitching() const { return context_->using_keyswitching(); }
 
     private:
         void validate(const seal::Ciphertext &ct, const char *what) const;

@@ -46,3 +46,31 @@ def test_shim_against_simulator(simlib):
     p = subprocess.run([BIN], capture_output=True, text=True, timeout=900, env=env)
     assert p.returncode == 0, p.stdout[-3000:] + p.stderr[-1000:]
     assert "SHIM_CHECK PASS" in p.stdout and "MISMATCH" not in p.stdout
+
+
+CBIN = os.path.join(ROOT, "oracle", "_ref", "c_layer_check")
+
+
+@pytest.mark.gpu
+def test_c_export_layer_on_device():
+    """the reference's C export entry points (Evaluator_*, Decryptor_*; what the .NET
+    wrapper P/Invokes) served by shim/gsb_seal_c.cpp, compared with seal::Evaluator / seal::Decryptor."""
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    if not os.path.exists(CBIN):
+        pytest.skip("oracle/_ref/c_layer_check not built (needs /root/reference at build time)")
+    p = subprocess.run([CBIN], capture_output=True, text=True, timeout=600)
+    print(p.stdout[-4000:])
+    assert p.returncode == 0, p.stdout[-3000:] + p.stderr[-1000:]
+    assert "C_LAYER_CHECK PASS" in p.stdout and "FAIL " not in p.stdout
+
+
+def test_c_export_layer_against_simulator(simlib):
+    """CPU-side twin of the test above (simulator build preloaded, see test_shim_against_simulator)."""
+    if not os.path.exists(CBIN):
+        pytest.skip("oracle/_ref/c_layer_check not built (needs /root/reference at build time)")
+    env = dict(os.environ, LD_PRELOAD=simlib._name)
+    p = subprocess.run([CBIN], capture_output=True, text=True, timeout=900, env=env)
+    assert p.returncode == 0, p.stdout[-3000:] + p.stderr[-1000:]
+    assert "C_LAYER_CHECK PASS" in p.stdout
