@@ -3,7 +3,7 @@
 (BASELINE.json configs #4/#5: 881-bit default modulus, L = 15, K = 16, k = 1), ciphertexts sharded
 across GPUs, plus limb-NTT/s and rotations/s as secondary numbers.
 
-    python bench.py --gpus 1 --steps 5 --warmup 3              # our arm
+    python bench.py --gpus 1 --steps 20 --warmup 3             # our arm
     python bench.py --impl reference --steps 2 --warmup 1      # the reference's CPU path on host cores
     python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N ...
 
@@ -53,7 +53,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(
-                ["nvidia-smi", "--query-gpu=" + self.FIELDS, "--format=csv,noheader,nounits", "-lms", "100"],
+                ["nvidia-smi", "--query-gpu=" + self.FIELDS, "--format=csv,noheader,nounits", "-lms", "20"],
                 stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._read, daemon=True)
             self.thread.start()
@@ -489,7 +489,7 @@ def run_ours(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=64, help="ciphertext pairs per GPU per step")
