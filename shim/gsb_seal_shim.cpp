@@ -729,6 +729,225 @@ namespace gsb_seal
         check(rc);
     }
 
+    // ---- device-resident handles (CKKS) --------------------------------------------------
+    // Same checks, same metadata updates and the same device entry points as the host-object overloads
+    // above; the limbs never leave HBM between upload() and download().  Everything runs on the default
+    // stream; download() synchronises.
+    DeviceCiphertext::~DeviceCiphertext()
+    {
+        release();
+    }
+    DeviceCiphertext::DeviceCiphertext(DeviceCiphertext &&o) noexcept
+    {
+        *this = move(o);
+    }
+    DeviceCiphertext &DeviceCiphertext::operator=(DeviceCiphertext &&o) noexcept
+    {
+        if (this != &o)
+        {
+            release();
+            ctx_ = o.ctx_, d_ = o.d_, cap_ = o.cap_, size_ = o.size_, L_ = o.L_;
+            parms_id_ = o.parms_id_, scale_ = o.scale_, ntt_ = o.ntt_;
+            o.ctx_ = nullptr, o.d_ = nullptr, o.cap_ = o.size_ = o.L_ = 0;
+        }
+        return *this;
+    }
+    void DeviceCiphertext::release()
+    {
+        if (d_)
+            gsb_free(ctx_, d_);
+        d_ = nullptr;
+        cap_ = 0;
+    }
+    void DeviceCiphertext::reserve(gsb_ctx *ctx, size_t words)
+    {
+        if (ctx_ == ctx && cap_ >= words)
+            return;
+        release();
+        void *p = nullptr;
+        check(gsb_malloc(ctx, words * sizeof(uint64_t), &p));
+        ctx_ = ctx, d_ = static_cast<uint64_t *>(p), cap_ = words;
+    }
+
+    void Evaluator::own(const DeviceCiphertext &ct, const char *what) const
+    {
+        if (ct.ctx_ != ctx_ || ct.d_ == nullptr || ct.size_ < 2 || !context_->get_context_data(ct.parms_id_))
+            throw invalid_argument(string(what) + " is not valid for encryption parameters");
+    }
+
+    void Evaluator::upload(const Ciphertext &encrypted, DeviceCiphertext &destination)
+    {
+        validate(encrypted, "encrypted");
+        if (bfv_)
+            throw logic_error("device-resident handles serve CKKS");
+        const size_t L = level_limbs(encrypted), words = encrypted.size() * L * N_;
+        destination.reserve(ctx_, words);
+        check(gsb_memcpy_h2d(ctx_, destination.d_, encrypted.data(), words * sizeof(uint64_t), nullptr));
+        check(gsb_stream_sync(ctx_, nullptr)); // the host object may be changed once this returns
+        destination.size_ = encrypted.size(), destination.L_ = L;
+        destination.parms_id_ = encrypted.parms_id(), destination.scale_ = encrypted.scale(), destination.ntt_ = encrypted.is_ntt_form();
+    }
+
+    void Evaluator::download(const DeviceCiphertext &encrypted, Ciphertext &destination)
+    {
+        own(encrypted, "encrypted");
+        destination.resize(context_, encrypted.parms_id_, encrypted.size_);
+        check(gsb_memcpy_d2h(ctx_, destination.data(), encrypted.d_, encrypted.size_ * encrypted.L_ * N_ * sizeof(uint64_t), nullptr));
+        check(gsb_stream_sync(ctx_, nullptr));
+        destination.is_ntt_form() = encrypted.ntt_;
+        destination.scale() = encrypted.scale_;
+    }
+
+    void Evaluator::multiply_inplace(DeviceCiphertext &e1, const DeviceCiphertext &e2)
+    {
+        own(e1, "encrypted1");
+        own(e2, "encrypted2");
+        if (e1.parms_id_ != e2.parms_id_) // evaluator.cpp:238-249, 449-468
+            throw invalid_argument("encrypted1 and encrypted2 parameter mismatch");
+        if (!(e1.ntt_ && e2.ntt_))
+            throw invalid_argument("encrypted1 or encrypted2 must be in NTT form");
+        auto &context_data = *context_->get_context_data(e1.parms_id_);
+        const double new_scale = e1.scale_ * e2.scale_;
+        if (new_scale <= 0 || (static_cast<int>(log2(new_scale)) >= context_data.total_coeff_modulus_bit_count()))
+            throw invalid_argument("scale out of bounds");
+        if (e1.size_ != 2 || e2.size_ != 2)
+            throw logic_error("device multiply serves size-2 operands (relinearize first)");
+        DeviceCiphertext out;
+        out.reserve(ctx_, 3 * e1.L_ * N_);
+        check(gsb_ckks_multiply_dev(ctx_, e1.d_, e2.d_, out.d_, 1, e1.L_, nullptr));
+        out.size_ = 3, out.L_ = e1.L_, out.parms_id_ = e1.parms_id_, out.scale_ = new_scale, out.ntt_ = true;
+        e1 = move(out);
+    }
+
+    void Evaluator::relinearize_inplace(DeviceCiphertext &e, const RelinKeys &relin_keys)
+    {
+        own(e, "encrypted");
+        if (relin_keys.parms_id() != context_->key_parms_id()) // evaluator.cpp:776-796
+            throw invalid_argument("relin_keys is not valid for encryption parameters");
+        if (relin_keys.size() < e.size_ - 2)
+            throw invalid_argument("not enough relinearization keys");
+        if (e.size_ == 2)
+            return;
+        if (!e.ntt_)
+            throw logic_error("CKKS encrypted must be in NTT form");
+        if (e.size_ != 3)
+            throw logic_error("device-resident relinearization serves size-3 ciphertexts");
+        ensure_relin(relin_keys, RelinKeys::get_index(2));
+        DeviceCiphertext out;
+        out.reserve(ctx_, 2 * e.L_ * N_);
+        check(gsb_relinearize_dev(ctx_, nullptr, e.d_, out.d_, 1, e.L_, nullptr));
+        out.size_ = 2, out.L_ = e.L_, out.parms_id_ = e.parms_id_, out.scale_ = e.scale_, out.ntt_ = true;
+        e = move(out);
+    }
+
+    void Evaluator::rescale_to_next_inplace(DeviceCiphertext &e)
+    {
+        own(e, "encrypted");
+        if (context_->last_parms_id() == e.parms_id_) // evaluator.cpp:1093-1104
+            throw invalid_argument("end of modulus switching chain reached");
+        if (!e.ntt_)
+            throw invalid_argument("CKKS encrypted must be in NTT form");
+        auto &context_data = *context_->get_context_data(e.parms_id_);
+        DeviceCiphertext out;
+        out.reserve(ctx_, e.size_ * (e.L_ - 1) * N_);
+        check(gsb_rescale_dev(ctx_, nullptr, e.d_, out.d_, 1, e.size_, e.L_, nullptr));
+        out.size_ = e.size_, out.L_ = e.L_ - 1, out.parms_id_ = context_data.next_context_data()->parms_id();
+        out.scale_ = e.scale_ / static_cast<double>(context_data.parms().coeff_modulus().back().value()), out.ntt_ = true;
+        e = move(out);
+    }
+
+    void Evaluator::apply_galois_inplace(DeviceCiphertext &e, uint32_t galois_elt, const GaloisKeys &galois_keys)
+    {
+        own(e, "encrypted");
+        if (galois_keys.parms_id() != context_->key_parms_id()) // evaluator.cpp:1845-1887
+            throw invalid_argument("galois_keys is not valid for encryption parameters");
+        if (!galois_keys.has_key(galois_elt))
+            throw invalid_argument("Galois key not present");
+        if (!(galois_elt & 1) || galois_elt >= 2 * N_)
+            throw invalid_argument("Galois element is not valid");
+        if (e.size_ > 2)
+            throw invalid_argument("encrypted size must be 2");
+        if (!e.ntt_)
+            throw logic_error("CKKS encrypted must be in NTT form");
+        ensure_galois(galois_keys, galois_elt);
+        DeviceCiphertext out;
+        out.reserve(ctx_, 2 * e.L_ * N_);
+        check(gsb_apply_galois_dev(ctx_, nullptr, galois_elt, e.d_, out.d_, 1, e.L_, nullptr));
+        out.size_ = 2, out.L_ = e.L_, out.parms_id_ = e.parms_id_, out.scale_ = e.scale_, out.ntt_ = true;
+        e = move(out);
+    }
+
+    void Evaluator::rotate_internal(DeviceCiphertext &e, int steps, const GaloisKeys &galois_keys)
+    {
+        auto context_data_ptr = context_->get_context_data(e.parms_id_); // evaluator.cpp:1945-2000
+        if (!context_data_ptr->qualifiers().using_batching)
+            throw logic_error("encryption parameters do not support batching");
+        if (galois_keys.parms_id() != context_->key_parms_id())
+            throw invalid_argument("galois_keys is not valid for encryption parameters");
+        if (steps == 0)
+            return;
+        auto galois_tool = context_data_ptr->galois_tool();
+        if (galois_keys.has_key(galois_tool->get_elt_from_step(steps)))
+        {
+            apply_galois_inplace(e, galois_tool->get_elt_from_step(steps), galois_keys);
+            return;
+        }
+        const vector<int> naf_steps = seal::util::naf(steps);
+        if (naf_steps.size() == 1)
+            throw invalid_argument("Galois key not present");
+        for (int step : naf_steps)
+            if (static_cast<size_t>(abs(step)) != (N_ >> 1))
+                rotate_internal(e, step, galois_keys);
+    }
+
+    void Evaluator::rotate_vector_inplace(DeviceCiphertext &e, int steps, const GaloisKeys &galois_keys)
+    {
+        own(e, "encrypted");
+        rotate_internal(e, steps, galois_keys);
+    }
+
+    void Evaluator::complex_conjugate_inplace(DeviceCiphertext &e, const GaloisKeys &galois_keys)
+    {
+        own(e, "encrypted");
+        apply_galois_inplace(e, static_cast<uint32_t>(2 * N_ - 1), galois_keys); // evaluator.h:1269-1277
+    }
+
+    void Evaluator::add_inplace(DeviceCiphertext &e1, const DeviceCiphertext &e2)
+    {
+        own(e1, "encrypted1");
+        own(e2, "encrypted2");
+        if (e1.parms_id_ != e2.parms_id_) // evaluator.cpp:90-152
+            throw invalid_argument("encrypted1 and encrypted2 parameter mismatch");
+        if (e1.ntt_ != e2.ntt_)
+            throw invalid_argument("NTT form mismatch");
+        if (!seal::util::are_close<double>(e1.scale_, e2.scale_))
+            throw invalid_argument("scale mismatch");
+        if (e1.size_ != e2.size_)
+            throw logic_error("device-resident add / sub serve operands of equal size");
+        check(gsb_poly_op_dev(ctx_, GSB_OP_ADD, e1.d_, e2.d_, nullptr, e1.d_, e1.size_, e1.L_, 0, nullptr));
+    }
+
+    void Evaluator::sub_inplace(DeviceCiphertext &e1, const DeviceCiphertext &e2)
+    {
+        own(e1, "encrypted1");
+        own(e2, "encrypted2");
+        if (e1.parms_id_ != e2.parms_id_) // evaluator.cpp:174-233
+            throw invalid_argument("encrypted1 and encrypted2 parameter mismatch");
+        if (e1.ntt_ != e2.ntt_)
+            throw invalid_argument("NTT form mismatch");
+        if (!seal::util::are_close<double>(e1.scale_, e2.scale_))
+            throw invalid_argument("scale mismatch");
+        if (e1.size_ != e2.size_)
+            throw logic_error("device-resident add / sub serve operands of equal size");
+        check(gsb_poly_op_dev(ctx_, GSB_OP_SUB, e1.d_, e2.d_, nullptr, e1.d_, e1.size_, e1.L_, 0, nullptr));
+    }
+
+    void Evaluator::negate_inplace(DeviceCiphertext &e)
+    {
+        own(e, "encrypted");
+        check(gsb_poly_op_dev(ctx_, GSB_OP_NEGATE, e.d_, nullptr, nullptr, e.d_, e.size_, e.L_, 0, nullptr));
+    }
+
     // ---- Decryptor (decryptor.cpp:21-149) ------------------------------------------------------------------
     Decryptor::Decryptor(shared_ptr<SEALContext> context, const SecretKey &secret_key, int device) : context_(move(context))
     {

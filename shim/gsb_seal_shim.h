@@ -26,6 +26,42 @@
 
 namespace gsb_seal
 {
+    class Evaluator;
+
+    // Device-resident ciphertext handle (no counterpart in the reference): the limbs
+    // of a CKKS ciphertext stay in HBM across evaluator calls, only the metadata lives on the host.
+    // Evaluator::upload validates exactly as the reference's evaluator validates its operands
+    // (is_metadata_valid_for + is_buffer_valid); the overloads below then run multiply / relinearize /
+    // rescale / rotate / add / sub / negate without a host copy per operation; Evaluator::download gives
+    // back a seal::Ciphertext that is word for word what the same calls on seal::Evaluator produce.
+    class DeviceCiphertext
+    {
+    public:
+        DeviceCiphertext() = default;
+        ~DeviceCiphertext();
+        DeviceCiphertext(DeviceCiphertext &&other) noexcept;
+        DeviceCiphertext &operator=(DeviceCiphertext &&other) noexcept;
+        DeviceCiphertext(const DeviceCiphertext &) = delete;
+        DeviceCiphertext &operator=(const DeviceCiphertext &) = delete;
+        std::size_t size() const { return size_; }
+        std::size_t coeff_modulus_size() const { return L_; }
+        const seal::parms_id_type &parms_id() const { return parms_id_; }
+        double scale() const { return scale_; }
+        bool is_ntt_form() const { return ntt_; }
+        const std::uint64_t *device_data() const { return d_; }
+
+    private:
+        friend class Evaluator;
+        void reserve(gsb_ctx *ctx, std::size_t words);
+        void release();
+        gsb_ctx *ctx_ = nullptr;
+        std::uint64_t *d_ = nullptr;
+        std::size_t cap_ = 0, size_ = 0, L_ = 0;
+        seal::parms_id_type parms_id_ = seal::parms_id_zero;
+        double scale_ = 1.0;
+        bool ntt_ = false;
+    };
+
     class Evaluator
     {
     public:
@@ -120,6 +156,19 @@ namespace gsb_seal
             std::vector<seal::Ciphertext *> &encrypted1, const std::vector<const seal::Ciphertext *> &encrypted2,
             const seal::RelinKeys &relin_keys);
 
+        // ---- device-resident handles (CKKS) ------------------------------------------------------------
+        void upload(const seal::Ciphertext &encrypted, DeviceCiphertext &destination);
+        void download(const DeviceCiphertext &encrypted, seal::Ciphertext &destination);
+        void multiply_inplace(DeviceCiphertext &encrypted1, const DeviceCiphertext &encrypted2);
+        void relinearize_inplace(DeviceCiphertext &encrypted, const seal::RelinKeys &relin_keys);
+        void rescale_to_next_inplace(DeviceCiphertext &encrypted);
+        void apply_galois_inplace(DeviceCiphertext &encrypted, std::uint32_t galois_elt, const seal::GaloisKeys &galois_keys);
+        void rotate_vector_inplace(DeviceCiphertext &encrypted, int steps, const seal::GaloisKeys &galois_keys);
+        void complex_conjugate_inplace(DeviceCiphertext &encrypted, const seal::GaloisKeys &galois_keys);
+        void add_inplace(DeviceCiphertext &encrypted1, const DeviceCiphertext &encrypted2);
+        void sub_inplace(DeviceCiphertext &encrypted1, const DeviceCiphertext &encrypted2);
+        void negate_inplace(DeviceCiphertext &encrypted);
+
         gsb_ctx *device_context() const { return ctx_; }
         // what the C layer's Evaluator_ContextUsingKeyswitching reports (c/evaluator.cpp:23-29)
         bool using_keyswitching() const { return context_->using_keyswitching(); }
@@ -133,6 +182,8 @@ namespace gsb_seal
         void ensure_galois(const seal::GaloisKeys &keys, std::uint32_t elt);
         void upload_key(int kind, std::uint32_t slot, const std::vector<seal::PublicKey> &bundles);
         void rotate_internal(seal::Ciphertext &encrypted, int steps, const seal::GaloisKeys &galois_keys);
+        void rotate_internal(DeviceCiphertext &encrypted, int steps, const seal::GaloisKeys &galois_keys);
+        void own(const DeviceCiphertext &ct, const char *what) const;
         [[noreturn]] void fail(int rc) const;
 
         std::shared_ptr<seal::SEALContext> context_;

@@ -128,6 +128,41 @@ static int run(size_t N, vector<int> bits, int k_special)
     dev.complex_conjugate_inplace(d, glk);
     same("complex_conjugate_inplace", r, d);
     {
+        // row f3: the same chain on device-resident handles -- one upload per operand, one download
+        gsb_seal::DeviceCiphertext da, db, dc;
+        dev.upload(a, da);
+        dev.upload(b, db);
+        dev.multiply_inplace(da, db);
+        dev.relinearize_inplace(da, rlk);
+        dev.rescale_to_next_inplace(da);
+        dev.rotate_vector_inplace(da, 1, glk);
+        dev.rotate_vector_inplace(da, -3, glk);
+        dev.complex_conjugate_inplace(da, glk);
+        Ciphertext back;
+        dev.download(da, back);
+        same("device-resident chain (6 ops)", r, back);
+        Ciphertext r5 = a, back5;
+        ref.add_inplace(r5, b);
+        ref.negate_inplace(r5);
+        ref.sub_inplace(r5, a);
+        dev.upload(a, dc);
+        dev.add_inplace(dc, db);
+        dev.negate_inplace(dc);
+        gsb_seal::DeviceCiphertext da2;
+        dev.upload(a, da2);
+        dev.sub_inplace(dc, da2);
+        dev.download(dc, back5);
+        same("device-resident add / negate / sub", r5, back5);
+        expect_throw("device-resident level mismatch", [&] { dev.add_inplace(da, db); }, 0);
+        expect_throw("device-resident multiply of size 3", [&] {
+            gsb_seal::DeviceCiphertext x, y;
+            dev.upload(a, x);
+            dev.upload(b, y);
+            dev.multiply_inplace(x, y);
+            dev.multiply_inplace(x, y);
+        }, 1);
+    }
+    {
         Ciphertext r2 = a, d2 = a;
         ref.square_inplace(r2);
         dev.multiply_inplace(d2, d2);
