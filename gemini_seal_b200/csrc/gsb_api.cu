@@ -252,10 +252,11 @@ int gsb_ctx_create(int device, int logn, const uint64_t *moduli, size_t K, size_
             // GSB_LITERAL=1 (read at context creation; a testing aid): every congruent-word shortcut off, the
             // kernels carry the reference's own intermediate words.  tests/test_gpu_parity.py runs the full
             // size both ways and requires identical outputs.
+            ctx->wide_inv = static_cast<u128>(qmax) * 10 < (static_cast<u128>(1) << 63);
             const char *lit = std::getenv("GSB_LITERAL");
             if (lit && lit[0] == '1')
             {
-                ctx->fast_ntt = ctx->lazy_modup = ctx->lazy_mac = false;
+                ctx->fast_ntt = ctx->lazy_modup = ctx->lazy_mac = ctx->wide_inv = false;
                 for (auto &c : limb)
                     c.mu = 0;
             }
@@ -460,7 +461,7 @@ static void ntt_dev(
         uint64_t *p = data + p0 * per;
         if (inverse)
         {
-            GSB_DISPATCH_LOGN(ctx->logn, ntt_inverse_plain<LOGN>(tab, mm, p, per, p, per, static_cast<int>(n_limbs), nz, lazy, st));
+            GSB_DISPATCH_LOGN(ctx->logn, ntt_inverse_plain<LOGN>(tab, mm, p, per, p, per, static_cast<int>(n_limbs), nz, lazy, st, "plain", !lazy && ctx->wide_inv));
         }
         else
         {

@@ -96,6 +96,9 @@ struct gsb_ctx
     //   lazy_modup: = fast_ntt                        (single-limb bundle enters the NTT unreduced)
     //   lazy_mac:   beta0 (5n + 2) q_max^2 < 2^128    (sum of beta0 products operand x key)
     bool fast_ntt = false;
+    //   wide_inv:   10 q_max < 2^63                   (wide-range inverse butterflies keep words in [0,5q);
+    //                                                  no growth, so it also holds for 59-bit moduli)
+    bool wide_inv = false;
     bool lazy_modup = false, lazy_mac = false;
     std::vector<gsb::host::LimbTables> tables; // host copies (introspection + constants)
     gsb::Twiddle *d_WW = nullptr, *d_VV = nullptr;

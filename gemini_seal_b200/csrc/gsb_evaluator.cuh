@@ -318,7 +318,7 @@ namespace gsb
                 coef, L * N * sizeof(uint64_t), target, target_stride * sizeof(uint64_t), L * N * sizeof(uint64_t), B,
                 cudaMemcpyDeviceToDevice, st));
         else
-            ntt_inverse_plain<LOGN>(tab, ModMap{ 1 << 30, 0, 0 }, target, target_stride, coef, L * N, iL, iB, false, st, "ks_target");
+            ntt_inverse_plain<LOGN>(tab, ModMap{ 1 << 30, 0, 0 }, target, target_stride, coef, L * N, iL, iB, false, st, "ks_target", ctx->wide_inv);
 
         // Step 2 + first NTT pass of step 3 (:2310, :2322): mod-up fused into the column pass.
         if constexpr (two)
@@ -352,7 +352,7 @@ namespace gsb
         // Step 4 (:2353-2357): lazy inverse NTT of the special slots.
         ntt_inverse_plain<LOGN>(
             tab, ModMap{ 0, static_cast<int>(ctx->L0), 0 }, red + L * N, E * N, red + L * N, E * N, static_cast<int>(k),
-            static_cast<int>(2 * B), true, st, "ks_special");
+            static_cast<int>(2 * B), true, st, "ks_special", ctx->wide_inv);
         // Step 5 (mod-down) + final add (:2360-2366).
         const MdLoadArgs la{ ks, red };
         const MdStoreArgs sa{ ks, red, o.add_src, o.add_bs, o.add_ls, o.dst, o.dst_bs, o.dst_ls, o.table, o.zero_l1 || o.table != nullptr };
@@ -582,7 +582,7 @@ namespace gsb
         p.ct_stride = (size - 1) * LN;
         p.c0 = nullptr;
         GSB_LAUNCH("dot_sk", "coeff", dot_sk_kernel, dim3(grid_for(p.pairs, 256)), dim3(256), 0, st, p);
-        ntt_inverse_plain<LOGN>(tab, mm, out, LN, out, LN, static_cast<int>(L), static_cast<int>(B), false, st, "dot_sk");
+        ntt_inverse_plain<LOGN>(tab, mm, out, LN, out, LN, static_cast<int>(L), static_cast<int>(B), false, st, "dot_sk", ctx->wide_inv);
         // add_poly_coeffmod(destination, c_0) (:265): c_0 of ciphertext b sits at in + b*size*LN
         for (size_t b = 0; b < B; b++)
         {

@@ -324,10 +324,17 @@ namespace gsb
     // ---- inverse round: BackwardLazy / BackwardLazyLast (util/ntt.cpp:265-281) -----------------
     // Round covers gaps 2^BOT ... 2^(BOT+R-1), smallest first.  LAST: the gap-2^(BOT+R-1) stage is
     // the global last stage (m = 1), where n^-1 is folded in (util/ntt.cpp:391-402).
-    template <int BOT, int R, int T_LOG, bool LAST, class TW>
+    // FAST (wide-range inverse butterflies, gsb_ctx::wide_inv: 10 q_max < 2^63): words live in [0,5q)
+    // instead of [0,2q) -- the sum takes a conditional subtraction of 5q, the difference u - v + 5q < 10q
+    // goes through mulmod_wide_add -- with no growth from stage to stage.  The global last stage stays
+    // the literal BackwardLazyLast (exact Shoup products accept any 64-bit word), so the transform's
+    // outputs are in [0,2q) as in the reference.  Only for transforms whose output is canonicalised
+    // (strict) or consumed inside the library.
+    template <int BOT, int R, int T_LOG, bool LAST, bool FAST = false, class TW>
     GSB_DEV void inv_round(uint64_t (&x)[8], uint32_t tid, const TW &tw, const LimbC &c)
     {
         constexpr int TOP = BOT + R - 1;
+        const uint64_t five_q = c.two_q + c.two_q + c.q, neg_two_q = 0 - c.two_q;
 #pragma unroll
         for (int sub = 0; sub < (8 >> R); sub++)
         {
@@ -340,17 +347,37 @@ namespace gsb
                 for (int grp = 0; grp < (1 << (R - 1 - s)); grp++)
                 {
                     const Twiddle w = tw.inv(g, base, grp);
+                    const bool last = LAST && s == R - 1;
+                    const uint64_t wsh = w.y >> 1;
 #pragma unroll
                     for (int i = 0; i < (1 << s); i++)
                     {
                         const int a = sub * (1 << R) + (grp << (s + 1)) + i, b = a + (1 << s);
                         const uint64_t u = x[a], v = x[b];
                         uint64_t t = u + v + c.pad; // c.pad == 0 at run time, see fwd_round
-                        t -= (t >= c.two_q) ? c.two_q : 0;
-                        if (LAST && s == R - 1)
-                            t = mulmod_lazy(t, c.inv_n, c.inv_n_s, c.q);
-                        x[a] = t;
-                        x[b] = mulmod_lazy(u - v + c.two_q, w.x, w.y, c.q);
+                        if (FAST)
+                        {
+                            GSB_SIM_ASSERT(u < five_q && v < five_q);
+                            if (last)
+                            {
+                                x[a] = mulmod_lazy(t, c.inv_n, c.inv_n_s, c.q);
+                                x[b] = mulmod_lazy(u - v + five_q, w.x, w.y, c.q);
+                            }
+                            else
+                            {
+                                t -= (t >= five_q) ? five_q : 0;
+                                x[a] = t;
+                                x[b] = mulmod_wide_add(u - v + five_q, w.x, wsh, neg_two_q, 0, c.pad);
+                            }
+                        }
+                        else
+                        {
+                            t -= (t >= c.two_q) ? c.two_q : 0;
+                            if (last)
+                                t = mulmod_lazy(t, c.inv_n, c.inv_n_s, c.q);
+                            x[a] = t;
+                            x[b] = mulmod_lazy(u - v + c.two_q, w.x, w.y, c.q);
+                        }
                     }
                 }
             }
@@ -552,7 +579,7 @@ namespace gsb
     }
 
     // Inverse: rounds run in the reverse order of the forward plan (smallest gaps first).
-    template <int T_LOG, int G_HI, int G_LO, bool LAST, int IDX, class TW>
+    template <int T_LOG, int G_HI, int G_LO, bool LAST, int IDX, bool FAST = false, class TW>
     GSB_DEV void inv_compute(uint64_t (&x)[8], uint64_t *smem, uint32_t tid, const TW &tw, const LimbC &c, int &parity)
     {
         constexpr int NS = G_HI - G_LO + 1;
@@ -570,12 +597,12 @@ namespace gsb
                 __syncthreads();
                 tile_load<TOP, R, T_LOG>(buf, x, tid);
             }
-            inv_round<BOT, R, T_LOG, (LAST && IDX == NR - 1)>(x, tid, tw, c);
+            inv_round<BOT, R, T_LOG, (LAST && IDX == NR - 1), FAST>(x, tid, tw, c);
             if constexpr (IDX < NR - 1)
             {
                 uint64_t *buf = smem + (static_cast<size_t>(parity) << (T_LOG + 3));
                 tile_store<TOP, R, T_LOG>(buf, x, tid);
-                inv_compute<T_LOG, G_HI, G_LO, LAST, IDX + 1>(x, smem, tid, tw, c, parity);
+                inv_compute<T_LOG, G_HI, G_LO, LAST, IDX + 1, FAST>(x, smem, tid, tw, c, parity);
             }
         }
     }

@@ -114,7 +114,7 @@ namespace gsb
         static constexpr size_t smem_bytes = exch_words * sizeof(uint64_t) + PAIRS * sizeof(Twiddle) + 16;
     };
 
-    // FAST (forward only): wide-range butterflies, see fwd_round.
+    // FAST: wide-range butterflies, see fwd_round / inv_round.
     template <bool INVERSE, int T_LOG, int G_HI, int G_LO, bool LAST, int A, class IO, bool FAST = false>
     __global__ void __launch_bounds__(1 << T_LOG, T_LOG <= 8 ? GSB_TILE_MIN_CTAS : 1) ntt_tile_kernel(IO io, NttTables tab, ModMap mm, int nz, int zb)
     {
@@ -175,7 +175,7 @@ namespace gsb
                 if constexpr (has_prefetch<typename IO::Epi>::value)
                     xf_prefetch<T_LOG, G_HI, G_LO, INVERSE>(tid, tile, map, epi);
                 if constexpr (INVERSE)
-                    inv_compute<T_LOG, G_HI, G_LO, LAST, 0>(x, smem, tid, tw, c, parity);
+                    inv_compute<T_LOG, G_HI, G_LO, LAST, 0, FAST>(x, smem, tid, tw, c, parity);
                 else if constexpr (FAST)
                     fwd_compute<T_LOG, G_HI, G_LO, LAST, 0, true>(x, smem, tid, TwPreshifted<std::decay_t<decltype(tw)>>{ tw }, c, parity);
                 else
@@ -274,25 +274,25 @@ namespace gsb
     }
 
     // Inverse pass 1 (contiguous) -- or the whole transform when !two_pass.
-    template <int LOGN, class IO>
+    template <int LOGN, bool FAST = false, class IO>
     inline void launch_inv_contig(
         const IO &io, const NttTables &tab, const ModMap &mm, int ny, int nz, cudaStream_t st, const char *tag = "plain")
     {
         using SP = Split<LOGN>;
         if constexpr (SP::two_pass)
-            launch_tile<true, 8, LOGN - SP::A - 1, 0, false, 0>("inv_contig", tag, io, tab, mm, 1u << (LOGN - 11), ny, nz, st);
+            launch_tile<true, 8, LOGN - SP::A - 1, 0, false, 0, FAST>("inv_contig", tag, io, tab, mm, 1u << (LOGN - 11), ny, nz, st);
         else
-            launch_tile<true, SP::T1, LOGN - 1, 0, true, 0>("inv_contig", tag, io, tab, mm, 1u, ny, nz, st);
+            launch_tile<true, SP::T1, LOGN - 1, 0, true, 0, FAST>("inv_contig", tag, io, tab, mm, 1u, ny, nz, st);
     }
 
     // Inverse pass 2 (columns; carries the global last stage with n^-1).
-    template <int LOGN, class IO>
+    template <int LOGN, bool FAST = false, class IO>
     inline void launch_inv_cols(
         const IO &io, const NttTables &tab, const ModMap &mm, int ny, int nz, cudaStream_t st, const char *tag = "plain")
     {
         using SP = Split<LOGN>;
         constexpr int A = SP::A, TC = SP::TC, C = TC + 3 - A;
-        launch_tile<true, TC, A + C - 1, C, true, A>("inv_cols", tag, io, tab, mm, (1u << (LOGN - A)) >> C, ny, nz, st);
+        launch_tile<true, TC, A + C - 1, C, true, A, FAST>("inv_cols", tag, io, tab, mm, (1u << (LOGN - A)) >> C, ny, nz, st);
     }
 
     // Plain batched transforms: element (z, y, d) of src/dst at base + z*zs + y*N + d; in place
@@ -314,26 +314,39 @@ namespace gsb
             launch_fwd_contig<LOGN>(IoPlain<OUT_FWD_STRICT>{ src, dst, src_zs, dst_zs }, tab, mm, ny, nz, st, tag);
     }
 
-    template <int LOGN>
-    inline void ntt_inverse_plain(
+    // wide: run the wide-range inverse butterflies (inv_round FAST).  Callers pass it only under
+    // gsb_ctx::wide_inv and only when the output is strict (canonical) or stays inside the library.
+    template <int LOGN, bool FAST>
+    inline void ntt_inverse_plain_t(
         const NttTables &tab, const ModMap &mm, const uint64_t *src, size_t src_zs, uint64_t *dst, size_t dst_zs, int ny,
-        int nz, bool lazy, cudaStream_t st, const char *tag = "plain")
+        int nz, bool lazy, cudaStream_t st, const char *tag)
     {
         if constexpr (Split<LOGN>::two_pass)
         {
-            launch_inv_contig<LOGN>(IoPlain<OUT_RAW>{ src, dst, src_zs, dst_zs }, tab, mm, ny, nz, st, tag);
+            launch_inv_contig<LOGN, FAST>(IoPlain<OUT_RAW>{ src, dst, src_zs, dst_zs }, tab, mm, ny, nz, st, tag);
             if (lazy)
-                launch_inv_cols<LOGN>(IoPlain<OUT_RAW>{ dst, dst, dst_zs, dst_zs }, tab, mm, ny, nz, st, tag);
+                launch_inv_cols<LOGN, FAST>(IoPlain<OUT_RAW>{ dst, dst, dst_zs, dst_zs }, tab, mm, ny, nz, st, tag);
             else
-                launch_inv_cols<LOGN>(IoPlain<OUT_INV_STRICT>{ dst, dst, dst_zs, dst_zs }, tab, mm, ny, nz, st, tag);
+                launch_inv_cols<LOGN, FAST>(IoPlain<OUT_INV_STRICT>{ dst, dst, dst_zs, dst_zs }, tab, mm, ny, nz, st, tag);
         }
         else
         {
             if (lazy)
-                launch_inv_contig<LOGN>(IoPlain<OUT_RAW>{ src, dst, src_zs, dst_zs }, tab, mm, ny, nz, st, tag);
+                launch_inv_contig<LOGN, FAST>(IoPlain<OUT_RAW>{ src, dst, src_zs, dst_zs }, tab, mm, ny, nz, st, tag);
             else
-                launch_inv_contig<LOGN>(IoPlain<OUT_INV_STRICT>{ src, dst, src_zs, dst_zs }, tab, mm, ny, nz, st, tag);
+                launch_inv_contig<LOGN, FAST>(IoPlain<OUT_INV_STRICT>{ src, dst, src_zs, dst_zs }, tab, mm, ny, nz, st, tag);
         }
+    }
+
+    template <int LOGN>
+    inline void ntt_inverse_plain(
+        const NttTables &tab, const ModMap &mm, const uint64_t *src, size_t src_zs, uint64_t *dst, size_t dst_zs, int ny,
+        int nz, bool lazy, cudaStream_t st, const char *tag = "plain", bool wide = false)
+    {
+        if (wide)
+            ntt_inverse_plain_t<LOGN, true>(tab, mm, src, src_zs, dst, dst_zs, ny, nz, lazy, st, tag);
+        else
+            ntt_inverse_plain_t<LOGN, false>(tab, mm, src, src_zs, dst, dst_zs, ny, nz, lazy, st, tag);
     }
 
 // Dispatch a templated call on the runtime log2(N) (10..16 supported on the device path).
