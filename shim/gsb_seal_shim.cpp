@@ -746,9 +746,9 @@ namespace gsb_seal
         if (this != &o)
         {
             release();
-            ctx_ = o.ctx_, d_ = o.d_, cap_ = o.cap_, size_ = o.size_, L_ = o.L_;
+            ctx_ = o.ctx_, d_ = o.d_, cap_ = o.cap_, size_ = o.size_, L_ = o.L_, batch_ = o.batch_;
             parms_id_ = o.parms_id_, scale_ = o.scale_, ntt_ = o.ntt_;
-            o.ctx_ = nullptr, o.d_ = nullptr, o.cap_ = o.size_ = o.L_ = 0;
+            o.ctx_ = nullptr, o.d_ = nullptr, o.cap_ = o.size_ = o.L_ = 0, o.batch_ = 1;
         }
         return *this;
     }
@@ -771,7 +771,7 @@ namespace gsb_seal
 
     void Evaluator::own(const DeviceCiphertext &ct, const char *what) const
     {
-        if (ct.ctx_ != ctx_ || ct.d_ == nullptr || ct.size_ < 2 || !context_->get_context_data(ct.parms_id_))
+        if (ct.ctx_ != ctx_ || ct.d_ == nullptr || ct.size_ < 2 || ct.batch_ < 1 || !context_->get_context_data(ct.parms_id_))
             throw invalid_argument(string(what) + " is not valid for encryption parameters");
     }
 
@@ -784,13 +784,55 @@ namespace gsb_seal
         destination.reserve(ctx_, words);
         check(gsb_memcpy_h2d(ctx_, destination.d_, encrypted.data(), words * sizeof(uint64_t), nullptr));
         check(gsb_stream_sync(ctx_, nullptr)); // the host object may be changed once this returns
-        destination.size_ = encrypted.size(), destination.L_ = L;
+        destination.size_ = encrypted.size(), destination.L_ = L, destination.batch_ = 1;
         destination.parms_id_ = encrypted.parms_id(), destination.scale_ = encrypted.scale(), destination.ntt_ = encrypted.is_ntt_form();
+    }
+
+    void Evaluator::upload(const vector<const Ciphertext *> &encrypted, DeviceCiphertext &destination)
+    {
+        if (encrypted.empty() || encrypted[0] == nullptr)
+            throw invalid_argument("encrypted vector must not be empty");
+        if (bfv_)
+            throw logic_error("device-resident handles serve CKKS");
+        const Ciphertext &first = *encrypted[0];
+        for (const Ciphertext *ct : encrypted)
+        {
+            if (ct == nullptr)
+                throw invalid_argument("encrypted is not valid for encryption parameters");
+            validate(*ct, "encrypted");
+            if (ct->parms_id() != first.parms_id() || ct->size() != first.size() || ct->is_ntt_form() != first.is_ntt_form() ||
+                !seal::util::are_close<double>(ct->scale(), first.scale()))
+                throw invalid_argument("batched ciphertexts must share level, size, form and scale");
+        }
+        const size_t L = level_limbs(first), words = first.size() * L * N_, n = encrypted.size();
+        destination.reserve(ctx_, n * words);
+        for (size_t i = 0; i < n; i++)
+            check(gsb_memcpy_h2d(ctx_, destination.d_ + i * words, encrypted[i]->data(), words * sizeof(uint64_t), nullptr));
+        check(gsb_stream_sync(ctx_, nullptr));
+        destination.size_ = first.size(), destination.L_ = L, destination.batch_ = n;
+        destination.parms_id_ = first.parms_id(), destination.scale_ = first.scale(), destination.ntt_ = first.is_ntt_form();
+    }
+
+    void Evaluator::download(const DeviceCiphertext &encrypted, vector<Ciphertext> &destination)
+    {
+        own(encrypted, "encrypted");
+        const size_t words = encrypted.size_ * encrypted.L_ * N_;
+        destination.resize(encrypted.batch_);
+        for (size_t i = 0; i < encrypted.batch_; i++)
+        {
+            destination[i].resize(context_, encrypted.parms_id_, encrypted.size_);
+            check(gsb_memcpy_d2h(ctx_, destination[i].data(), encrypted.d_ + i * words, words * sizeof(uint64_t), nullptr));
+            destination[i].is_ntt_form() = encrypted.ntt_;
+            destination[i].scale() = encrypted.scale_;
+        }
+        check(gsb_stream_sync(ctx_, nullptr));
     }
 
     void Evaluator::download(const DeviceCiphertext &encrypted, Ciphertext &destination)
     {
         own(encrypted, "encrypted");
+        if (encrypted.batch_ != 1)
+            throw invalid_argument("handle holds a batch: download into a vector");
         destination.resize(context_, encrypted.parms_id_, encrypted.size_);
         check(gsb_memcpy_d2h(ctx_, destination.data(), encrypted.d_, encrypted.size_ * encrypted.L_ * N_ * sizeof(uint64_t), nullptr));
         check(gsb_stream_sync(ctx_, nullptr));
@@ -812,10 +854,12 @@ namespace gsb_seal
             throw invalid_argument("scale out of bounds");
         if (e1.size_ != 2 || e2.size_ != 2)
             throw logic_error("device multiply serves size-2 operands (relinearize first)");
+        if (e1.batch_ != e2.batch_)
+            throw invalid_argument("encrypted1 and encrypted2 batch mismatch");
         DeviceCiphertext out;
-        out.reserve(ctx_, 3 * e1.L_ * N_);
-        check(gsb_ckks_multiply_dev(ctx_, e1.d_, e2.d_, out.d_, 1, e1.L_, nullptr));
-        out.size_ = 3, out.L_ = e1.L_, out.parms_id_ = e1.parms_id_, out.scale_ = new_scale, out.ntt_ = true;
+        out.reserve(ctx_, e1.batch_ * 3 * e1.L_ * N_);
+        check(gsb_ckks_multiply_dev(ctx_, e1.d_, e2.d_, out.d_, e1.batch_, e1.L_, nullptr));
+        out.size_ = 3, out.L_ = e1.L_, out.batch_ = e1.batch_, out.parms_id_ = e1.parms_id_, out.scale_ = new_scale, out.ntt_ = true;
         e1 = move(out);
     }
 
@@ -834,9 +878,9 @@ namespace gsb_seal
             throw logic_error("device-resident relinearization serves size-3 ciphertexts");
         ensure_relin(relin_keys, RelinKeys::get_index(2));
         DeviceCiphertext out;
-        out.reserve(ctx_, 2 * e.L_ * N_);
-        check(gsb_relinearize_dev(ctx_, nullptr, e.d_, out.d_, 1, e.L_, nullptr));
-        out.size_ = 2, out.L_ = e.L_, out.parms_id_ = e.parms_id_, out.scale_ = e.scale_, out.ntt_ = true;
+        out.reserve(ctx_, e.batch_ * 2 * e.L_ * N_);
+        check(gsb_relinearize_dev(ctx_, nullptr, e.d_, out.d_, e.batch_, e.L_, nullptr));
+        out.size_ = 2, out.L_ = e.L_, out.batch_ = e.batch_, out.parms_id_ = e.parms_id_, out.scale_ = e.scale_, out.ntt_ = true;
         e = move(out);
     }
 
@@ -849,9 +893,9 @@ namespace gsb_seal
             throw invalid_argument("CKKS encrypted must be in NTT form");
         auto &context_data = *context_->get_context_data(e.parms_id_);
         DeviceCiphertext out;
-        out.reserve(ctx_, e.size_ * (e.L_ - 1) * N_);
-        check(gsb_rescale_dev(ctx_, nullptr, e.d_, out.d_, 1, e.size_, e.L_, nullptr));
-        out.size_ = e.size_, out.L_ = e.L_ - 1, out.parms_id_ = context_data.next_context_data()->parms_id();
+        out.reserve(ctx_, e.batch_ * e.size_ * (e.L_ - 1) * N_);
+        check(gsb_rescale_dev(ctx_, nullptr, e.d_, out.d_, e.batch_, e.size_, e.L_, nullptr));
+        out.size_ = e.size_, out.L_ = e.L_ - 1, out.batch_ = e.batch_, out.parms_id_ = context_data.next_context_data()->parms_id();
         out.scale_ = e.scale_ / static_cast<double>(context_data.parms().coeff_modulus().back().value()), out.ntt_ = true;
         e = move(out);
     }
@@ -871,9 +915,9 @@ namespace gsb_seal
             throw logic_error("CKKS encrypted must be in NTT form");
         ensure_galois(galois_keys, galois_elt);
         DeviceCiphertext out;
-        out.reserve(ctx_, 2 * e.L_ * N_);
-        check(gsb_apply_galois_dev(ctx_, nullptr, galois_elt, e.d_, out.d_, 1, e.L_, nullptr));
-        out.size_ = 2, out.L_ = e.L_, out.parms_id_ = e.parms_id_, out.scale_ = e.scale_, out.ntt_ = true;
+        out.reserve(ctx_, e.batch_ * 2 * e.L_ * N_);
+        check(gsb_apply_galois_dev(ctx_, nullptr, galois_elt, e.d_, out.d_, e.batch_, e.L_, nullptr));
+        out.size_ = 2, out.L_ = e.L_, out.batch_ = e.batch_, out.parms_id_ = e.parms_id_, out.scale_ = e.scale_, out.ntt_ = true;
         e = move(out);
     }
 
@@ -922,9 +966,9 @@ namespace gsb_seal
             throw invalid_argument("NTT form mismatch");
         if (!seal::util::are_close<double>(e1.scale_, e2.scale_))
             throw invalid_argument("scale mismatch");
-        if (e1.size_ != e2.size_)
-            throw logic_error("device-resident add / sub serve operands of equal size");
-        check(gsb_poly_op_dev(ctx_, GSB_OP_ADD, e1.d_, e2.d_, nullptr, e1.d_, e1.size_, e1.L_, 0, nullptr));
+        if (e1.size_ != e2.size_ || e1.batch_ != e2.batch_)
+            throw logic_error("device-resident add / sub serve operands of equal size and batch");
+        check(gsb_poly_op_dev(ctx_, GSB_OP_ADD, e1.d_, e2.d_, nullptr, e1.d_, e1.batch_ * e1.size_, e1.L_, 0, nullptr));
     }
 
     void Evaluator::sub_inplace(DeviceCiphertext &e1, const DeviceCiphertext &e2)
@@ -937,15 +981,15 @@ namespace gsb_seal
             throw invalid_argument("NTT form mismatch");
         if (!seal::util::are_close<double>(e1.scale_, e2.scale_))
             throw invalid_argument("scale mismatch");
-        if (e1.size_ != e2.size_)
-            throw logic_error("device-resident add / sub serve operands of equal size");
-        check(gsb_poly_op_dev(ctx_, GSB_OP_SUB, e1.d_, e2.d_, nullptr, e1.d_, e1.size_, e1.L_, 0, nullptr));
+        if (e1.size_ != e2.size_ || e1.batch_ != e2.batch_)
+            throw logic_error("device-resident add / sub serve operands of equal size and batch");
+        check(gsb_poly_op_dev(ctx_, GSB_OP_SUB, e1.d_, e2.d_, nullptr, e1.d_, e1.batch_ * e1.size_, e1.L_, 0, nullptr));
     }
 
     void Evaluator::negate_inplace(DeviceCiphertext &e)
     {
         own(e, "encrypted");
-        check(gsb_poly_op_dev(ctx_, GSB_OP_NEGATE, e.d_, nullptr, nullptr, e.d_, e.size_, e.L_, 0, nullptr));
+        check(gsb_poly_op_dev(ctx_, GSB_OP_NEGATE, e.d_, nullptr, nullptr, e.d_, e.batch_ * e.size_, e.L_, 0, nullptr));
     }
 
     // ---- Decryptor (decryptor.cpp:21-149) ------------------------------------------------------------------

@@ -44,6 +44,7 @@ namespace gsb_seal
         DeviceCiphertext(const DeviceCiphertext &) = delete;
         DeviceCiphertext &operator=(const DeviceCiphertext &) = delete;
         std::size_t size() const { return size_; }
+        std::size_t batch() const { return batch_; } // ciphertexts held back to back (same level, size, scale)
         std::size_t coeff_modulus_size() const { return L_; }
         const seal::parms_id_type &parms_id() const { return parms_id_; }
         double scale() const { return scale_; }
@@ -56,7 +57,7 @@ namespace gsb_seal
         void release();
         gsb_ctx *ctx_ = nullptr;
         std::uint64_t *d_ = nullptr;
-        std::size_t cap_ = 0, size_ = 0, L_ = 0;
+        std::size_t cap_ = 0, size_ = 0, L_ = 0, batch_ = 1;
         seal::parms_id_type parms_id_ = seal::parms_id_zero;
         double scale_ = 1.0;
         bool ntt_ = false;
@@ -159,6 +160,11 @@ namespace gsb_seal
         // ---- device-resident handles (CKKS) ------------------------------------------------------------
         void upload(const seal::Ciphertext &encrypted, DeviceCiphertext &destination);
         void download(const DeviceCiphertext &encrypted, seal::Ciphertext &destination);
+        // Batched form: n ciphertexts of the same level, size, form and scale in one handle; every
+        // overload below then runs ONE batched device pass over all of them (this is how the
+        // throughput of bench.py is reached from C++).
+        void upload(const std::vector<const seal::Ciphertext *> &encrypted, DeviceCiphertext &destination);
+        void download(const DeviceCiphertext &encrypted, std::vector<seal::Ciphertext> &destination);
         void multiply_inplace(DeviceCiphertext &encrypted1, const DeviceCiphertext &encrypted2);
         void relinearize_inplace(DeviceCiphertext &encrypted, const seal::RelinKeys &relin_keys);
         void rescale_to_next_inplace(DeviceCiphertext &encrypted);

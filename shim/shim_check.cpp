@@ -153,6 +153,33 @@ static int run(size_t N, vector<int> bits, int k_special)
         dev.sub_inplace(dc, da2);
         dev.download(dc, back5);
         same("device-resident add / negate / sub", r5, back5);
+        {
+            // batched handle: three (a_i, b_i) pairs through one batched device pass per operation
+            vector<Ciphertext> as(3, a), bs(3, b), want(3), got;
+            dev.negate_inplace(as[1]);
+            dev.add_inplace(bs[2], a);
+            vector<const Ciphertext *> pa2, pb2;
+            for (size_t i = 0; i < 3; i++)
+            {
+                pa2.push_back(&as[i]);
+                pb2.push_back(&bs[i]);
+                want[i] = as[i];
+                ref.multiply_inplace(want[i], bs[i]);
+                ref.relinearize_inplace(want[i], rlk);
+                ref.rescale_to_next_inplace(want[i]);
+                ref.rotate_vector_inplace(want[i], 1, glk);
+            }
+            gsb_seal::DeviceCiphertext ba, bb;
+            dev.upload(pa2, ba);
+            dev.upload(pb2, bb);
+            dev.multiply_inplace(ba, bb);
+            dev.relinearize_inplace(ba, rlk);
+            dev.rescale_to_next_inplace(ba);
+            dev.rotate_vector_inplace(ba, 1, glk);
+            dev.download(ba, got);
+            for (size_t i = 0; i < 3; i++)
+                same("device-resident batch of 3, element", want[i], got[i]);
+        }
         expect_throw("device-resident level mismatch", [&] { dev.add_inplace(da, db); }, 0);
         expect_throw("device-resident multiply of size 3", [&] {
             gsb_seal::DeviceCiphertext x, y;
