@@ -72,12 +72,10 @@ PROTOTYPES = {
     "gsb_dot_product_ct_sk_host": (i32, [vp, vp, vp, sz, sz, sz, i32]),
     "gsb_bfv_decrypt_dev": (i32, [vp, vp, u64, vp, vp, sz, sz, sz, vp]),
     "gsb_bfv_decrypt_host": (i32, [vp, u64, vp, vp, sz, sz, sz]),
-    "gsb_int_peak": (i32, [vp, i32, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double)]),
-    "gsb_int_peak_wide": (i32, [vp, i32, C.POINTER(C.c_double)]),
     "gsb_ctx_fast_ntt": (i32, [vp]),
 }
-# measurement aids that the test-only simulator build does not provide
-CUDA_ONLY = {"gsb_int_peak", "gsb_int_peak_wide"}
+# symbols that the test-only simulator build does not provide
+CUDA_ONLY = set()
 
 
 def bind(lib):

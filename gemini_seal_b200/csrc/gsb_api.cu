@@ -98,6 +98,7 @@ namespace gsb
         require(ctx != nullptr, GSB_E_INVALID_ARG, "ctx is null");
         require(n_limbs >= 1 && limb_offset + n_limbs <= ctx->K, GSB_E_INVALID_ARG, "limb range exceeds the key-level modulus");
         require(n_polys >= 1 && n_polys <= 65535 * 64, GSB_E_INVALID_ARG, "n_polys out of range");
+        GSB_CUDA_CHECK(cudaSetDevice(ctx->device)); // the calling thread's current device may be another GPU
     }
 } // namespace gsb
 
@@ -199,7 +200,14 @@ int gsb_ctx_create(int device, int logn, const uint64_t *moduli, size_t K, size_
         require(K >= 1 && K <= 64, GSB_E_INVALID_ARG, "coeff_modulus size out of range (1..64)");
         // encryptionparams.h:205-214 / context.cpp:524-530
         require(k_special >= 1 && (K == 1 || k_special < K), GSB_E_LOGIC, "n_special_primes must be in [1, #moduli)");
+        int prev_device = 0;
+        GSB_CUDA_CHECK(cudaGetDevice(&prev_device));
         GSB_CUDA_CHECK(cudaSetDevice(device));
+        struct Restore // the creating thread keeps its current device
+        {
+            int d;
+            ~Restore() { cudaSetDevice(d); }
+        } restore{ prev_device };
         std::unique_ptr<gsb_ctx> ctx(new gsb_ctx());
         ctx->device = device;
         ctx->logn = logn;
@@ -544,6 +552,3 @@ int gsb_ctx_fast_ntt(const gsb_ctx *ctx)
 } // extern "C"
 
 #include "gsb_evaluator.cuh"
-#ifndef GSB_CUSIM
-#include "int_peak.cuh"
-#endif

@@ -253,6 +253,9 @@ namespace gsb
 
     static KsDev make_ksdev(gsb_ctx *ctx, size_t L)
     {
+        // SEALContext::using_keyswitching() is false when every prime is special (context.cpp:461-464):
+        // the reference then refuses to key-switch (evaluator.cpp:2271-2274)
+        require(ctx->K > ctx->k, GSB_E_LOGIC, "keyswitching is not supported by the context");
         const KsLevelConsts &lc = ctx->consts_for(L);
         KsDev ks;
         ks.limb = ctx->d_limb;
@@ -598,9 +601,12 @@ namespace gsb
         }
     }
 
+    // Every *_dev entry point may be called from a thread whose current device is not the context's
+    // (e.g. a worker thread of a multi-GPU host): allocations, attribute calls and launches must go there.
     static void check_batch(const gsb_ctx *ctx, size_t batch, size_t L, size_t min_L)
     {
         require(ctx != nullptr, GSB_E_INVALID_ARG, "ctx is null");
+        GSB_CUDA_CHECK(cudaSetDevice(ctx->device));
         require(batch >= 1 && batch <= (size_t(1) << 20), GSB_E_INVALID_ARG, "batch out of range");
         require(L >= min_L && L <= ctx->L0, GSB_E_INVALID_ARG, "no ciphertext level with that many limbs");
     }
@@ -642,6 +648,7 @@ int gsb_key_upload(gsb_ctx *ctx, int kind, uint32_t galois_elt, const uint64_t *
     return guarded([&] {
         require(ctx != nullptr && key_host != nullptr, GSB_E_INVALID_ARG, "null argument");
         require(kind == GSB_KEY_RELIN || kind == GSB_KEY_GALOIS, GSB_E_INVALID_ARG, "key kind");
+        require(ctx->K > ctx->k, GSB_E_LOGIC, "keyswitching is not supported by the context");
         // keygenerator.cpp:333-343: one PublicKey per bundle of the first-level modulus
         const size_t beta0 = (ctx->L0 + ctx->k - 1) / ctx->k;
         require(n_bundles == beta0, GSB_E_INVALID_ARG, "kswitch_keys is not valid for encryption parameters");
@@ -945,6 +952,7 @@ static int host_call(
         require(ctx != nullptr, GSB_E_INVALID_ARG, "ctx is null");
         require(in0 != nullptr && out != nullptr && (in1 != nullptr || w1 == 0), GSB_E_INVALID_ARG, "null operand");
         require(batch >= 1 && batch <= (size_t(1) << 20), GSB_E_INVALID_ARG, "batch out of range");
+        require(w0 + w1 > 0 && wo > 0, GSB_E_INVALID_ARG, "no ciphertext level with that many limbs");
         std::lock_guard<std::mutex> lock(ctx->host_mu);
         GSB_CUDA_CHECK(cudaSetDevice(ctx->device));
         if (!ctx->pipe_ready)

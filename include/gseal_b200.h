@@ -18,6 +18,8 @@
  *     as each thread uses its own stream AND its own workspace (gsb_ws_*).  Calls that pass
  *     ws = NULL share the context's default workspace: they must all be enqueued on one stream
  *     (or be serialised by the caller); the *_host entry points take a per-context lock.
+ *   - every entry point makes the context's device the calling thread's current CUDA device (and leaves it
+ *     so); gsb_ctx_create restores the creating thread's previous device before it returns.
  *   - ciphertext and key words must be canonical residues (word < its limb's modulus), which is what
  *     the reference's is_buffer_valid (valcheck.cpp) demands before any Evaluator call; the shim and
  *     gsb_key_upload check it, the device entry points do not scan their inputs.  On such inputs
@@ -154,7 +156,8 @@ int gsb_switch_key_dev(
 int gsb_relinearize_dev(gsb_ctx *ctx, gsb_ws *ws, const uint64_t *in, uint64_t *out, size_t batch, size_t L, void *stream);
 
 /* Evaluator::rescale_to_next (evaluator.cpp:1090-1126,829-892; util/rns.cpp:777-851):
- * in = [batch][size][L][N] -> out = [batch][size][L-1][N]  (the caller divides `scale` by q_{L-1}). */
+ * in = [batch][size][L][N] -> out = [batch][size][L-1][N]  (the caller divides `scale` by q_{L-1}).
+ * out must not overlap in: the two-pass plans use `out` as the buffer between their passes. */
 int gsb_rescale_dev(gsb_ctx *ctx, gsb_ws *ws, const uint64_t *in, uint64_t *out, size_t batch, size_t size, size_t L, void *stream);
 
 /* Evaluator::apply_galois_inplace (evaluator.cpp:1841-1943; rotate_vector = elt from step,
@@ -218,14 +221,6 @@ int gsb_dot_product_ct_sk_host(gsb_ctx *ctx, const uint64_t *in, uint64_t *out, 
 int gsb_bfv_decrypt_dev(gsb_ctx *ctx, gsb_ws *ws, uint64_t plain_modulus, const uint64_t *in, uint64_t *out, size_t batch, size_t size, size_t L, void *stream);
 int gsb_bfv_decrypt_host(gsb_ctx *ctx, uint64_t plain_modulus, const uint64_t *in, uint64_t *out, size_t batch, size_t size, size_t L);
 
-/* ---- integer-pipe roofline (measurement aid, not part of the reference's interface) -------------
- * Register-resident microbenchmarks on ctx's device with `ctas_per_sm` x 256 threads per SM:
- * 32-bit IMAD/s, IMAD.WIDE.U32/s and forward lazy Harvey butterflies/s (the exact butterfly of the
- * NTT kernels, twiddles in registers, no memory traffic).  Any output pointer may be NULL. */
-int gsb_int_peak(gsb_ctx *ctx, int ctas_per_sm, double *imad_per_s, double *imad_wide_per_s, double *butterflies_per_s);
-/* The same butterfly microbenchmark for the wide-range butterfly (5 instead of 6 IMAD.WIDE) that the
- * library-internal transforms use when gsb_ctx_fast_ntt(ctx) is 1. */
-int gsb_int_peak_wide(gsb_ctx *ctx, int ctas_per_sm, double *wide_butterflies_per_s);
 /* 1 when the context's moduli satisfy q_max (5 log2 N + 2) < 2^63, i.e. the key-switch / rescale
  * internals run the wide-range butterflies (identical outputs); else 0. */
 int gsb_ctx_fast_ntt(const gsb_ctx *ctx);

@@ -190,3 +190,81 @@ def check_decrypt(lib, oracle, logn=11, to_device=None):
             bad[0, 0] = mods[0]
             g.Decryptor(ctx, bad)
         ctx.close()
+
+
+def threshold_primes(logn, k_special=1, L0=3):
+    """For each no-wrap flag of gsb_ctx_create (fast_ntt: q (5n+2) < 2^63; lazy_mac: beta0 (5n+2) q^2 < 2^128;
+    wide_inv: 10 q < 2^63) the largest NTT prime satisfying the bound and the smallest violating it."""
+    n = logn
+    step = 2 << logn
+    beta0 = (L0 + k_special - 1) // k_special
+
+    def around(bound):  # largest prime q = 1 mod 2N with q < bound, smallest with q >= bound
+        lo = (bound - 1) // step * step + 1
+        while lo >= bound or not is_prime(lo):
+            lo -= step
+        hi = (bound + step - 1) // step * step + 1
+        while hi < bound or not is_prime(hi):
+            hi += step
+        return lo, hi
+    import math
+    fast = -(-(1 << 63) // (5 * n + 2))
+    mac = math.isqrt((1 << 128) // (beta0 * (5 * n + 2))) + 1
+    inv = -(-(1 << 63) // 10)
+    return {"fast_ntt": around(fast), "lazy_mac": around(min(mac, fast)), "wide_inv": around(inv)}
+
+
+def check_threshold_and_patterns(lib, oracle, logn, literal_too=True, light=False):
+    """contexts whose largest modulus sits just below / just above each shortcut threshold, fed with
+    structured extreme inputs (all q-1, all 0, alternating 0 / q-1; keys full of q-1) next to random ones, through
+    multiply / relinearize / rescale / mul_relin_rescale / apply_galois against the oracle; the default build and a
+    GSB_LITERAL=1 context must both equal it."""
+    import os
+    import gemini_seal_b200 as g
+    N, k, L0 = 1 << logn, 1, 3
+    th = threshold_primes(logn, k, L0)
+    primes = sorted({q for pair in th.values() for q in pair})
+    small = ntt_primes(logn, 50, L0)
+    for qbig in primes:
+        # the big prime once as a ciphertext modulus and once as the special prime
+        for vi, mods in enumerate((small[:L0 - 1] + [qbig] + ntt_primes(logn, 51, 1), small + [qbig])):
+            L = L0
+            rng = np.random.default_rng(qbig % (1 << 31))
+            top = np.array([q - 1 for q in mods], dtype=np.uint64)
+            pats = []
+            full = np.broadcast_to(top[:L, None], (L, N))
+            alt = np.where((np.arange(N) & 1)[None, :] == 1, full, 0).astype(np.uint64)
+            for x in (full, np.zeros((L, N), dtype=np.uint64), alt):
+                pats.append(np.ascontiguousarray(np.stack([x, x[:, ::-1]])))
+            a = np.ascontiguousarray(np.stack(pats + [rand_poly(rng, mods[:L], (2,), N)]))
+            b = np.ascontiguousarray(np.stack([pats[0], pats[2], pats[0], rand_poly(rng, mods[:L], (2,), N)]))
+            key_max = np.ascontiguousarray(np.broadcast_to(top[None, None, :, None], (L0, 2, len(mods), N)))
+            for ki, key in enumerate((key_max, rand_key(rng, mods, L0, N))):
+                if light and ki != vi:  # the simulator run pairs each placement with one key kind
+                    continue
+                oc = oracle.context(logn, mods, k)
+                elt = oracle.elt_from_step(logn, 1)
+                want = None
+                for literal in ((False, True) if literal_too else (False,)):
+                    if literal:
+                        os.environ["GSB_LITERAL"] = "1"
+                    try:
+                        ctx = g.Context(N, mods, k, lib=lib)
+                    finally:
+                        os.environ.pop("GSB_LITERAL", None)
+                    ctx.set_relin_keys(key)
+                    ctx.set_galois_key(elt, key)
+                    ev = g.Evaluator(ctx)
+                    c3 = ev.multiply(a, b)
+                    got = [c3, ev.relinearize(c3), ev.rescale_to_next(c3), ev.mul_relin_rescale(a, b), ev.apply_galois(a, elt),
+                           g.ntt_negacyclic_harvey(g.inverse_ntt_negacyclic_harvey(a.copy(), ctx), ctx)]
+                    ctx.close()
+                    if want is None:
+                        want = [np.stack([oc.multiply(a[i], b[i]) for i in range(4)])]
+                        want.append(np.stack([oc.relinearize(want[0][i], key) for i in range(4)]))
+                        want.append(np.stack([oc.rescale(want[0][i]) for i in range(4)]))
+                        want.append(np.stack([oc.mul_relin_rescale(a[i], b[i], key) for i in range(4)]))
+                        want.append(np.stack([oc.apply_galois(a[i], elt, key) for i in range(4)]))
+                        want.append(oracle.ntt_rns(logn, mods, oracle.ntt_rns(logn, mods, a, 3), 1))
+                    for i, (x, y) in enumerate(zip(got, want)):
+                        assert np.array_equal(x, y), (logn, qbig, literal, i)

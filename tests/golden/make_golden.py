@@ -1,4 +1,5 @@
-"""Regenerates tests/golden/evaluator_digests.json by running the UNMODIFIED reference
+"""Regenerates tests/golden/evaluator_digests.json and batch64_digests.json (per-ciphertext digests of the
+batch-64 C3 / C4 cases) by running the UNMODIFIED reference
 (oracle/_ref/libref_harness.so, compiled from /root/reference by oracle/Makefile) on the seeded
 cases of tests/golden_cases.py.  Run in the build container only:
 
@@ -32,6 +33,13 @@ def main():
         "cases": cases,
     }
     with open(os.path.join(HERE, "evaluator_digests.json"), "w") as f:
+        json.dump(out, f, indent=1, sort_keys=True)
+    b64 = {}
+    for name in golden_cases.EVAL_B64:
+        b64[name] = golden_cases.run_case_per_ct(name, be)
+        print(name, "ok", flush=True)
+    out["cases"] = b64
+    with open(os.path.join(HERE, "batch64_digests.json"), "w") as f:
         json.dump(out, f, indent=1, sort_keys=True)
 
 

@@ -39,6 +39,13 @@ EVAL = {
     "n65536_k2_L3": (16, [50, 50, 50, 51, 51], 2, 3, 1, -1),
     "n16384_k3_L5_ragged": (14, BFV_DEFAULT[16384], 3, 5, 1, 5),
 }
+# Batch-64 cases ("every config and batch element"): per-ciphertext digests of multiply / relinearize /
+# rescale / mul_relin_rescale / rotate live in tests/golden/batch64_digests.json.  Too slow for the CPU oracle as a
+# whole (the CPU suite pins two ciphertexts of each), so they are kept out of EVAL.
+EVAL_B64 = {
+    "c3_n16384_default_b64": (14, BFV_DEFAULT[16384], 1, 8, 64, 1),
+    "c4_n32768_default_b64": (15, BFV_DEFAULT[32768], 1, 15, 64, 1),
+}
 # BFV branches (BASELINE config #1 = the first one): coefficient-form ciphertexts.
 # name -> (logn, moduli spec, k special, level L, batch, rotation step, plain modulus)
 BFV = {
@@ -65,7 +72,7 @@ def case_seed(name):
 
 
 def eval_inputs(name):
-    logn, spec, k, L, batch, step = EVAL[name]
+    logn, spec, k, L, batch, step = EVAL[name] if name in EVAL else EVAL_B64[name]
     N = 1 << logn
     mods = list(spec) if spec[0] > 64 else mixed_moduli(logn, spec)
     rng = np.random.default_rng(case_seed(name))
@@ -135,6 +142,23 @@ def run_case(name, be):
     out["decrypt"] = digest(be.decrypt(c["a"], c["sk"]))            # Decryptor::ckks_decrypt, size 2
     out["decrypt3"] = digest(be.decrypt(c3, c["sk"]))               # size 3: uses s^2
     return out
+
+
+def run_case_per_ct(name, be, only=None):
+    """Per-ciphertext digests of a batch case: {op: [sha256 of ciphertext i's output limbs]}.  `only` restricts the
+    batch to the given ciphertext indices (inputs are still drawn for the whole batch, so indices keep their words)."""
+    c = eval_inputs(name)
+    be.setup(c["logn"], c["mods"], c["k"])
+    elt = be.elt_from_step(c["logn"], c["step"])
+    be.set_keys(c["relin"], elt, c["galois"])
+    a, b = c["a"], c["b"]
+    if only is not None:
+        a, b = np.ascontiguousarray(a[list(only)]), np.ascontiguousarray(b[list(only)])
+    c3 = be.multiply(a, b)
+    c2 = be.relinearize(c3)
+    res = {"multiply": c3, "relinearize": c2, "rescale": be.rescale(c2), "mul_relin_rescale": be.mul_relin_rescale(a, b),
+           "rotate": be.apply_galois(a, elt)}
+    return {op: [digest(x[i]) for i in range(x.shape[0])] for op, x in res.items()}
 
 
 class _PerCt:

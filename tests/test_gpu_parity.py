@@ -24,6 +24,48 @@ def test_matches_reference_digests(cudalib, name):
     assert got == GOLDEN[name]
 
 
+with open(os.path.join(os.path.dirname(__file__), "golden", "batch64_digests.json")) as f:
+    GOLDEN_B64 = json.load(f)["cases"]
+
+
+@pytest.mark.parametrize("name", list(golden_cases.EVAL_B64))
+def test_batch64_matches_reference_digests(cudalib, name):
+    """SURVEY 8(d) parity gate "for every config and batch element": the C3 and C4 workloads at batch 64, every
+    ciphertext of every operation against the digest the unmodified reference produced for it."""
+    got = golden_cases.run_case_per_ct(name, golden_cases.DeviceBackend(cudalib))
+    want = GOLDEN_B64[name]
+    for op in want:
+        bad = [i for i, (x, y) in enumerate(zip(got[op], want[op])) if x != y]
+        assert not bad and len(got[op]) == len(want[op]) == 64, (name, op, bad)
+
+
+@pytest.mark.parametrize("logn", [12, 13, 14, 15, 16])
+@pytest.mark.parametrize("n_limbs", [1, 16, 48])
+def test_ntt_grid_vs_oracle(cudalib, oracle, logn, n_limbs):
+    """BASELINE config #2, the whole grid: N = 2^12..2^16 x {1, 16, 48} limbs of 59-bit primes (48 limbs also on the
+    two-pass plans), lazy + strict, forward + inverse, device buffers and host buffers, against the oracle."""
+    import torch
+    import gemini_seal_b200 as g
+    mods = ntt_primes(logn, 59, n_limbs)
+    ctx = g.Context(1 << logn, mods + ntt_primes(logn, 58, 1), 1, lib=cudalib)
+    rng = np.random.default_rng(logn * 100 + n_limbs)
+    x = rand_poly(rng, mods, (2,), 1 << logn)
+    fns = [g.ntt_negacyclic_harvey_lazy, g.ntt_negacyclic_harvey, g.inverse_ntt_negacyclic_harvey_lazy,
+           g.inverse_ntt_negacyclic_harvey]
+    for kind, fn in enumerate(fns):
+        want = oracle.ntt_rns(logn, mods, x, kind)
+        assert np.array_equal(fn(x.copy(), ctx), want), (logn, n_limbs, kind, "host")
+        d = torch.from_numpy(x.view(np.int64)).cuda()
+        assert np.array_equal(fn(d, ctx).cpu().numpy().view(np.uint64), want), (logn, n_limbs, kind, "device")
+    ctx.close()
+
+
+@pytest.mark.parametrize("logn", [12, 13, 15])
+def test_threshold_primes_and_extreme_patterns(cudalib, oracle, logn):
+    from common import check_threshold_and_patterns
+    check_threshold_and_patterns(cudalib, oracle, logn)
+
+
 @pytest.mark.parametrize("name", ["n2048_k2_L4", "n8192_k2_L3", "c3_n16384_default"])
 def test_matches_oracle_arrays(cudalib, oracle, name):
     """Array-level comparison with the oracle (locates a mismatch, unlike a digest)."""

@@ -233,3 +233,34 @@ def test_golden_digests(oracle):
     for name, want in golden["cases"].items():
         got = golden_cases.run_case(name, golden_cases.OracleBackend(oracle))
         assert got == want, name
+
+
+def test_batch64_digests_sample(oracle):
+    """Two ciphertexts of the batch-64 C3 case (the GPU suite checks all 64 of C3 and C4) through the oracle."""
+    import golden_cases
+    with open(os.path.join(os.path.dirname(__file__), "golden", "batch64_digests.json")) as f:
+        want = json.load(f)["cases"]["c3_n16384_default_b64"]
+    got = golden_cases.run_case_per_ct("c3_n16384_default_b64", golden_cases.OracleBackend(oracle), only=(0, 63))
+    for op, d in got.items():
+        assert d == [want[op][0], want[op][63]], op
+
+
+def test_bench_digests_and_synth(oracle):
+    """bench.py's parity-gate inputs: the splitmix residues are the same words from numpy and from torch's int64
+    arithmetic, and the committed reference digest of C3 ciphertext 255 is what the oracle computes."""
+    import torch
+    import bench
+    import synth
+    mods = [36028797017456641, 72057594037338113, 65537]
+    a = synth.residues_numpy(99, 3, 5, 2, mods, 1024)
+    b = synth.residues_torch(torch, 99, 3, 5, 2, mods, 1024, device="cpu", chunk=2).numpy().view(np.uint64)
+    assert np.array_equal(a, b)
+    assert np.array_equal(synth.residues_numpy(99, 5, 1, 2, mods, 1024)[0], a[2])  # a ciphertext does not depend on its batch
+    w = bench.workload("c3")
+    keys = bench.synthetic_keys(w)
+    oc = oracle.context(w.logn, w.mods, w.k)
+    ca = synth.residues_numpy(bench.SEED_A, 255, 1, 2, w.mods[:w.L], w.N)[0]
+    cb = synth.residues_numpy(bench.SEED_B, 255, 1, 2, w.mods[:w.L], w.N)[0]
+    want = bench.load_digests()["c3"]
+    assert bench.digest(oc.mul_relin_rescale(ca, cb, keys[0])) == want["mrr"]["255"]
+    assert bench.digest(oc.apply_galois(ca, oracle.elt_from_step(w.logn, 1), keys[1])) == want["rot"]["255"]

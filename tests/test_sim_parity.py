@@ -71,3 +71,10 @@ def test_sim_fast_flag_and_literal_mode(simlib, oracle):
         outs.append(g.Evaluator(ctx).mul_relin_rescale(a, b))
         ctx.close()
     assert np.array_equal(outs[0], outs[1])
+
+
+def test_sim_threshold_primes_and_extreme_patterns(simlib, oracle):
+    """Shortcut thresholds and structured extreme inputs under the simulator, whose GSB_SIM_ASSERTs also check every
+    no-wrap precondition on these inputs (the GPU suite repeats it at N = 2^12, 2^13, 2^15)."""
+    from common import check_threshold_and_patterns
+    check_threshold_and_patterns(simlib, oracle, 10, light=True)
