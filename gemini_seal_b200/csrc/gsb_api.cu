@@ -261,6 +261,8 @@ int gsb_ctx_create(int device, int logn, const uint64_t *moduli, size_t K, size_
             // kernels carry the reference's own intermediate words.  tests/test_gpu_parity.py runs the full
             // size both ways and requires identical outputs.
             ctx->wide_inv = static_cast<u128>(qmax) * 10 < (static_cast<u128>(1) << 63);
+            const char *split = std::getenv("GSB_SPLIT_TAIL");
+            ctx->split_tail = split && split[0] == '1';
             const char *lit = std::getenv("GSB_LITERAL");
             if (lit && lit[0] == '1')
             {
@@ -293,6 +295,7 @@ void gsb_ctx_destroy(gsb_ctx *ctx)
         cudaFree(kv.second.d_inv_hat);
         cudaFree(kv.second.d_neg_hat);
         cudaFree(kv.second.d_inv_p);
+        cudaFree(kv.second.d_neg_p);
         cudaFree(kv.second.d_inv_qlast);
         cudaFree(kv.second.d_neg_half);
     }

@@ -49,6 +49,7 @@ namespace gsb
         uint64_t *d_inv_hat = nullptr;  // [k][2]  (prod_{j'!=j} p_j')^-1 mod p_j (+ Shoup)
         uint64_t *d_neg_hat = nullptr;  // [L][k]  -(prod_{j'!=j} p_j') mod q_i
         uint64_t *d_inv_p = nullptr;    // [L][2]  (prod_j p_j)^-1 mod q_i (+ Shoup)
+        uint64_t *d_neg_p = nullptr;    // [L][2]  -(prod_j p_j) mod q_i (+ Shoup): fused mul+relin+rescale tail
         // rescale (util/rns.cpp:719-728, 824): q_last^-1 mod q_i ; q_i - (half mod q_i)
         uint64_t *d_inv_qlast = nullptr; // [L-1][2] (+ Shoup)
         uint64_t *d_neg_half = nullptr;  // [L-1]
@@ -100,6 +101,9 @@ struct gsb_ctx
     //                                                  no growth, so it also holds for 59-bit moduli)
     bool wide_inv = false;
     bool lazy_modup = false, lazy_mac = false;
+    // testing aid (GSB_SPLIT_TAIL=1 at context creation): gsb_mul_relin_rescale_* runs mod-down and rescale as
+    // the separate passes of the stand-alone entry points instead of the fused tail (identical outputs)
+    bool split_tail = false;
     std::vector<gsb::host::LimbTables> tables; // host copies (introspection + constants)
     gsb::Twiddle *d_WW = nullptr, *d_VV = nullptr;
     gsb::LimbC *d_limb = nullptr;

@@ -68,7 +68,7 @@ const gsb::KsLevelConsts &gsb_ctx::consts_for(size_t L)
         }
     }
     // mod-down constants (multi_special_primes.cpp:186-234, 292-299)
-    std::vector<uint64_t> inv_hat(k * 2, 0), neg_hat(L * k, 0), inv_p(L * 2, 0);
+    std::vector<uint64_t> inv_hat(k * 2, 0), neg_hat(L * k, 0), inv_p(L * 2, 0), neg_p(L * 2, 0);
     for (size_t j = 0; j < k; j++)
     {
         const host::ModConst &pj = modc(L0 + j);
@@ -98,6 +98,8 @@ const gsb::KsLevelConsts &gsb_ctx::consts_for(size_t L)
         require(host::inv_mod(P, qi.q, inv), GSB_E_LOGIC, "moddown: inv_mod fail");
         inv_p[2 * i] = inv;
         inv_p[2 * i + 1] = host::shoup(inv, qi.q);
+        neg_p[2 * i] = P ? qi.q - P : 0;
+        neg_p[2 * i + 1] = host::shoup(neg_p[2 * i], qi.q);
     }
     // rescale constants (util/rns.cpp:719-728, 824)
     std::vector<uint64_t> inv_qlast, neg_half;
@@ -120,6 +122,7 @@ const gsb::KsLevelConsts &gsb_ctx::consts_for(size_t L)
     c.d_inv_hat = upload_words(inv_hat);
     c.d_neg_hat = upload_words(neg_hat);
     c.d_inv_p = upload_words(inv_p);
+    c.d_neg_p = upload_words(neg_p);
     c.d_inv_qlast = upload_words(inv_qlast);
     c.d_neg_half = upload_words(neg_half);
     return level_consts.emplace(L, c).first->second;
@@ -295,11 +298,13 @@ namespace gsb
     };
 
     // switch_key_inplace for `B` ciphertexts (evaluator.cpp:2259-2368).  scratch must hold
-    // B * ks_words_per_ct words (+ alignment slack).
+    // B * ks_words_per_ct words (+ alignment slack).  front_only: stop after step 3 + the Barrett part of
+    // step 4 (red = the reduced inner product of every ext slot, NTT form) and return `red`; the fused
+    // mul+relin+rescale tail continues from there.
     template <int LOGN, bool K1>
-    static void switch_key_core_t(
+    static uint64_t *switch_key_core_t(
         gsb_ctx *ctx, void *scratch, const uint64_t *target, size_t target_stride, const SwitchKey &key, const KsOutput &o,
-        size_t B, size_t L, cudaStream_t st)
+        size_t B, size_t L, cudaStream_t st, bool front_only = false)
     {
         constexpr bool two = Split<LOGN>::two_pass;
         const size_t N = ctx->N;
@@ -352,6 +357,8 @@ namespace gsb
             else
                 launch(ks_mac_kernel<LOGN, K1, false>);
         }
+        if (front_only)
+            return red;
         // Step 4 (:2353-2357): lazy inverse NTT of the special slots.
         ntt_inverse_plain<LOGN>(
             tab, ModMap{ 0, static_cast<int>(ctx->L0), 0 }, red + L * N, E * N, red + L * N, E * N, static_cast<int>(k),
@@ -401,6 +408,7 @@ namespace gsb
             else
                 launch_fwd_contig<LOGN>(io, tab, mm, iL, static_cast<int>(2 * B), st, "moddown");
         }
+        return red;
     }
 
     template <int LOGN>
@@ -412,6 +420,60 @@ namespace gsb
             switch_key_core_t<LOGN, true>(ctx, scratch, target, target_stride, key, o, B, L, st);
         else
             switch_key_core_t<LOGN, false>(ctx, scratch, target, target_stride, key, o, B, L, st);
+    }
+
+    // Fused tail of multiply + relinearize + rescale (see TailInvLoad in gsb_ks_kernels.cuh): from the
+    // reduced inner product `red` and the tensor product `c3` = [B][3][L][N] straight to the rescaled
+    // ciphertext out = [B][2][L-1][N].  Only for k = 1 contexts under gsb_ctx::fast_ntt / wide_inv, L >= 2.
+    // buf = B*2*2*N words of scratch.
+    template <int LOGN>
+    static void mrr_tail_core(gsb_ctx *ctx, uint64_t *buf, const uint64_t *red, const uint64_t *c3, uint64_t *out, size_t B, size_t L, cudaStream_t st)
+    {
+        constexpr bool two = Split<LOGN>::two_pass;
+        const size_t N = ctx->N, LN = L * N;
+        const KsDev ks = make_ksdev(ctx, L);
+        const KsLevelConsts &lc = ctx->consts_for(L);
+        const NttTables tab = ctx->ntt_tables();
+        const int nz = static_cast<int>(2 * B), iL = static_cast<int>(L);
+        // inverse transforms of (u_{L-1} P^-1 + c3_{L-1}) and of the special slot
+        const ModMap mlast{ iL, static_cast<int>(ctx->L0), iL - 1 };
+        const TailInvArgs ia{ ks, red, c3, 3 * LN, LN };
+        IoPair<TailInvLoad, PlainStore<OUT_RAW>> io_inv{ ia, PlainStoreArgs{ buf, 2 * N } };
+        launch_inv_contig<LOGN, true>(io_inv, tab, mlast, 2, nz, st, "tail_last");
+        if constexpr (two)
+            launch_inv_cols<LOGN, true>(IoPlain<OUT_RAW>{ buf, buf, 2 * N, 2 * N }, tab, mlast, 2, nz, st, "tail_last");
+        // t and t1 per coefficient
+        {
+            const host::LimbTables &tl = ctx->tables[L - 1], &tp = ctx->tables[ctx->L0];
+            TailMidArgs a{};
+            a.buf = buf;
+            a.last.q = tl.mod.q;
+            a.last.two_q = tl.mod.q << 1;
+            a.last.cr1 = tl.mod.cr1;
+            a.sp.q = tp.mod.q;
+            a.sp.two_q = tp.mod.q << 1;
+            uint64_t P = tp.mod.q % tl.mod.q, inv = 0;
+            require(host::inv_mod(P, tl.mod.q, inv), GSB_E_LOGIC, "moddown: inv_mod fail");
+            a.ip = inv;
+            a.ips = host::shoup(inv, tl.mod.q);
+            a.N = static_cast<uint32_t>(N);
+            a.total = 2 * B * N;
+            GSB_LAUNCH("tail_mid", "", tail_mid_kernel, dim3(grid_for(a.total, 256)), dim3(256), 0, st, a);
+        }
+        // one forward transform per remaining limb; `out` doubles as the buffer between the two passes
+        const ModMap mm{ 1 << 30, 0, 0 };
+        const int ny = iL - 1;
+        const TailLoadArgs la{ buf, lc.d_neg_half, lc.d_neg_p };
+        const TailStoreArgs sa{ ks, red, c3, 3 * LN, LN, out, lc.d_inv_qlast };
+        if constexpr (two)
+        {
+            IoPair<TailLoad, PlainStore<OUT_RAW>> io1{ la, PlainStoreArgs{ out, (L - 1) * N } };
+            IoPair<PlainLoad, TailStore> io2{ PlainArgs{ out, (L - 1) * N }, sa };
+            launch_fwd_cols<LOGN, true>(io1, tab, mm, ny, nz, st, "tail");
+            launch_fwd_contig<LOGN, true>(io2, tab, mm, ny, nz, st, "tail");
+        }
+        else
+            launch_fwd_contig<LOGN, true>(IoPair<TailLoad, TailStore>{ la, sa }, tab, mm, ny, nz, st, "tail");
     }
 
     // rescale for n_polys polynomials of L limbs (util/rns.cpp:777-851). t = n_polys*N words scratch.
@@ -922,14 +984,26 @@ int gsb_mul_relin_rescale_dev(
         gsb_ws *w = pick_ws(ctx, ws);
         cudaStream_t st = static_cast<cudaStream_t>(stream);
         const size_t N = ctx->N, LN = L * N;
-        const size_t per = ks_words_per_ct(ctx, L) + 3 * LN + 2 * LN + 2 * N, chunk = chunk_for(per, batch);
+        // one forward transform per limb for mod-down + rescale together (identical words, see mrr_tail_core)
+        const bool fused_tail = ctx->k == 1 && ctx->fast_ntt && ctx->wide_inv && !ctx->split_tail;
+        const size_t per = ks_words_per_ct(ctx, L) + 3 * LN + (fused_tail ? 4 * N : 2 * LN + 2 * N), chunk = chunk_for(per, batch);
         void *scratch = w->reserve((chunk * per + 2048) * sizeof(uint64_t));
         for (size_t b0 = 0; b0 < batch; b0 += chunk)
         {
             const size_t B = std::min(chunk, batch - b0);
             Arena ar(scratch);
-            uint64_t *c3 = ar.words(B * 3 * LN), *c2 = ar.words(B * 2 * LN), *t = ar.words(B * 2 * N);
+            uint64_t *c3 = ar.words(B * 3 * LN);
             ckks_multiply_core(ctx, a + b0 * 2 * LN, b + b0 * 2 * LN, c3, B, L, st);
+            if (fused_tail)
+            {
+                uint64_t *buf = ar.words(B * 4 * N);
+                const KsOutput o{ c3, 3 * LN, LN, nullptr, 0, 0, nullptr };
+                uint64_t *red = nullptr;
+                GSB_DISPATCH_LOGN(ctx->logn, red = (switch_key_core_t<LOGN, true>(ctx, ar.base + ar.off, c3 + 2 * LN, 3 * LN, key, o, B, L, st, true)));
+                GSB_DISPATCH_LOGN(ctx->logn, mrr_tail_core<LOGN>(ctx, buf, red, c3, out + b0 * 2 * (L - 1) * N, B, L, st));
+                continue;
+            }
+            uint64_t *c2 = ar.words(B * 2 * LN), *t = ar.words(B * 2 * N);
             const KsOutput o{ c3, 3 * LN, LN, c2, 2 * LN, LN, nullptr };
             GSB_DISPATCH_LOGN(ctx->logn, switch_key_core<LOGN>(ctx, ar.base + ar.off, c3 + 2 * LN, 3 * LN, key, o, B, L, st));
             GSB_DISPATCH_LOGN(ctx->logn, rescale_core<LOGN>(ctx, t, c2, out + b0 * 2 * (L - 1) * N, B * 2, L, st));

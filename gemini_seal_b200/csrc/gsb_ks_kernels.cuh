@@ -389,6 +389,167 @@ namespace gsb
         }
     };
 
+    // ---- fused tail of multiply + relinearize + rescale (k = 1 contexts under gsb_ctx::fast_ntt) --------
+    // gsb_mul_relin_rescale_* only hands out the rescaled ciphertext, so the mod-down of the key switch
+    // (multi_special_primes.cpp:237-304), the final add (evaluator.cpp:2363-2366) and the rescale
+    // (util/rns.cpp:777-851) are evaluated as ONE forward transform per remaining limb instead of two.
+    // With c_p = [c]_p (special slot, coefficient form), t1 = -c_p in [0,p), P = p mod q_i, u = red_i
+    // (reduced inner product, NTT form) and c3 = the tensor product's component (the key switch's addend),
+    // the reference computes, all mod q_i,
+    //     dst_i = (u_i + NTT_i(t1)) P^-1 + c3_i                                  (mod-down + add)
+    //     t     = barrett63(strict_iNTT(dst_{L-1}) + q_{L-1}/2)                  (rescale, last limb)
+    //     out_i = (dst_i - NTT_i(t + (q_i - half))) q_{L-1}^-1                   (rescale, limb i < L-1)
+    // and canonicalises out_i.  The NTT is linear mod q_i, hence
+    //     strict_iNTT(dst_{L-1}) = canon( iNTT(u_{L-1} P^-1 + c3_{L-1}) + P^-1 t1 )
+    //     out_i = canon( ((u_i + NTT_i(t1 - P (t + q_i - half))) P^-1 + c3_i) q_{L-1}^-1 ):
+    // the same canonical words from 2 inverse + (L-1) forward transforms per polynomial instead of
+    // 2 inverse + (2L-1) forward ones.  Every intermediate word is congruent to the reference's and inside
+    // the ranges the wide-range transforms accept (inverse input < 2q, forward input < 2 q_max).
+    //
+    // Inverse transforms, grid y in {0, 1}, z = b*2 + l: y = 0 is limb L-1 with the prologue
+    // u P^-1 + c3 (< 2q), y = 1 is the special slot as it is.  ModMap{L, L0, L-1} maps them to their moduli.
+    struct TailInvArgs
+    {
+        KsDev ks;
+        const uint64_t *red; // [B*2][E][N]
+        const uint64_t *c3;  // tensor product, ciphertext b at c3 + b*c3_bs, component l at + l*c3_ls
+        size_t c3_bs, c3_ls;
+        GSB_DEV bool skip(int, int) const { return false; }
+    };
+    struct TailInvLoad
+    {
+        typedef TailInvArgs Args;
+        const uint64_t *r, *c;
+        uint64_t q, ip, ips;
+        bool last;
+        GSB_DEV TailInvLoad(const Args &a, int y, int z, int, const LimbC &lc, uint32_t N)
+        {
+            const int b = z >> 1, l = z & 1, L = static_cast<int>(a.ks.L);
+            last = y == 0;
+            r = a.red + (static_cast<size_t>(z) * a.ks.E + (L - 1 + y)) * N;
+            c = a.c3 + static_cast<size_t>(b) * a.c3_bs + static_cast<size_t>(l) * a.c3_ls + static_cast<size_t>(L - 1) * N;
+            q = lc.q;
+            ip = a.ks.inv_p[2 * (L - 1)];
+            ips = a.ks.inv_p[2 * (L - 1) + 1];
+        }
+        GSB_DEV uint64_t raw(uint32_t d) const { return last ? mulmod_shoup(r[d], ip, ips, q) + c[d] : r[d]; }
+        GSB_DEV void raw2(uint32_t d, uint64_t &x, uint64_t &y) const
+        {
+            const ulonglong2 v = *reinterpret_cast<const ulonglong2 *>(r + d);
+            x = v.x;
+            y = v.y;
+            if (last)
+            {
+                const ulonglong2 w = *reinterpret_cast<const ulonglong2 *>(c + d);
+                x = mulmod_shoup(x, ip, ips, q) + w.x;
+                y = mulmod_shoup(y, ip, ips, q) + w.y;
+            }
+        }
+        GSB_DEV uint64_t xform(uint64_t v) const { return v; }
+    };
+
+    // Between the inverse and the forward transforms: buf = [B*2][2][N] holds, per polynomial, the lazy
+    // inverse transforms u' = iNTT(u_{L-1} P^-1 + c3_{L-1}) in [0,2q) and s = iNTT(special slot) in [0,2p);
+    // they are replaced in place by t (rescale's rounded last limb, canonical mod q_{L-1}) and t1 = -[c]_p.
+    struct TailMidArgs
+    {
+        uint64_t *buf;
+        LimbC last, sp;
+        uint64_t ip, ips; // P^-1 mod q_{L-1} with its Shoup scaling
+        uint32_t N;
+        size_t total; // B*2*N
+    };
+    __global__ void __launch_bounds__(256) tail_mid_kernel(TailMidArgs a)
+    {
+        for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < a.total;
+             i += static_cast<size_t>(gridDim.x) * blockDim.x)
+        {
+            const size_t z = i / a.N, d = i - z * a.N;
+            uint64_t *pu = a.buf + (z * 2) * a.N + d, *ps = pu + a.N;
+            const uint64_t s = *ps;
+            GSB_SIM_ASSERT(s < a.sp.two_q && *pu < a.last.two_q);
+            const uint64_t t1 = neg_mod(s - (s >= a.sp.q ? a.sp.q : 0), a.sp.q); // :268-275, -[c]_p in [0,p)
+            uint64_t y = *pu + mulmod_shoup(t1, a.ip, a.ips, a.last.q);             // < 3q
+            y -= (y >= a.last.two_q) ? a.last.two_q : 0;
+            y -= (y >= a.last.q) ? a.last.q : 0;                                    // = strict_iNTT(dst_{L-1})
+            *pu = barrett63(y + (a.last.q >> 1), a.last.q, a.last.cr1);             // util/rns.cpp:798-806
+            *ps = t1;
+        }
+    }
+
+    // Forward transforms, grid y = limb i < L-1, z = b*2 + l.  Prologue: t1 + (t + (q_i - half)) (-P) mod q_i
+    // (< p + q_i <= 2 q_max, the input range of a wide-range transform).
+    struct TailLoadArgs
+    {
+        const uint64_t *buf;      // [B*2][2][N]: t, t1
+        const uint64_t *neg_half; // [L-1]
+        const uint64_t *neg_p;    // [L][2]: -p mod q_i with its Shoup scaling
+        GSB_DEV bool skip(int, int) const { return false; }
+    };
+    struct TailLoad
+    {
+        typedef TailLoadArgs Args;
+        const uint64_t *t, *t1;
+        uint64_t q, nh, np, nps;
+        GSB_DEV TailLoad(const Args &a, int y, int z, int, const LimbC &lc, uint32_t N)
+            : t(a.buf + static_cast<size_t>(z) * 2 * N), t1(t + N), q(lc.q), nh(a.neg_half[y]), np(a.neg_p[2 * y]), nps(a.neg_p[2 * y + 1])
+        {}
+        GSB_DEV uint64_t one(uint64_t tv, uint64_t t1v) const { return t1v + mulmod_shoup(tv + nh, np, nps, q); }
+        GSB_DEV uint64_t raw(uint32_t d) const { return one(t[d], t1[d]); }
+        GSB_DEV void raw2(uint32_t d, uint64_t &x, uint64_t &y) const
+        {
+            const ulonglong2 a = *reinterpret_cast<const ulonglong2 *>(t + d), b = *reinterpret_cast<const ulonglong2 *>(t1 + d);
+            x = one(a.x, b.x);
+            y = one(a.y, b.y);
+        }
+        GSB_DEV uint64_t xform(uint64_t v) const { return v; }
+    };
+
+    // Epilogue: out_i = MulModShoup(MulModShoup(u_i + ntt; P^-1) + c3_i; q_{L-1}^-1), canonical.
+    struct TailStoreArgs
+    {
+        KsDev ks;
+        const uint64_t *red;
+        const uint64_t *c3;
+        size_t c3_bs, c3_ls;
+        uint64_t *out;             // [B][2][L-1][N]
+        const uint64_t *inv_qlast; // [L-1][2]
+    };
+    struct TailStore
+    {
+        typedef TailStoreArgs Args;
+        const uint64_t *r, *c;
+        uint64_t *o;
+        uint64_t q, ip, ips, iq, iqs;
+        GSB_DEV TailStore(const Args &a, int y, int z, int, const LimbC &lc, uint32_t N)
+        {
+            const int b = z >> 1, l = z & 1;
+            r = a.red + (static_cast<size_t>(z) * a.ks.E + y) * N;
+            c = a.c3 + static_cast<size_t>(b) * a.c3_bs + static_cast<size_t>(l) * a.c3_ls + static_cast<size_t>(y) * N;
+            o = a.out + (static_cast<size_t>(z) * (a.ks.L - 1) + y) * N;
+            q = lc.q;
+            ip = a.ks.inv_p[2 * y];
+            ips = a.ks.inv_p[2 * y + 1];
+            iq = a.inv_qlast[2 * y];
+            iqs = a.inv_qlast[2 * y + 1];
+        }
+        GSB_DEV void prefetch(uint32_t d) const
+        {
+            prefetch_l2(r + d);
+            prefetch_l2(c + d);
+        }
+        GSB_DEV uint64_t one(uint64_t u, uint64_t c3v, uint64_t v) const
+        {
+            return mulmod_shoup(mulmod_shoup(u + v, ip, ips, q) + c3v, iq, iqs, q);
+        }
+        GSB_DEV void store(uint32_t d, uint64_t v, int) const { o[d] = one(r[d], c[d], v); }
+        GSB_DEV void store2(uint32_t d, uint64_t a, uint64_t b, int) const
+        {
+            const ulonglong2 u = *reinterpret_cast<const ulonglong2 *>(r + d), w = *reinterpret_cast<const ulonglong2 *>(c + d);
+            *reinterpret_cast<ulonglong2 *>(o + d) = make_ulonglong2(one(u.x, w.x, a), one(u.y, w.y, b));
+        }
+    };
+
     // ---- epilogue that leaves the transform in registers (used by the fused inner product) --------
     struct KeepInRegs
     {
