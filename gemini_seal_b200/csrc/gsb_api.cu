@@ -555,3 +555,4 @@ int gsb_ctx_fast_ntt(const gsb_ctx *ctx)
 } // extern "C"
 
 #include "gsb_evaluator.cuh"
+#include "gsb_noalloc.cuh"

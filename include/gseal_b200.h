@@ -221,6 +221,20 @@ int gsb_dot_product_ct_sk_host(gsb_ctx *ctx, const uint64_t *in, uint64_t *out, 
 int gsb_bfv_decrypt_dev(gsb_ctx *ctx, gsb_ws *ws, uint64_t plain_modulus, const uint64_t *in, uint64_t *out, size_t batch, size_t size, size_t L, void *stream);
 int gsb_bfv_decrypt_host(gsb_ctx *ctx, uint64_t plain_modulus, const uint64_t *in, uint64_t *out, size_t batch, size_t size, size_t L);
 
+/* ---- allocation-free rescale ---------------------------------------------------------------------
+ * No counterpart in the reference: added for callers that cannot
+ * call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same operation and same output words as gsb_rescale_dev: in = [batch][size][L][N] -> out =
+ * [batch][size][L-1][N], out must not overlap in.  Its scratch (the rounded last limb and the level's
+ * constants) lives in a file-scope static device array inside the library -- 4 MiB + 2 KiB that every GPU
+ * which loads the library holds until the process exits -- so the call issues no cudaMalloc, cudaFree or
+ * memcpy: kernels only.  Limit: batch * size * N <= 524288 words (e.g. 8 size-2 ciphertexts at N = 32768,
+ * 64 at N = 4096); larger calls fail with GSB_E_RANGE and a message naming the limit.  Every call on a
+ * device shares that array and it keeps the last call's contents; nothing needs to start at zero (each call
+ * writes every word it later reads), but calls that overlap on the GPU -- different streams, or host
+ * threads without a common stream -- race: serialise them on one stream. */
+int gsb_rescale_noalloc_dev(gsb_ctx *ctx, const uint64_t *in, uint64_t *out, size_t batch, size_t size, size_t L, void *stream);
+
 /* 1 when the context's moduli satisfy q_max (5 log2 N + 2) < 2^63, i.e. the key-switch / rescale
  * internals run the wide-range butterflies (identical outputs); else 0. */
 int gsb_ctx_fast_ntt(const gsb_ctx *ctx);
