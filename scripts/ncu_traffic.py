@@ -1,6 +1,7 @@
 """Extract per-launch DRAM traffic (dram__bytes_read.sum + dram__bytes_write.sum) and duration of the hot-path
-kernels from an `ncu --set full` report of one bench step and write profiles/r1_ncu_traffic.json, which bench.py
-reads for `roofline.traffic`.  Usage: python scripts/ncu_traffic.py gpurun_out/step.ncu-rep <batch_per_launch>"""
+kernels from an `ncu --set full` report of one step (scripts/prof_step.py) and write profiles/<round>_ncu_traffic.json,
+which bench.py reads for `roofline.traffic`.
+Usage: python scripts/ncu_traffic.py gpurun_out/step.ncu-rep <batch_per_launch> [round tag, default r2]"""
 import csv
 import json
 import os
@@ -9,6 +10,7 @@ import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 rep, batch = sys.argv[1], int(sys.argv[2])
+tag = sys.argv[3] if len(sys.argv) > 3 else "r2"
 raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(raw.splitlines()))
 hdr, units = rows[0], rows[1]
@@ -28,6 +30,14 @@ def label(name):
         return "ckks_multiply"
     if "ModupLoad" in name:
         return "fwd_cols/modup"
+    if "tail_mid" in name:
+        return "tail_mid"
+    if "TailInvLoad" in name:
+        return "inv_contig/tail_last"
+    if "TailLoad" in name:
+        return "fwd_cols/tail"
+    if "TailStore" in name:
+        return "fwd_contig/tail"
     if "MdLoad" in name:
         return "fwd_cols/moddown"
     if "MdStore" in name:
@@ -58,9 +68,11 @@ for row in rows[2:]:
         "issue_active_pct": float(row[hdr.index("smsp__issue_active.avg.pct_of_peak_sustained_active")]),
         "registers": int(float(row[hdr.index("launch__registers_per_thread")])),
     }
-doc = {"source": os.path.basename(rep), "command": "ncu --set full --clock-control none -s 105 -c 13 "
-       "python bench.py --no-cpu-baseline --steps 1 --warmup 3  (launches 105..117 = the 13 kernels of the 64-ciphertext timed step)", "kernels": out}
-path = os.path.join(ROOT, "profiles", "r1_ncu_traffic.json")
+total = sum(col(row, "dram__bytes_read.sum") + col(row, "dram__bytes_write.sum") for row in rows[2:])
+doc = {"source": os.path.basename(rep), "command": "ncu --set full --clock-control none --import-source on --profile-from-start off "
+       "python scripts/prof_step.py  (the kernels of one 64-ciphertext mul+relin+rescale step after 3 warm-up steps)",
+       "launches_in_step": len(rows) - 2, "dram_bytes_per_step": total, "kernels": out}
+path = os.path.join(ROOT, "profiles", tag + "_ncu_traffic.json")
 with open(path, "w") as f:
     json.dump(doc, f, indent=1)
 print(json.dumps(doc, indent=1))
