@@ -67,6 +67,13 @@ PROTOTYPES = {
     "gsb_bfv_apply_galois_dev": (i32, [vp, vp, u32, vp, vp, sz, sz, vp]),
     "gsb_bfv_relinearize_host": (i32, [vp, vp, vp, sz, sz]),
     "gsb_bfv_apply_galois_host": (i32, [vp, u32, vp, vp, sz, sz]),
+    "gsb_ckks_multiply_sizes_dev": (i32, [vp, vp, sz, vp, sz, vp, sz, sz, vp]),
+    "gsb_ckks_multiply_sizes_host": (i32, [vp, vp, sz, vp, sz, vp, sz, sz]),
+    "gsb_bfv_multiply_sizes_dev": (i32, [vp, vp, u64, vp, sz, vp, sz, vp, sz, sz, vp]),
+    "gsb_bfv_multiply_sizes_host": (i32, [vp, u64, vp, sz, vp, sz, vp, sz, sz]),
+    "gsb_relinearize_sizes_dev": (i32, [vp, vp, vp, sz, vp, sz, sz, i32, vp]),
+    "gsb_relinearize_sizes_host": (i32, [vp, vp, sz, vp, sz, sz, i32]),
+    "gsb_drop_last_limb_dev": (i32, [vp, vp, vp, sz, sz, vp]),
     "gsb_secret_key_set": (i32, [vp, vp]),
     "gsb_dot_product_ct_sk_dev": (i32, [vp, vp, vp, vp, sz, sz, sz, i32, vp]),
     "gsb_dot_product_ct_sk_host": (i32, [vp, vp, vp, sz, sz, sz, i32]),

@@ -555,4 +555,5 @@ int gsb_ctx_fast_ntt(const gsb_ctx *ctx)
 } // extern "C"
 
 #include "gsb_evaluator.cuh"
+#include "gsb_general.cuh"
 #include "gsb_noalloc.cuh"

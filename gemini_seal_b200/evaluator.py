@@ -112,8 +112,11 @@ class Context:
         return (*arrs, sc)
 
     # RelinKeys / GaloisKeys upload: key = [n_bundles][2][K][N] (kswitchkeys.h:343)
-    def set_relin_keys(self, key):
-        self._upload(GSB_KEY_RELIN, 0, key)
+    def set_relin_keys(self, key, key_power=2):
+        """keys.data()[RelinKeys::get_index(key_power)] (relinkeys.h:61): the key for s^key_power."""
+        if key_power < 2:
+            raise ValueError("key_power cannot be less than 2")
+        self._upload(GSB_KEY_RELIN, int(key_power) - 2, key)
 
     def set_galois_key(self, galois_elt, key):
         self._upload(GSB_KEY_GALOIS, int(galois_elt), key)
@@ -229,25 +232,37 @@ class Evaluator:
         return x.shape[0], x.shape[1], x.shape[2]
 
     def multiply(self, a, b):
-        """multiply_inplace of two size-2 NTT-form ciphertexts (evaluator.cpp:235,447-527) -> size 3."""
-        B, _, L = self._shape(a, 2)
-        if tuple(b.shape) != tuple(a.shape):
+        """multiply_inplace of NTT-form ciphertexts of sizes s1, s2 >= 2 (evaluator.cpp:235,447-527) -> size
+        s1 + s2 - 1.  Two size-2 operands take the specialised kernel."""
+        B, s1, L = self._shape(a)
+        if b.ndim != 4 or (b.shape[0], b.shape[2], b.shape[3]) != (B, L, self.ctx.N):
             raise ValueError("encrypted1 and encrypted2 parameter mismatch")
-        out = _empty_like(a, (B, 3, L, self.ctx.N))
+        s2 = b.shape[1]
+        out = _empty_like(a, (B, s1 + s2 - 1, L, self.ctx.N))
         if _is_torch(a):
-            _check(self.lib, self.lib.gsb_ckks_multiply_dev(self.ctx.handle, _ptr(a), _ptr(b), _ptr(out), B, L, _stream()))
+            _check(self.lib, self.lib.gsb_ckks_multiply_sizes_dev(self.ctx.handle, _ptr(a), s1, _ptr(b), s2, _ptr(out), B, L, _stream()))
         else:
-            _check(self.lib, self.lib.gsb_ckks_multiply_host(self.ctx.handle, _ptr(a), _ptr(b), _ptr(out), B, L))
+            _check(self.lib, self.lib.gsb_ckks_multiply_sizes_host(self.ctx.handle, _ptr(a), s1, _ptr(b), s2, _ptr(out), B, L))
         return out
 
+    _BFV = 0
+
     def relinearize(self, c):
-        """relinearize_inplace of size-3 ciphertexts (evaluator.cpp:772-827) -> size 2."""
-        B, _, L = self._shape(c, 3)
+        """relinearize_inplace (evaluator.cpp:772-827) of ciphertexts of any size >= 2 -> size 2; size 3 takes the
+        single key switch, larger sizes need the keys of the higher powers (Context.set_relin_keys(key, power))."""
+        B, size, L = self._shape(c)
         out = _empty_like(c, (B, 2, L, self.ctx.N))
-        if _is_torch(c):
-            _check(self.lib, self.lib.gsb_relinearize_dev(self.ctx.handle, self._ws, _ptr(c), _ptr(out), B, L, _stream()))
+        if size == 3:
+            dev, host = ((self.lib.gsb_bfv_relinearize_dev, self.lib.gsb_bfv_relinearize_host) if self._BFV
+                         else (self.lib.gsb_relinearize_dev, self.lib.gsb_relinearize_host))
+            if _is_torch(c):
+                _check(self.lib, dev(self.ctx.handle, self._ws, _ptr(c), _ptr(out), B, L, _stream()))
+            else:
+                _check(self.lib, host(self.ctx.handle, _ptr(c), _ptr(out), B, L))
+        elif _is_torch(c):
+            _check(self.lib, self.lib.gsb_relinearize_sizes_dev(self.ctx.handle, self._ws, _ptr(c), size, _ptr(out), B, L, self._BFV, _stream()))
         else:
-            _check(self.lib, self.lib.gsb_relinearize_host(self.ctx.handle, _ptr(c), _ptr(out), B, L))
+            _check(self.lib, self.lib.gsb_relinearize_sizes_host(self.ctx.handle, _ptr(c), size, _ptr(out), B, L, self._BFV))
         return out
 
     def rescale_to_next(self, c):
@@ -355,14 +370,7 @@ class BfvEvaluator(Evaluator):
     relinearize_inplace (evaluator.cpp:772-827 -> :2259-2368 with is_ckks == false) and
     apply_galois_inplace / rotate_rows / rotate_columns (evaluator.cpp:1893-1904, evaluator.h:1079-1176)."""
 
-    def relinearize(self, c):
-        B, _, L = self._shape(c, 3)
-        out = _empty_like(c, (B, 2, L, self.ctx.N))
-        if _is_torch(c):
-            _check(self.lib, self.lib.gsb_bfv_relinearize_dev(self.ctx.handle, self._ws, _ptr(c), _ptr(out), B, L, _stream()))
-        else:
-            _check(self.lib, self.lib.gsb_bfv_relinearize_host(self.ctx.handle, _ptr(c), _ptr(out), B, L))
-        return out
+    _BFV = 1  # relinearize() of the base class then takes the coefficient-form branches
 
     def apply_galois(self, c, galois_elt):
         B, _, L = self._shape(c, 2)
@@ -386,15 +394,16 @@ class BfvEvaluator(Evaluator):
         self.plain_modulus = int(plain_modulus)
 
     def multiply(self, a, b):
-        """multiply_inplace -> bfv_multiply (BEHZ, evaluator.cpp:274-445) of size-2 ciphertexts -> size 3."""
-        B, _, L = self._shape(a, 2)
-        if tuple(b.shape) != tuple(a.shape):
+        """multiply_inplace -> bfv_multiply (BEHZ, evaluator.cpp:274-445) of ciphertexts of sizes s1, s2 >= 2."""
+        B, s1, L = self._shape(a)
+        if b.ndim != 4 or (b.shape[0], b.shape[2], b.shape[3]) != (B, L, self.ctx.N):
             raise ValueError("encrypted1 and encrypted2 parameter mismatch")
-        out = _empty_like(a, (B, 3, L, self.ctx.N))
+        s2 = b.shape[1]
+        out = _empty_like(a, (B, s1 + s2 - 1, L, self.ctx.N))
         if _is_torch(a):
-            _check(self.lib, self.lib.gsb_bfv_multiply_dev(self.ctx.handle, self._ws, self.plain_modulus, _ptr(a), _ptr(b), _ptr(out), B, L, _stream()))
+            _check(self.lib, self.lib.gsb_bfv_multiply_sizes_dev(self.ctx.handle, self._ws, self.plain_modulus, _ptr(a), s1, _ptr(b), s2, _ptr(out), B, L, _stream()))
         else:
-            _check(self.lib, self.lib.gsb_bfv_multiply_host(self.ctx.handle, self.plain_modulus, _ptr(a), _ptr(b), _ptr(out), B, L))
+            _check(self.lib, self.lib.gsb_bfv_multiply_sizes_host(self.ctx.handle, self.plain_modulus, _ptr(a), s1, _ptr(b), s2, _ptr(out), B, L))
         return out
 
     def aux_base(self, L):

@@ -204,6 +204,26 @@ int gsb_rescale_host(gsb_ctx *ctx, const uint64_t *in, uint64_t *out, size_t bat
 int gsb_apply_galois_host(gsb_ctx *ctx, uint32_t galois_elt, const uint64_t *in, uint64_t *out, size_t batch, size_t L);
 int gsb_mul_relin_rescale_host(gsb_ctx *ctx, const uint64_t *a, const uint64_t *b, uint64_t *out, size_t batch, size_t L);
 
+/* ---- general ciphertext sizes ------------------------------------------------------------------------
+ * Evaluator::multiply_inplace for operands of any sizes (dest_size = size_a + size_b - 1, evaluator.cpp:470-472;
+ * index window :493-519): a = [batch][size_a][L][N], b = [batch][size_b][L][N] -> out =
+ * [batch][size_a + size_b - 1][L][N]; sizes >= 2, size_a + size_b - 1 <= 16 (SEAL_CIPHERTEXT_SIZE_MAX).
+ * CKKS = ckks_multiply (NTT form), BFV = bfv_multiply (coefficient form, BEHZ, evaluator.cpp:274-445). */
+int gsb_ckks_multiply_sizes_dev(gsb_ctx *ctx, const uint64_t *a, size_t size_a, const uint64_t *b, size_t size_b, uint64_t *out, size_t batch, size_t L, void *stream);
+int gsb_ckks_multiply_sizes_host(gsb_ctx *ctx, const uint64_t *a, size_t size_a, const uint64_t *b, size_t size_b, uint64_t *out, size_t batch, size_t L);
+int gsb_bfv_multiply_sizes_dev(gsb_ctx *ctx, gsb_ws *ws, uint64_t plain_modulus, const uint64_t *a, size_t size_a, const uint64_t *b, size_t size_b, uint64_t *out, size_t batch, size_t L, void *stream);
+int gsb_bfv_multiply_sizes_host(gsb_ctx *ctx, uint64_t plain_modulus, const uint64_t *a, size_t size_a, const uint64_t *b, size_t size_b, uint64_t *out, size_t batch, size_t L);
+/* Evaluator::relinearize_inplace = relinearize_internal(destination_size = 2) (evaluator.cpp:772-827) of
+ * ciphertexts of any size: in = [batch][size][L][N] -> out = [batch][2][L][N]; needs the keys
+ * RelinKeys::get_index(2 .. size-1) (gsb_key_upload with galois_elt = index).  Mirrors the reference's loop
+ * word for word: every one of its size - 2 steps switches the LAST component (evaluator.cpp:806-815 never
+ * moves the iterator).  bfv = 1: coefficient-form (BFV) branch.  out must not overlap in. */
+int gsb_relinearize_sizes_dev(gsb_ctx *ctx, gsb_ws *ws, const uint64_t *in, size_t size, uint64_t *out, size_t batch, size_t L, int bfv, void *stream);
+int gsb_relinearize_sizes_host(gsb_ctx *ctx, const uint64_t *in, size_t size, uint64_t *out, size_t batch, size_t L, int bfv);
+/* Evaluator::mod_switch_to_next, CKKS branch = mod_switch_drop_to_next (evaluator.cpp:894-957): in =
+ * [n_polys][L][N] -> out = [n_polys][L-1][N], the first L-1 limbs of every polynomial (device buffers). */
+int gsb_drop_last_limb_dev(gsb_ctx *ctx, const uint64_t *in, uint64_t *out, size_t n_polys, size_t L, void *stream);
+
 /* ---- Decryptor (seal::Decryptor, decryptor.cpp) --------------------------------
  * gsb_secret_key_set: SecretKey::data() in NTT form at key level, sk_host = [K][N] canonical residues
  * (Decryptor::Decryptor, decryptor.cpp:21-58; rejects what is_valid_for(SecretKey) rejects).  Powers

@@ -54,6 +54,9 @@ class Oracle:
         lib.so_ctx_create.restype = vp
         lib.so_ctx_destroy.argtypes = [vp]
         lib.so_ckks_multiply.argtypes = [vp, sz, vp, vp, vp]
+        lib.so_ckks_multiply_sizes.argtypes = [vp, sz, vp, sz, vp, sz, vp]
+        lib.so_relinearize_sizes.argtypes = [vp, sz, sz, vp, vp, sz, i32, vp]
+        lib.so_bfv_multiply_sizes.argtypes = [i32, C.POINTER(u64), sz, u64, vp, sz, vp, sz, vp]
         lib.so_switch_key.argtypes = [vp, sz, vp, vp, vp]
         lib.so_relinearize.argtypes = [vp, sz, vp, vp, vp]
         lib.so_rescale.argtypes = [vp, sz, sz, vp, vp]
@@ -129,6 +132,13 @@ class Oracle:
         assert self.lib.so_bfv_multiply(logn, _u64arr(moduli[:L]), L, plain_modulus, _p(a), _p(b), _p(out)) == 0
         return out
 
+    def bfv_multiply_sizes(self, logn, moduli, plain_modulus, a, b):
+        """bfv_multiply of coefficient-form ciphertexts of any sizes [sa][L][N] x [sb][L][N] -> [sa+sb-1][L][N]."""
+        L, sa, sb = a.shape[1], a.shape[0], b.shape[0]
+        out = np.empty((sa + sb - 1, L, 1 << logn), dtype=np.uint64)
+        assert self.lib.so_bfv_multiply_sizes(logn, _u64arr(moduli[:L]), L, plain_modulus, _p(a), sa, _p(b), sb, _p(out)) == 0
+        return out
+
     def bfv_aux_base(self, logn, moduli, plain_modulus):
         out = np.zeros(64, dtype=np.uint64)
         assert self.lib.so_bfv_aux_base(logn, _u64arr(moduli), len(moduli), plain_modulus, _p(out)) == 0
@@ -173,6 +183,20 @@ class OracleCtx:
         L = c3.shape[1]
         out = np.empty((2, L, self.N), dtype=np.uint64)
         assert self.lib.so_relinearize(self.h, L, _p(c3), _p(key), _p(out)) == 0
+        return out
+
+    def multiply_sizes(self, a, b):
+        L, sa, sb = a.shape[1], a.shape[0], b.shape[0]
+        out = np.empty((sa + sb - 1, L, self.N), dtype=np.uint64)
+        assert self.lib.so_ckks_multiply_sizes(self.h, L, _p(a), sa, _p(b), sb, _p(out)) == 0
+        return out
+
+    def relinearize_sizes(self, c, keys, bfv=False):
+        """c = [size][L][N]; keys = [size - 2][n_bundles][2][K][N], keys[p] = RelinKeys::get_index(p + 2)."""
+        size, L = c.shape[0], c.shape[1]
+        keys = np.ascontiguousarray(keys)
+        out = np.empty((2, L, self.N), dtype=np.uint64)
+        assert self.lib.so_relinearize_sizes(self.h, L, size, _p(c), _p(keys), keys[0].size, 0 if bfv else 1, _p(out)) == 0
         return out
 
     def rescale(self, c):
@@ -254,6 +278,9 @@ class RefLib:
         lib.ref_get_key.argtypes = [vp, i32, u32, vp]
         lib.ref_set_key.argtypes = [vp, i32, u32, vp]
         lib.ref_multiply.argtypes = [vp, sz, vp, vp, vp]
+        lib.ref_set_relin_count.argtypes = [vp, sz]
+        lib.ref_multiply_sizes.argtypes = [vp, sz, vp, sz, vp, sz, vp]
+        lib.ref_relinearize_sizes.argtypes = [vp, sz, sz, vp, vp]
         lib.ref_relinearize.argtypes = [vp, sz, vp, vp]
         lib.ref_rescale.argtypes = [vp, sz, sz, vp, vp]
         lib.ref_apply_galois.argtypes = [vp, sz, u32, vp, vp]
@@ -368,6 +395,21 @@ class RefCtx:
         L = c3.shape[1]
         out = np.empty((2, L, self.N), dtype=np.uint64)
         self._run(self.lib.ref_relinearize(self.h, L, _p(c3), _p(out)))
+        return out
+
+    def set_relin_count(self, count):
+        self._run(self.lib.ref_set_relin_count(self.h, count))
+
+    def multiply_sizes(self, a, b):
+        L, sa, sb = a.shape[1], a.shape[0], b.shape[0]
+        out = np.empty((sa + sb - 1, L, self.N), dtype=np.uint64)
+        self._run(self.lib.ref_multiply_sizes(self.h, L, _p(a), sa, _p(b), sb, _p(out)))
+        return out
+
+    def relinearize_sizes(self, c):
+        size, L = c.shape[0], c.shape[1]
+        out = np.empty((2, L, self.N), dtype=np.uint64)
+        self._run(self.lib.ref_relinearize_sizes(self.h, L, size, _p(c), _p(out)))
         return out
 
     def rescale(self, c):

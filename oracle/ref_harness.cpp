@@ -39,6 +39,7 @@ namespace
         GaloisKeys galois;
         bool have_relin = false, have_galois = false;
         bool bfv = false; // BFV context: coefficient-form ciphertexts, scale 1
+        size_t n_relin = 1; // relinearization keys (powers s^2 ..) made by ref_keygen / ref_make_synthetic_keys
         size_t N = 0, K = 0, k = 0, L0 = 0;
 
         parms_id_type parms_at(size_t L) const
@@ -277,6 +278,10 @@ extern "C"
         return guarded([&] {
             c->keygen.reset(new KeyGenerator(c->context));
             c->relin = c->keygen->relin_keys_local();
+            // the public KeyGenerator only makes the s^2 key (keygenerator.h:82-85); further powers get the same
+            // shape here and their limbs from ref_set_key
+            for (size_t p = 1; p < c->n_relin; p++)
+                c->relin.data().push_back(c->relin.data()[0]);
             c->have_relin = true;
             if (n_elts)
             {
@@ -314,8 +319,9 @@ extern "C"
                 }
             };
             c->relin = RelinKeys();
-            c->relin.data().resize(1);
-            fill(c->relin.data()[0]);
+            c->relin.data().resize(c->n_relin);
+            for (auto &v : c->relin.data())
+                fill(v);
             c->relin.parms_id() = key_cd->parms_id();
             c->have_relin = true;
             c->galois = GaloisKeys();
@@ -341,7 +347,9 @@ extern "C"
         {
             if (!c->have_relin)
                 throw std::logic_error("no relin keys");
-            return c->relin.data()[RelinKeys::get_index(2)];
+            if (elt >= c->relin.data().size())
+                throw std::logic_error("no relin key of that power");
+            return c->relin.data()[elt]; // elt = RelinKeys::get_index(key_power)
         }
         if (!c->have_galois || !c->galois.has_key(elt))
             throw std::logic_error("no galois key for elt");
@@ -375,6 +383,40 @@ extern "C"
             size_t per = 2 * c->K * c->N;
             for (size_t j = 0; j < v.size(); j++)
                 std::memcpy(v[j].data().data(), in + j * per, per * 8);
+        });
+    }
+
+    // how many relinearization keys ref_keygen / ref_make_synthetic_keys produce from now on (default 1)
+    int ref_set_relin_count(void *h, size_t count)
+    {
+        auto *c = static_cast<RefCtx *>(h);
+        return guarded([&] {
+            if (count < 1 || count > 14)
+                throw std::invalid_argument("count");
+            c->n_relin = count;
+        });
+    }
+
+    // multiply_inplace for any sizes: a = [sa][L][N], b = [sb][L][N] -> out [sa + sb - 1][L][N]
+    int ref_multiply_sizes(void *h, size_t L, const uint64_t *a, size_t sa, const uint64_t *b, size_t sb, uint64_t *out)
+    {
+        auto *c = static_cast<RefCtx *>(h);
+        return guarded([&] {
+            auto x = c->make_ct(a, sa, L, std::pow(2.0, 10));
+            auto y = c->make_ct(b, sb, L, std::pow(2.0, 10));
+            c->evaluator->multiply_inplace(x, y);
+            std::memcpy(out, x.data(), (sa + sb - 1) * L * c->N * 8);
+        });
+    }
+
+    // relinearize_inplace from any size: in [size][L][N] -> out [2][L][N]
+    int ref_relinearize_sizes(void *h, size_t L, size_t size, const uint64_t *in, uint64_t *out)
+    {
+        auto *c = static_cast<RefCtx *>(h);
+        return guarded([&] {
+            auto x = c->make_ct(in, size, L, std::pow(2.0, 30));
+            c->evaluator->relinearize_inplace(x, c->relin);
+            std::memcpy(out, x.data(), 2 * L * c->N * 8);
         });
     }
 

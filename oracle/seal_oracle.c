@@ -484,14 +484,15 @@ void so_ctx_destroy(so_ctx *c)
 /* ======================================================================================== */
 /* CKKS multiply  (evaluator.cpp:447-527)                                                   */
 /* ======================================================================================== */
-int so_ckks_multiply(const so_ctx *c, size_t L, const uint64_t *a, const uint64_t *b, uint64_t *out)
+/* General sizes: a = [sa][L][N], b = [sb][L][N] -> out = [sa + sb - 1][L][N] (dest_size, :470-472). */
+int so_ckks_multiply_sizes(const so_ctx *c, size_t L, const uint64_t *a, size_t sa, const uint64_t *b, size_t sb, uint64_t *out)
 {
-    if (L < 1 || L > c->L0)
+    if (L < 1 || L > c->L0 || sa < 1 || sb < 1)
         return -1;
-    const size_t N = c->N;
+    const size_t N = c->N, sd = sa + sb - 1;
     /* dest[I] = sum over (i + j = I) of a_i o b_j, accumulated with add_poly_coeffmod into a
-     * zeroed buffer (:491-520); i ascending, j descending. */
-    for (size_t I = 0; I < 3; I++)
+     * zeroed buffer (:491-520); i ascending, j descending; index window of :497-503. */
+    for (size_t I = 0; I < sd; I++)
     {
         for (size_t l = 0; l < L; l++)
         {
@@ -499,7 +500,7 @@ int so_ckks_multiply(const so_ctx *c, size_t L, const uint64_t *a, const uint64_
             const uint64_t *cr = c->tab[l].cr;
             uint64_t *dst = out + (I * L + l) * N;
             memset(dst, 0, N * 8);
-            size_t i_last = I < 1 ? I : 1, j_first = I < 1 ? I : 1, i_first = I - j_first;
+            size_t i_last = I < sa - 1 ? I : sa - 1, j_first = I < sb - 1 ? I : sb - 1, i_first = I - j_first;
             for (size_t i = i_first; i <= i_last; i++)
             {
                 size_t j = I - i;
@@ -510,6 +511,11 @@ int so_ckks_multiply(const so_ctx *c, size_t L, const uint64_t *a, const uint64_
         }
     }
     return 0;
+}
+
+int so_ckks_multiply(const so_ctx *c, size_t L, const uint64_t *a, const uint64_t *b, uint64_t *out)
+{
+    return so_ckks_multiply_sizes(c, L, a, 2, b, 2, out);
 }
 
 /* ======================================================================================== */
@@ -798,6 +804,29 @@ int so_relinearize(const so_ctx *c, size_t L, const uint64_t *in, const uint64_t
     uint64_t *tmp = (uint64_t *)malloc(3 * L * N * 8);
     memcpy(tmp, in, 3 * L * N * 8);
     int rc = so_switch_key(c, L, tmp, tmp + 2 * L * N, key);
+    if (!rc)
+        memcpy(out, tmp, 2 * L * N * 8);
+    free(tmp);
+    return rc;
+}
+
+/* relinearize_internal (evaluator.cpp:772-827) from any size down to 2.  keys = the relinearization keys
+ * back to back, key_words each, key p (RelinKeys::get_index(p + 2)) at keys + p * key_words.  The loop at
+ * :809-815 switches `*encrypted_iter` with key get_index(size - 1 - I); encrypted_iter was set to the LAST
+ * component at :806-807 and is not moved inside the loop, so every step's target is component size - 1. */
+int so_relinearize_sizes(const so_ctx *c, size_t L, size_t size, const uint64_t *in, const uint64_t *keys, size_t key_words, int is_ckks, uint64_t *out)
+{
+    const size_t N = c->N;
+    if (size < 2)
+        return -1;
+    uint64_t *tmp = (uint64_t *)malloc(size * L * N * 8);
+    memcpy(tmp, in, size * L * N * 8);
+    int rc = 0;
+    for (size_t I = 0; !rc && I + 2 < size; I++)
+    {
+        const uint64_t *key = keys + (size - 1 - I - 2) * key_words;
+        rc = is_ckks ? so_switch_key(c, L, tmp, tmp + (size - 1) * L * N, key) : so_switch_key_bfv(c, L, tmp, tmp + (size - 1) * L * N, key);
+    }
     if (!rc)
         memcpy(out, tmp, 2 * L * N * 8);
     free(tmp);

@@ -79,10 +79,12 @@ so_ctx *so_ctx_create(int logn, const uint64_t *moduli, size_t K, size_t k_speci
 void so_ctx_destroy(so_ctx *c);
 /* a,b [2][L][N] -> out [3][L][N] */
 int so_ckks_multiply(const so_ctx *c, size_t L, const uint64_t *a, const uint64_t *b, uint64_t *out);
+int so_ckks_multiply_sizes(const so_ctx *c, size_t L, const uint64_t *a, size_t sa, const uint64_t *b, size_t sb, uint64_t *out);
 /* enc [>=2][L][N] (components 0,1 updated in place); target [L][N]; key [beta][2][K][N] */
 int so_switch_key(const so_ctx *c, size_t L, uint64_t *enc, const uint64_t *target, const uint64_t *key);
 /* in [3][L][N] -> out [2][L][N] */
 int so_relinearize(const so_ctx *c, size_t L, const uint64_t *in, const uint64_t *key, uint64_t *out);
+int so_relinearize_sizes(const so_ctx *c, size_t L, size_t size, const uint64_t *in, const uint64_t *keys, size_t key_words, int is_ckks, uint64_t *out);
 /* in [size][L][N] -> out [size][L-1][N] */
 int so_rescale(const so_ctx *c, size_t L, size_t size, const uint64_t *in, uint64_t *out);
 /* in/out [2][L][N] */
@@ -97,6 +99,7 @@ int so_apply_galois_bfv(const so_ctx *c, size_t L, uint32_t elt, const uint64_t 
 /* Evaluator::bfv_multiply (BEHZ, evaluator.cpp:274-445; seal_oracle_bfv.c): a, b [2][L][N] in
  * coefficient form over q[0..L) -> out [3][L][N] */
 int so_bfv_multiply(int logn, const uint64_t *q, size_t L, uint64_t plain_modulus, const uint64_t *a, const uint64_t *b, uint64_t *out);
+int so_bfv_multiply_sizes(int logn, const uint64_t *q, size_t L, uint64_t plain_modulus, const uint64_t *a, size_t sa, const uint64_t *b, size_t sb, uint64_t *out);
 /* out[0] = |B|, out[1..] = the |B|+1 moduli of Bsk (rns.cpp:585-603) */
 int so_bfv_aux_base(int logn, const uint64_t *q, size_t L, uint64_t plain_modulus, uint64_t *out);
 /* ---- Decryptor (seal_oracle_bfv.c) -------------------------------------- */

@@ -361,27 +361,28 @@ static void fastbconv_sk(const behz_t *b, const uint64_t *in, uint64_t *out)
     free(alpha);
 }
 
-/* Evaluator::bfv_multiply for two size-2 ciphertexts (evaluator.cpp:274-445).
- * a, b = [2][L][n] coefficient form over q[0..L); out = [3][L][n]. */
-int so_bfv_multiply(int logn, const uint64_t *q, size_t L, uint64_t plain_modulus, const uint64_t *a, const uint64_t *b, uint64_t *out)
+/* Evaluator::bfv_multiply (evaluator.cpp:274-445) for ciphertexts of sizes sa, sb:
+ * a = [sa][L][n], b = [sb][L][n] coefficient form over q[0..L); out = [sa + sb - 1][L][n]. */
+int so_bfv_multiply_sizes(int logn, const uint64_t *q, size_t L, uint64_t plain_modulus, const uint64_t *a, size_t sa, const uint64_t *b, size_t sb, uint64_t *out)
 {
     behz_t *z = (behz_t *)malloc(sizeof(behz_t));
     if (!z)
         return -1;
-    if (behz_init(z, logn, q, L, plain_modulus))
+    if (sa < 1 || sb < 1 || behz_init(z, logn, q, L, plain_modulus))
     {
         free(z);
         return -1;
     }
-    const size_t n = z->n, nBsk = z->nBsk;
+    const size_t n = z->n, nBsk = z->nBsk, sd = sa + sb - 1;
     uint64_t *eq[2], *eB[2];
     const uint64_t *src[2] = { a, b };
+    const size_t sz[2] = { sa, sb };
     uint64_t *temp = (uint64_t *)malloc((nBsk + 1) * n * 8);
     for (int s = 0; s < 2; s++)
     {
-        eq[s] = (uint64_t *)malloc(2 * L * n * 8);
-        eB[s] = (uint64_t *)malloc(2 * nBsk * n * 8);
-        for (size_t p = 0; p < 2; p++) /* behz_extend_base_convert_to_ntt (:331-350) */
+        eq[s] = (uint64_t *)malloc(sz[s] * L * n * 8);
+        eB[s] = (uint64_t *)malloc(sz[s] * nBsk * n * 8);
+        for (size_t p = 0; p < sz[s]; p++) /* behz_extend_base_convert_to_ntt (:331-350) */
         {
             const uint64_t *in = src[s] + p * L * n;
             uint64_t *oq = eq[s] + p * L * n, *oB = eB[s] + p * nBsk * n;
@@ -395,10 +396,10 @@ int so_bfv_multiply(int logn, const uint64_t *q, size_t L, uint64_t plain_modulu
         }
     }
     free(temp);
-    uint64_t *dq = (uint64_t *)calloc(3 * L * n, 8), *dB = (uint64_t *)calloc(3 * nBsk * n, 8);
-    for (size_t I = 0; I < 3; I++) /* step (4), :372-421 */
+    uint64_t *dq = (uint64_t *)calloc(sd * L * n, 8), *dB = (uint64_t *)calloc(sd * nBsk * n, 8);
+    for (size_t I = 0; I < sd; I++) /* step (4), :372-421 */
     {
-        size_t i_last = I < 1 ? I : 1, j_first = I < 1 ? I : 1, i_first = I - j_first;
+        size_t i_last = I < sa - 1 ? I : sa - 1, j_first = I < sb - 1 ? I : sb - 1, i_first = I - j_first;
         for (size_t i = i_first; i <= i_last; i++)
         {
             const size_t j = I - i;
@@ -419,7 +420,7 @@ int so_bfv_multiply(int logn, const uint64_t *q, size_t L, uint64_t plain_modulu
         }
     }
     uint64_t *tqB = (uint64_t *)malloc((L + nBsk) * n * 8), *tB = (uint64_t *)malloc(nBsk * n * 8);
-    for (size_t I = 0; I < 3; I++)
+    for (size_t I = 0; I < sd; I++)
     {
         for (size_t l = 0; l < L; l++) /* step (5), :424-425 */
             so_ntt_inv(dq + (I * L + l) * n, &z->qtab[l]);
@@ -446,6 +447,11 @@ int so_bfv_multiply(int logn, const uint64_t *q, size_t L, uint64_t plain_modulu
     behz_free(z);
     free(z);
     return 0;
+}
+
+int so_bfv_multiply(int logn, const uint64_t *q, size_t L, uint64_t plain_modulus, const uint64_t *a, const uint64_t *b, uint64_t *out)
+{
+    return so_bfv_multiply_sizes(logn, q, L, plain_modulus, a, 2, b, 2, out);
 }
 
 /* The auxiliary base the reference derives for (n, q[0..L), t): out[0] = |B|, then the |B| + 1 Bsk

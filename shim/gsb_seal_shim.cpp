@@ -99,18 +99,26 @@ namespace gsb_seal
         const double new_scale = encrypted1.scale() * encrypted2.scale();
         if (new_scale <= 0 || (static_cast<int>(log2(new_scale)) >= context_data.total_coeff_modulus_bit_count()))
             throw invalid_argument("scale out of bounds");
-        if (encrypted1.size() != 2 || encrypted2.size() != 2)
-            throw logic_error("device multiply serves size-2 operands (relinearize first)");
-        const size_t L = level_limbs(encrypted1);
+        const size_t L = level_limbs(encrypted1), s1 = encrypted1.size(), s2 = encrypted2.size();
+        const size_t dest_size = seal::util::sub_safe(seal::util::add_safe(s1, s2), size_t(1)); // evaluator.cpp:470
+        if (!seal::util::product_fits_in(dest_size, N_, L))
+            throw logic_error("invalid parameters");
         vector<uint64_t> b;
         const uint64_t *pb = encrypted2.data();
         if (&encrypted1 == &encrypted2) // square: keep a copy, the destination is resized below
         {
-            b.assign(encrypted2.data(), encrypted2.data() + 2 * L * N_);
+            b.assign(encrypted2.data(), encrypted2.data() + s2 * L * N_);
             pb = b.data();
         }
-        encrypted1.resize(context_, context_data.parms_id(), 3);
-        check(gsb_ckks_multiply_host(ctx_, encrypted1.data(), pb, encrypted1.data(), 1, L));
+        // the resize keeps the operand's polynomials at the front of the buffer; the device call reads them before
+        // it writes the product there.  A device failure puts the operand back as it was.
+        encrypted1.resize(context_, context_data.parms_id(), dest_size);
+        const int rc = gsb_ckks_multiply_sizes_host(ctx_, encrypted1.data(), s1, pb, s2, encrypted1.data(), 1, L);
+        if (rc != GSB_OK)
+        {
+            encrypted1.resize(context_, context_data.parms_id(), s1);
+            fail(rc);
+        }
         encrypted1.scale() = new_scale;
 #ifdef SEAL_THROW_ON_TRANSPARENT_CIPHERTEXT
         if (encrypted1.is_transparent())
@@ -123,20 +131,25 @@ namespace gsb_seal
     {
         if (encrypted1.is_ntt_form() || encrypted2.is_ntt_form())
             throw invalid_argument("encrypted1 or encrypted2 cannot be in NTT form");
-        if (encrypted1.size() != 2 || encrypted2.size() != 2)
-            throw logic_error("device multiply serves size-2 operands (relinearize first)");
         auto &context_data = *context_->get_context_data(encrypted1.parms_id());
-        const size_t L = level_limbs(encrypted1);
+        const size_t L = level_limbs(encrypted1), s1 = encrypted1.size(), s2 = encrypted2.size();
+        const size_t dest_size = seal::util::sub_safe(seal::util::add_safe(s1, s2), size_t(1));
+        if (!seal::util::product_fits_in(dest_size, N_, context_data.rns_tool()->base_Bsk_m_tilde()->size())) // evaluator.cpp:297-300
+            throw logic_error("invalid parameters");
         vector<uint64_t> b;
         const uint64_t *pb = encrypted2.data();
         if (&encrypted1 == &encrypted2)
         {
-            b.assign(encrypted2.data(), encrypted2.data() + 2 * L * N_);
+            b.assign(encrypted2.data(), encrypted2.data() + s2 * L * N_);
             pb = b.data();
         }
-        vector<uint64_t> a(encrypted1.data(), encrypted1.data() + 2 * L * N_);
-        encrypted1.resize(context_, context_data.parms_id(), 3);
-        check(gsb_bfv_multiply_host(ctx_, plain_modulus_, a.data(), pb, encrypted1.data(), 1, L));
+        encrypted1.resize(context_, context_data.parms_id(), dest_size);
+        const int rc = gsb_bfv_multiply_sizes_host(ctx_, plain_modulus_, encrypted1.data(), s1, pb, s2, encrypted1.data(), 1, L);
+        if (rc != GSB_OK)
+        {
+            encrypted1.resize(context_, context_data.parms_id(), s1);
+            fail(rc);
+        }
 #ifdef SEAL_THROW_ON_TRANSPARENT_CIPHERTEXT
         if (encrypted1.is_transparent())
             throw logic_error("result ciphertext is transparent");
@@ -350,11 +363,40 @@ namespace gsb_seal
         check(gsb_key_upload(ctx_, kind, slot, flat.data(), bundles.size()));
     }
 
+    // Which host key sits in a device slot is decided by CONTENT, not by address: SEAL's MemoryPool hands a freed
+    // block to the next allocation of the same size, so a regenerated / reloaded / other client's key can live at
+    // the address of the one uploaded earlier.  The fingerprint mixes, for every bundle, its size, its first and
+    // last 512 words and one word out of every 1024 (a 120 MiB key costs ~ 20 k words to fingerprint).
+    static uint64_t key_fingerprint(const vector<PublicKey> &bundles)
+    {
+        uint64_t h = 0x9E3779B97F4A7C15ull ^ bundles.size();
+        auto mix = [&](uint64_t v) {
+            h ^= v + 0x9E3779B97F4A7C15ull + (h << 6) + (h >> 2);
+            h *= 0xBF58476D1CE4E5B9ull;
+            h ^= h >> 29;
+        };
+        for (auto &pk : bundles)
+        {
+            const uint64_t *p = pk.data().data();
+            const size_t n = pk.data().size() * pk.data().poly_modulus_degree() * pk.data().coeff_modulus_size();
+            mix(n);
+            const size_t edge = n < 1024 ? n / 2 : 512;
+            for (size_t i = 0; i < edge; i++)
+            {
+                mix(p[i]);
+                mix(p[n - 1 - i]);
+            }
+            for (size_t i = edge; i + edge < n; i += 1024)
+                mix(p[i]);
+        }
+        return h;
+    }
+
     void Evaluator::ensure_relin(const RelinKeys &keys, size_t index)
     {
         lock_guard<mutex> lock(mu_);
         const auto &bundles = keys.data()[index];
-        const void *id = bundles.empty() ? nullptr : static_cast<const void *>(bundles[0].data().data());
+        const uint64_t id = key_fingerprint(bundles);
         auto it = relin_loaded_.find(static_cast<uint32_t>(index));
         if (it != relin_loaded_.end() && it->second == id)
             return;
@@ -366,7 +408,7 @@ namespace gsb_seal
     {
         lock_guard<mutex> lock(mu_);
         const auto &bundles = keys.data()[GaloisKeys::get_index(elt)];
-        const void *id = bundles.empty() ? nullptr : static_cast<const void *>(bundles[0].data().data());
+        const uint64_t id = key_fingerprint(bundles);
         auto it = galois_loaded_.find(elt);
         if (it != galois_loaded_.end() && it->second == id)
             return;
@@ -390,40 +432,18 @@ namespace gsb_seal
             return;
         if (encrypted.is_ntt_form() == bfv_) // BFV ciphertexts are in coefficient form, CKKS ones in NTT form
             throw logic_error(bfv_ ? "BFV encrypted cannot be in NTT form" : "CKKS encrypted must be in NTT form");
-        const size_t L = level_limbs(encrypted), LN = L * N_;
-        if (size > 3 && bfv_)
-            throw logic_error("device BFV relinearization serves size-3 ciphertexts");
+        const size_t L = level_limbs(encrypted);
+        for (size_t p = 2; p < size; p++) // every key the loop at evaluator.cpp:809-815 uses: s^2 .. s^(size-1)
+            ensure_relin(relin_keys, RelinKeys::get_index(p));
+        // in place on the host buffer: one chunk, so the device has read all `size` polynomials before the two
+        // result polynomials are copied back over the front of the buffer; the return code is checked before the
+        // ciphertext is resized (no mutation on failure)
         if (size == 3)
-        {
-            ensure_relin(relin_keys, RelinKeys::get_index(2));
-            vector<uint64_t> out(2 * LN);
-            check(bfv_ ? gsb_bfv_relinearize_host(ctx_, encrypted.data(), out.data(), 1, L)
-                       : gsb_relinearize_host(ctx_, encrypted.data(), out.data(), 1, L));
-            encrypted.resize(context_, context_data_ptr->parms_id(), 2);
-            memcpy(encrypted.data(), out.data(), 2 * LN * sizeof(uint64_t));
-        }
+            check(bfv_ ? gsb_bfv_relinearize_host(ctx_, encrypted.data(), encrypted.data(), 1, L)
+                       : gsb_relinearize_host(ctx_, encrypted.data(), encrypted.data(), 1, L));
         else
-        {
-            // one key switch per extra component, last component first (evaluator.cpp:811-815), device resident
-            void *d = nullptr;
-            check(gsb_malloc(ctx_, size * LN * sizeof(uint64_t), &d));
-            int rc = gsb_memcpy_h2d(ctx_, d, encrypted.data(), size * LN * sizeof(uint64_t), nullptr);
-            for (size_t i = 0; rc == GSB_OK && i < size - 2; i++)
-            {
-                const size_t comp = size - 1 - i;
-                ensure_relin(relin_keys, RelinKeys::get_index(comp));
-                rc = gsb_switch_key_dev(
-                    ctx_, nullptr, static_cast<uint64_t *>(d), size, static_cast<uint64_t *>(d) + comp * LN, 0, GSB_KEY_RELIN,
-                    static_cast<uint32_t>(RelinKeys::get_index(comp)), 1, L, nullptr);
-            }
-            encrypted.resize(context_, context_data_ptr->parms_id(), 2);
-            if (rc == GSB_OK)
-                rc = gsb_memcpy_d2h(ctx_, encrypted.data(), d, 2 * LN * sizeof(uint64_t), nullptr);
-            if (rc == GSB_OK)
-                rc = gsb_stream_sync(ctx_, nullptr);
-            gsb_free(ctx_, d);
-            check(rc);
-        }
+            check(gsb_relinearize_sizes_host(ctx_, encrypted.data(), size, encrypted.data(), 1, L, bfv_ ? 1 : 0));
+        encrypted.resize(context_, context_data_ptr->parms_id(), 2);
 #ifdef SEAL_THROW_ON_TRANSPARENT_CIPHERTEXT
         if (encrypted.is_transparent())
             throw logic_error("result ciphertext is transparent");
@@ -778,8 +798,6 @@ namespace gsb_seal
     void Evaluator::upload(const Ciphertext &encrypted, DeviceCiphertext &destination)
     {
         validate(encrypted, "encrypted");
-        if (bfv_)
-            throw logic_error("device-resident handles serve CKKS");
         const size_t L = level_limbs(encrypted), words = encrypted.size() * L * N_;
         destination.reserve(ctx_, words);
         check(gsb_memcpy_h2d(ctx_, destination.d_, encrypted.data(), words * sizeof(uint64_t), nullptr));
@@ -792,8 +810,6 @@ namespace gsb_seal
     {
         if (encrypted.empty() || encrypted[0] == nullptr)
             throw invalid_argument("encrypted vector must not be empty");
-        if (bfv_)
-            throw logic_error("device-resident handles serve CKKS");
         const Ciphertext &first = *encrypted[0];
         for (const Ciphertext *ct : encrypted)
         {
@@ -846,20 +862,38 @@ namespace gsb_seal
         own(e2, "encrypted2");
         if (e1.parms_id_ != e2.parms_id_) // evaluator.cpp:238-249, 449-468
             throw invalid_argument("encrypted1 and encrypted2 parameter mismatch");
+        if (bfv_) // bfv_multiply (evaluator.cpp:274-445) on coefficient-form handles
+        {
+            if (e1.ntt_ || e2.ntt_)
+                throw invalid_argument("encrypted1 or encrypted2 cannot be in NTT form");
+            if (e1.batch_ != e2.batch_)
+                throw invalid_argument("encrypted1 and encrypted2 batch mismatch");
+            auto &cd = *context_->get_context_data(e1.parms_id_);
+            const size_t ds = seal::util::sub_safe(seal::util::add_safe(e1.size_, e2.size_), size_t(1));
+            if (!seal::util::product_fits_in(ds, N_, cd.rns_tool()->base_Bsk_m_tilde()->size()))
+                throw logic_error("invalid parameters");
+            DeviceCiphertext out;
+            out.reserve(ctx_, e1.batch_ * ds * e1.L_ * N_);
+            check(gsb_bfv_multiply_sizes_dev(ctx_, nullptr, plain_modulus_, e1.d_, e1.size_, e2.d_, e2.size_, out.d_, e1.batch_, e1.L_, nullptr));
+            out.size_ = ds, out.L_ = e1.L_, out.batch_ = e1.batch_, out.parms_id_ = e1.parms_id_, out.scale_ = e1.scale_, out.ntt_ = false;
+            e1 = move(out);
+            return;
+        }
         if (!(e1.ntt_ && e2.ntt_))
             throw invalid_argument("encrypted1 or encrypted2 must be in NTT form");
         auto &context_data = *context_->get_context_data(e1.parms_id_);
         const double new_scale = e1.scale_ * e2.scale_;
         if (new_scale <= 0 || (static_cast<int>(log2(new_scale)) >= context_data.total_coeff_modulus_bit_count()))
             throw invalid_argument("scale out of bounds");
-        if (e1.size_ != 2 || e2.size_ != 2)
-            throw logic_error("device multiply serves size-2 operands (relinearize first)");
         if (e1.batch_ != e2.batch_)
             throw invalid_argument("encrypted1 and encrypted2 batch mismatch");
+        const size_t dest_size = seal::util::sub_safe(seal::util::add_safe(e1.size_, e2.size_), size_t(1));
+        if (!seal::util::product_fits_in(dest_size, N_, e1.L_))
+            throw logic_error("invalid parameters");
         DeviceCiphertext out;
-        out.reserve(ctx_, e1.batch_ * 3 * e1.L_ * N_);
-        check(gsb_ckks_multiply_dev(ctx_, e1.d_, e2.d_, out.d_, e1.batch_, e1.L_, nullptr));
-        out.size_ = 3, out.L_ = e1.L_, out.batch_ = e1.batch_, out.parms_id_ = e1.parms_id_, out.scale_ = new_scale, out.ntt_ = true;
+        out.reserve(ctx_, e1.batch_ * dest_size * e1.L_ * N_);
+        check(gsb_ckks_multiply_sizes_dev(ctx_, e1.d_, e1.size_, e2.d_, e2.size_, out.d_, e1.batch_, e1.L_, nullptr));
+        out.size_ = dest_size, out.L_ = e1.L_, out.batch_ = e1.batch_, out.parms_id_ = e1.parms_id_, out.scale_ = new_scale, out.ntt_ = true;
         e1 = move(out);
     }
 
@@ -868,19 +902,22 @@ namespace gsb_seal
         own(e, "encrypted");
         if (relin_keys.parms_id() != context_->key_parms_id()) // evaluator.cpp:776-796
             throw invalid_argument("relin_keys is not valid for encryption parameters");
-        if (relin_keys.size() < e.size_ - 2)
+        if (relin_keys.size() < (e.size_ >= 2 ? e.size_ - 2 : 0))
             throw invalid_argument("not enough relinearization keys");
-        if (e.size_ == 2)
+        if (e.size_ <= 2)
             return;
-        if (!e.ntt_)
-            throw logic_error("CKKS encrypted must be in NTT form");
-        if (e.size_ != 3)
-            throw logic_error("device-resident relinearization serves size-3 ciphertexts");
-        ensure_relin(relin_keys, RelinKeys::get_index(2));
+        if (e.ntt_ == bfv_)
+            throw logic_error(bfv_ ? "BFV encrypted cannot be in NTT form" : "CKKS encrypted must be in NTT form");
+        for (size_t p = 2; p < e.size_; p++)
+            ensure_relin(relin_keys, RelinKeys::get_index(p));
         DeviceCiphertext out;
         out.reserve(ctx_, e.batch_ * 2 * e.L_ * N_);
-        check(gsb_relinearize_dev(ctx_, nullptr, e.d_, out.d_, e.batch_, e.L_, nullptr));
-        out.size_ = 2, out.L_ = e.L_, out.batch_ = e.batch_, out.parms_id_ = e.parms_id_, out.scale_ = e.scale_, out.ntt_ = true;
+        if (e.size_ == 3)
+            check(bfv_ ? gsb_bfv_relinearize_dev(ctx_, nullptr, e.d_, out.d_, e.batch_, e.L_, nullptr)
+                       : gsb_relinearize_dev(ctx_, nullptr, e.d_, out.d_, e.batch_, e.L_, nullptr));
+        else
+            check(gsb_relinearize_sizes_dev(ctx_, nullptr, e.d_, e.size_, out.d_, e.batch_, e.L_, bfv_ ? 1 : 0, nullptr));
+        out.size_ = 2, out.L_ = e.L_, out.batch_ = e.batch_, out.parms_id_ = e.parms_id_, out.scale_ = e.scale_, out.ntt_ = e.ntt_;
         e = move(out);
     }
 
@@ -889,6 +926,8 @@ namespace gsb_seal
         own(e, "encrypted");
         if (context_->last_parms_id() == e.parms_id_) // evaluator.cpp:1093-1104
             throw invalid_argument("end of modulus switching chain reached");
+        if (bfv_) // evaluator.cpp:1106-1122
+            throw invalid_argument("unsupported operation for scheme type");
         if (!e.ntt_)
             throw invalid_argument("CKKS encrypted must be in NTT form");
         auto &context_data = *context_->get_context_data(e.parms_id_);
@@ -911,14 +950,70 @@ namespace gsb_seal
             throw invalid_argument("Galois element is not valid");
         if (e.size_ > 2)
             throw invalid_argument("encrypted size must be 2");
-        if (!e.ntt_)
-            throw logic_error("CKKS encrypted must be in NTT form");
+        if (e.ntt_ == bfv_)
+            throw logic_error(bfv_ ? "BFV encrypted cannot be in NTT form" : "CKKS encrypted must be in NTT form");
         ensure_galois(galois_keys, galois_elt);
         DeviceCiphertext out;
         out.reserve(ctx_, e.batch_ * 2 * e.L_ * N_);
-        check(gsb_apply_galois_dev(ctx_, nullptr, galois_elt, e.d_, out.d_, e.batch_, e.L_, nullptr));
-        out.size_ = 2, out.L_ = e.L_, out.batch_ = e.batch_, out.parms_id_ = e.parms_id_, out.scale_ = e.scale_, out.ntt_ = true;
+        check(bfv_ ? gsb_bfv_apply_galois_dev(ctx_, nullptr, galois_elt, e.d_, out.d_, e.batch_, e.L_, nullptr)
+                   : gsb_apply_galois_dev(ctx_, nullptr, galois_elt, e.d_, out.d_, e.batch_, e.L_, nullptr));
+        out.size_ = 2, out.L_ = e.L_, out.batch_ = e.batch_, out.parms_id_ = e.parms_id_, out.scale_ = e.scale_, out.ntt_ = e.ntt_;
         e = move(out);
+    }
+
+    // mod_switch_to_next (evaluator.cpp:996-1036): BFV divides and rounds by the last prime
+    // (mod_switch_scale_to_next, :829-892), CKKS drops the last limb (mod_switch_drop_to_next, :894-957)
+    void Evaluator::mod_switch_to_next_inplace(DeviceCiphertext &e)
+    {
+        own(e, "encrypted");
+        if (context_->last_parms_id() == e.parms_id_)
+            throw invalid_argument("end of modulus switching chain reached");
+        auto &context_data = *context_->get_context_data(e.parms_id_);
+        auto &next = *context_data.next_context_data();
+        if (e.ntt_ == bfv_)
+            throw invalid_argument(bfv_ ? "BFV encrypted cannot be in NTT form" : "CKKS encrypted must be in NTT form");
+        if (!bfv_ && (e.scale_ <= 0 || (static_cast<int>(log2(e.scale_)) >= next.total_coeff_modulus_bit_count())))
+            throw invalid_argument("scale out of bounds");
+        DeviceCiphertext out;
+        out.reserve(ctx_, e.batch_ * e.size_ * (e.L_ - 1) * N_);
+        check(bfv_ ? gsb_bfv_mod_switch_dev(ctx_, e.d_, out.d_, e.batch_, e.size_, e.L_, nullptr)
+                   : gsb_drop_last_limb_dev(ctx_, e.d_, out.d_, e.batch_ * e.size_, e.L_, nullptr));
+        out.size_ = e.size_, out.L_ = e.L_ - 1, out.batch_ = e.batch_, out.parms_id_ = next.parms_id(), out.scale_ = e.scale_, out.ntt_ = e.ntt_;
+        e = move(out);
+    }
+
+    // multiply_inplace + relinearize_inplace + rescale_to_next_inplace of size-2 CKKS handles as ONE device pass
+    // (gsb_mul_relin_rescale_dev: fused tail, nothing but the result leaves the pipeline); the checks of the three
+    // reference entry points in their order, the metadata of their composition.
+    void Evaluator::multiply_relinearize_rescale_inplace(DeviceCiphertext &e1, const DeviceCiphertext &e2, const RelinKeys &relin_keys)
+    {
+        own(e1, "encrypted1");
+        own(e2, "encrypted2");
+        if (bfv_)
+            throw invalid_argument("unsupported operation for scheme type");
+        if (e1.parms_id_ != e2.parms_id_)
+            throw invalid_argument("encrypted1 and encrypted2 parameter mismatch");
+        if (!(e1.ntt_ && e2.ntt_))
+            throw invalid_argument("encrypted1 or encrypted2 must be in NTT form");
+        auto &context_data = *context_->get_context_data(e1.parms_id_);
+        const double new_scale = e1.scale_ * e2.scale_;
+        if (new_scale <= 0 || (static_cast<int>(log2(new_scale)) >= context_data.total_coeff_modulus_bit_count()))
+            throw invalid_argument("scale out of bounds");
+        if (e1.size_ != 2 || e2.size_ != 2 || e1.batch_ != e2.batch_)
+            throw invalid_argument("the fused pass serves size-2 operands of equal batch");
+        if (relin_keys.parms_id() != context_->key_parms_id())
+            throw invalid_argument("relin_keys is not valid for encryption parameters");
+        if (relin_keys.size() < 1)
+            throw invalid_argument("not enough relinearization keys");
+        if (context_->last_parms_id() == e1.parms_id_)
+            throw invalid_argument("end of modulus switching chain reached");
+        ensure_relin(relin_keys, RelinKeys::get_index(2));
+        DeviceCiphertext out;
+        out.reserve(ctx_, e1.batch_ * 2 * (e1.L_ - 1) * N_);
+        check(gsb_mul_relin_rescale_dev(ctx_, nullptr, e1.d_, e2.d_, out.d_, e1.batch_, e1.L_, nullptr));
+        out.size_ = 2, out.L_ = e1.L_ - 1, out.batch_ = e1.batch_, out.parms_id_ = context_data.next_context_data()->parms_id();
+        out.scale_ = new_scale / static_cast<double>(context_data.parms().coeff_modulus().back().value()), out.ntt_ = true;
+        e1 = move(out);
     }
 
     void Evaluator::rotate_internal(DeviceCiphertext &e, int steps, const GaloisKeys &galois_keys)

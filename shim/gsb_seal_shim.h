@@ -29,7 +29,7 @@ namespace gsb_seal
     class Evaluator;
 
     // Device-resident ciphertext handle (no counterpart in the reference): the limbs
-    // of a CKKS ciphertext stay in HBM across evaluator calls, only the metadata lives on the host.
+    // of a CKKS or BFV ciphertext stay in HBM across evaluator calls, only the metadata lives on the host.
     // Evaluator::upload validates exactly as the reference's evaluator validates its operands
     // (is_metadata_valid_for + is_buffer_valid); the overloads below then run multiply / relinearize /
     // rescale / rotate / add / sub / negate without a host copy per operation; Evaluator::download gives
@@ -174,6 +174,10 @@ namespace gsb_seal
         void add_inplace(DeviceCiphertext &encrypted1, const DeviceCiphertext &encrypted2);
         void sub_inplace(DeviceCiphertext &encrypted1, const DeviceCiphertext &encrypted2);
         void negate_inplace(DeviceCiphertext &encrypted);
+        void mod_switch_to_next_inplace(DeviceCiphertext &encrypted);
+        // multiply + relinearize + rescale_to_next of size-2 CKKS handles as one fused device pass
+        void multiply_relinearize_rescale_inplace(
+            DeviceCiphertext &encrypted1, const DeviceCiphertext &encrypted2, const seal::RelinKeys &relin_keys);
 
         gsb_ctx *device_context() const { return ctx_; }
         // what the C layer's Evaluator_ContextUsingKeyswitching reports (c/evaluator.cpp:23-29)
@@ -198,8 +202,8 @@ namespace gsb_seal
         bool bfv_ = false;
         std::uint64_t plain_modulus_ = 0;
         std::mutex mu_;
-        // which host key object (by data pointer) currently sits in each device key slot
-        std::map<std::uint32_t, const void *> relin_loaded_, galois_loaded_;
+        // content fingerprint of the host key that currently sits in each device key slot
+        std::map<std::uint32_t, std::uint64_t> relin_loaded_, galois_loaded_;
     };
 
     // seal::Decryptor (decryptor.h:62-120 / decryptor.cpp:21-149, 218-265): the secret

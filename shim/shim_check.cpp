@@ -181,13 +181,85 @@ static int run(size_t N, vector<int> bits, int k_special)
                 same("device-resident batch of 3, element", want[i], got[i]);
         }
         expect_throw("device-resident level mismatch", [&] { dev.add_inplace(da, db); }, 0);
-        expect_throw("device-resident multiply of size 3", [&] {
-            gsb_seal::DeviceCiphertext x, y;
-            dev.upload(a, x);
-            dev.upload(b, y);
-            dev.multiply_inplace(x, y);
-            dev.multiply_inplace(x, y);
-        }, 1);
+    }
+    {
+        // general ciphertext sizes (evaluator.cpp:470-520, 772-827): callers that multiply before they relinearize
+        Ciphertext a1 = a, b1 = b;
+        a1.scale() = b1.scale() = pow(2.0, 8); // scale is metadata; keeps four factors inside the modulus
+        Ciphertext r3 = a1, d3 = a1;
+        ref.multiply_inplace(r3, b1);
+        dev.multiply_inplace(d3, b1);
+        Ciphertext r4 = r3, d4 = d3;
+        ref.multiply_inplace(r4, b1);
+        dev.multiply_inplace(d4, b1);
+        same("multiply size 3 x size 2", r4, d4);
+        Ciphertext r5 = r3, d5 = d3, r3c = r3;
+        r5.scale() = d5.scale() = r3c.scale() = pow(2.0, 4);
+        ref.multiply_inplace(r5, r3c);
+        dev.multiply_inplace(d5, r3c);
+        same("multiply size 3 x size 3", r5, d5);
+        Ciphertext r23 = b1, d23 = b1;
+        ref.multiply_inplace(r23, r3);
+        dev.multiply_inplace(d23, r3);
+        same("multiply size 2 x size 3", r23, d23);
+        // the public KeyGenerator makes the s^2 key only: size 4 cannot be relinearized, by either evaluator
+        expect_throw("relinearize size 4, one key", [&] { Ciphertext t = d4; dev.relinearize_inplace(t, rlk); }, 0);
+        // hand-built RelinKeys with keys for s^2, s^3, s^4 (limbs taken from Galois keys: the claim is equal words)
+        RelinKeys rl3 = rlk;
+        const uint32_t elt1 = context->key_context_data()->galois_tool()->get_elt_from_step(1);
+        rl3.data().push_back(glk.data()[GaloisKeys::get_index(elt1)]);
+        rl3.data().push_back(glk.data()[GaloisKeys::get_index(static_cast<uint32_t>(2 * N - 1))]);
+        Ciphertext r4b = r4, d4b = d4;
+        ref.relinearize_inplace(r4b, rl3);
+        dev.relinearize_inplace(d4b, rl3);
+        same("relinearize size 4 -> 2", r4b, d4b);
+        ref.relinearize_inplace(r5, rl3);
+        dev.relinearize_inplace(d5, rl3);
+        same("relinearize size 5 -> 2", r5, d5);
+        gsb_seal::DeviceCiphertext x, y;
+        dev.upload(a1, x);
+        dev.upload(b1, y);
+        dev.multiply_inplace(x, y);
+        dev.multiply_inplace(x, y);
+        dev.relinearize_inplace(x, rl3);
+        Ciphertext back;
+        dev.download(x, back);
+        same("device-resident size 4 chain", r4b, back);
+    }
+    {
+        // key identity is decided by content, not by address: new key words written into the SAME
+        // RelinKeys storage the evaluator has already uploaded from
+        RelinKeys rl = rlk;
+        Ciphertext r3 = a, d3 = a;
+        ref.multiply_inplace(r3, b);
+        dev.multiply_inplace(d3, b);
+        Ciphertext t1 = d3;
+        dev.relinearize_inplace(t1, rl); // uploads rl
+        KeyGenerator keygen2(context);
+        RelinKeys other = keygen2.relin_keys_local();
+        for (size_t j = 0; j < rl.data()[0].size(); j++)
+        {
+            auto &dst = rl.data()[0][j].data();
+            memcpy(dst.data(), other.data()[0][j].data().data(), dst.size() * dst.coeff_modulus_size() * dst.poly_modulus_degree() * sizeof(uint64_t));
+        }
+        ref.relinearize_inplace(r3, rl);
+        dev.relinearize_inplace(d3, rl);
+        same("relinearize after in-place key reload", r3, d3);
+    }
+    {
+        // fused device-resident chain and mod_switch_to_next on handles
+        gsb_seal::DeviceCiphertext x, y;
+        dev.upload(a, x);
+        dev.upload(b, y);
+        dev.multiply_relinearize_rescale_inplace(x, y, rlk);
+        dev.mod_switch_to_next_inplace(x);
+        Ciphertext want = a, back;
+        ref.multiply_inplace(want, b);
+        ref.relinearize_inplace(want, rlk);
+        ref.rescale_to_next_inplace(want);
+        ref.mod_switch_to_next_inplace(want);
+        dev.download(x, back);
+        same("handles: fused mul+relin+rescale, mod_switch", want, back);
     }
     {
         Ciphertext r2 = a, d2 = a;
@@ -399,6 +471,38 @@ static int run_bfv(size_t N)
         }
         expect_throw("multiply_many(empty)", [&] { vector<Ciphertext> e; Ciphertext t; dev.multiply_many(e, rlk, t); }, 0);
         expect_throw("exponentiate(0)", [&] { Ciphertext t = a; dev.exponentiate_inplace(t, 0, rlk); }, 0);
+    }
+    {
+        // general sizes and device-resident handles, BFV
+        Ciphertext r3 = a, d3 = a;
+        ref.multiply_inplace(r3, b);
+        dev.multiply_inplace(d3, b);
+        Ciphertext r4 = r3, d4 = d3;
+        ref.multiply_inplace(r4, b);
+        dev.multiply_inplace(d4, b);
+        same("BFV multiply size 3 x size 2", r4, d4);
+        RelinKeys rl2 = rlk;
+        const uint32_t elt1 = context->key_context_data()->galois_tool()->get_elt_from_step(1);
+        rl2.data().push_back(glk.data()[GaloisKeys::get_index(elt1)]);
+        ref.relinearize_inplace(r4, rl2);
+        dev.relinearize_inplace(d4, rl2);
+        same("BFV relinearize size 4 -> 2", r4, d4);
+        gsb_seal::DeviceCiphertext x, y;
+        dev.upload(a, x);
+        dev.upload(b, y);
+        dev.multiply_inplace(x, y);
+        dev.relinearize_inplace(x, rlk);
+        dev.mod_switch_to_next_inplace(x);
+        dev.apply_galois_inplace(x, elt1, glk);
+        dev.add_inplace(x, x);
+        Ciphertext want = a, back;
+        ref.multiply_inplace(want, b);
+        ref.relinearize_inplace(want, rlk);
+        ref.mod_switch_to_next_inplace(want);
+        ref.apply_galois_inplace(want, elt1, glk);
+        ref.add_inplace(want, want);
+        dev.download(x, back);
+        same("BFV device-resident chain (5 ops)", want, back);
     }
     expect_throw("BFV rotate_vector (CKKS only)", [&] { Ciphertext t = a; dev.rotate_vector_inplace(t, 1, glk); }, 1);
     return failures;

@@ -24,7 +24,7 @@ def main():
     ref = pyoracle.RefLib()
     be = golden_cases.RefBackend(ref)
     cases = {}
-    for name in list(golden_cases.NTT) + list(golden_cases.EVAL) + list(golden_cases.BFV):
+    for name in list(golden_cases.NTT) + list(golden_cases.EVAL) + list(golden_cases.BFV) + list(golden_cases.GEN):
         cases[name] = golden_cases.run_case(name, be)
         print(name, "ok", flush=True)
     out = {

@@ -58,13 +58,26 @@ BFV = {
     "bfv_n4096_L1": (12, BFV_DEFAULT[4096], 1, 1, 1, 1, 65537),
 }
 
+# General ciphertext sizes (evaluator.cpp:470-520, :274-445, :772-827): multiply of a size-sa by a size-sb ciphertext,
+# then relinearization from size sa + sb - 1 to 2 with synthetic keys for s^2 .. s^(sa+sb-2).
+# name -> (logn, moduli spec, k special, level L, batch, sa, sb, plain modulus or None for CKKS)
+GEN = {
+    "gen_n2048_k1_L3_3x2": (11, [50, 40, 45, 51], 1, 3, 2, 3, 2, None),
+    "gen_n1024_k2_L4_2x4": (10, [45, 45, 45, 45, 46, 46], 2, 4, 1, 2, 4, None),
+    "gen_n8192_L4_3x3": (13, BFV_DEFAULT[8192], 1, 4, 1, 3, 3, None),
+    "gen_n32768_L15_3x2": (15, BFV_DEFAULT[32768], 1, 15, 1, 3, 2, None),
+    "gen_bfv_n2048_3x2": (11, [50, 40, 45, 51], 1, 3, 2, 3, 2, 65537),
+    "gen_bfv_n4096_2x3": (12, BFV_DEFAULT[4096], 1, 2, 1, 2, 3, 786433),
+    "gen_bfv_n8192_3x3": (13, BFV_DEFAULT[8192], 1, 4, 1, 3, 3, 786433),
+}
+
 # (logn, bits): 3 polys x 3 limbs, all four transforms
 NTT = {"ntt_n%d_b%d" % (ln, b): (ln, b) for ln in (10, 11, 12, 13, 14, 15, 16) for b in (30, 59)}
 NTT["ntt_n12_b60_wrap"] = (12, 60)  # lazy forward transform wraps mod 2^64
 NTT["ntt_n15_b60_wrap"] = (15, 60)
 
 SMALL = ([n for n, c in EVAL.items() if c[0] <= 12] + [n for n, c in NTT.items() if c[0] <= 13] +
-         [n for n, c in BFV.items() if c[0] <= 12])
+         [n for n, c in BFV.items() if c[0] <= 12] + [n for n, c in GEN.items() if c[0] <= 12])
 
 
 def case_seed(name):
@@ -98,6 +111,18 @@ def bfv_inputs(name):
         sk=rand_poly(rng, mods, (), N))
 
 
+def gen_inputs(name):
+    logn, spec, k, L, batch, sa, sb, t = GEN[name]
+    N = 1 << logn
+    mods = list(spec) if spec[0] > 64 else mixed_moduli(logn, spec)
+    rng = np.random.default_rng(case_seed(name))
+    nb = (len(mods) - k + k - 1) // k
+    return dict(
+        logn=logn, N=N, mods=mods, k=k, L=L, batch=batch, t=t,
+        a=rand_poly(rng, mods[:L], (batch, sa), N), b=rand_poly(rng, mods[:L], (batch, sb), N),
+        relin=[rand_key(rng, mods, nb, N) for _ in range(sa + sb - 3)])  # relin[p] = key of s^(p + 2)
+
+
 def ntt_inputs(name):
     logn, bits = NTT[name]
     mods = ntt_primes(logn, bits, 3)
@@ -111,6 +136,14 @@ def run_case(name, be):
         c = ntt_inputs(name)
         for kind in range(4):
             out["kind%d" % kind] = digest(be.ntt(c["logn"], c["mods"], c["x"], kind))
+        return out
+    if name in GEN:
+        c = gen_inputs(name)
+        be.setup(c["logn"], c["mods"], c["k"], bfv_t=c["t"])
+        be.set_relin_powers(c["relin"])
+        prod = be.multiply(c["a"], c["b"])
+        out["multiply"] = digest(prod)
+        out["relinearize"] = digest(be.relinearize(prod))
         return out
     if name in BFV:
         c = bfv_inputs(name)
@@ -184,16 +217,18 @@ class OracleBackend(_PerCt):
 
     def set_keys(self, relin, elt, galois, elt2=None, galois2=None):
         self.relin, self.gal = relin, {elt: galois, elt2: galois2}
+        self.relin_all = np.ascontiguousarray(relin[None])
+
+    def set_relin_powers(self, keys):
+        self.relin, self.relin_all = keys[0], np.ascontiguousarray(np.stack(keys))
 
     def multiply(self, a, b):
         if self.t is not None:
-            return self.each(lambda x, y: self.o.bfv_multiply(self.logn, self.mods, self.t, x, y), a, b)
-        return self.each(self.c.multiply, a, b)
+            return self.each(lambda x, y: self.o.bfv_multiply_sizes(self.logn, self.mods, self.t, x, y), a, b)
+        return self.each(self.c.multiply_sizes, a, b)
 
     def relinearize(self, c3):
-        if self.t is not None:
-            return self.each(lambda x: self.c.relinearize_bfv(x, self.relin), c3)
-        return self.each(lambda x: self.c.relinearize(x, self.relin), c3)
+        return self.each(lambda x: self.c.relinearize_sizes(x, self.relin_all, bfv=self.t is not None), c3)
 
     def rescale(self, c):
         return self.each(self.c.rescale, c)
@@ -245,11 +280,17 @@ class RefBackend(_PerCt):
         if elt2 is not None:
             self.c.set_key(1, elt2, galois2)
 
+    def set_relin_powers(self, keys):
+        self.c.set_relin_count(len(keys))
+        self.c.keygen([])
+        for p, key in enumerate(keys):
+            self.c.set_key(0, p, key)
+
     def multiply(self, a, b):
-        return self.each(self.c.multiply, a, b)
+        return self.each(self.c.multiply_sizes, a, b)
 
     def relinearize(self, c3):
-        return self.each(self.c.relinearize, c3)
+        return self.each(self.c.relinearize_sizes, c3)
 
     def rescale(self, c):
         return self.each(self.c.rescale, c)
@@ -301,6 +342,10 @@ class DeviceBackend:
         self.ctx.set_galois_key(elt, galois)
         if elt2 is not None:
             self.ctx.set_galois_key(elt2, galois2)
+
+    def set_relin_powers(self, keys):
+        for p, key in enumerate(keys):
+            self.ctx.set_relin_keys(key, key_power=p + 2)
 
     def multiply(self, a, b):
         return self.ev.multiply(a, b)

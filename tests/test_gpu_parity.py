@@ -18,7 +18,7 @@ with open(os.path.join(os.path.dirname(__file__), "golden", "evaluator_digests.j
     GOLDEN = json.load(f)["cases"]
 
 
-@pytest.mark.parametrize("name", list(golden_cases.NTT) + list(golden_cases.EVAL) + list(golden_cases.BFV))
+@pytest.mark.parametrize("name", list(golden_cases.NTT) + list(golden_cases.EVAL) + list(golden_cases.BFV) + list(golden_cases.GEN))
 def test_matches_reference_digests(cudalib, name):
     got = golden_cases.run_case(name, golden_cases.DeviceBackend(cudalib))
     assert got == GOLDEN[name]

@@ -13,7 +13,7 @@ import golden_cases
 with open(os.path.join(os.path.dirname(__file__), "golden", "evaluator_digests.json")) as f:
     GOLDEN = json.load(f)["cases"]
 
-SIM_CASES = golden_cases.SMALL + ["n8192_k2_L3", "ntt_n14_b59", "bfv_n8192_default"]
+SIM_CASES = golden_cases.SMALL + ["n8192_k2_L3", "ntt_n14_b59", "bfv_n8192_default", "gen_n8192_L4_3x3"]
 
 
 @pytest.mark.parametrize("name", SIM_CASES)
