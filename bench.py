@@ -498,6 +498,20 @@ def cpu_legs(w, rc, threads):
     return out
 
 
+def shim_numbers():
+    """The drop-in C++ boundary measured by shim/shim_bench.cpp (gsb_seal::Evaluator beside seal::Evaluator on real
+    seal objects): per-call latencies and the throughput of the batched device-resident route.  None where the
+    binary (built against /root/reference) did not travel."""
+    exe = os.path.join(ROOT, "oracle", "_ref", "shim_bench")
+    if not os.path.exists(exe):
+        return None
+    try:
+        p = subprocess.run([exe, "64", "7", "2"], capture_output=True, text=True, timeout=600)
+        return json.loads(p.stdout.strip().splitlines()[-1])
+    except (OSError, subprocess.TimeoutExpired, ValueError, IndexError) as e:
+        return {"error": str(e)}
+
+
 def run_ours(args):
     import numpy as np
     import torch
@@ -714,6 +728,9 @@ def run_ours(args):
             cpu = {"value": 2 / secs, "unit": "ops/s", "cores": 1, "kind": "port", "sample": "2 mul+relin+rescale ops, oracle port, 1 thread"}
     del rc
 
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        ctx.close()  # the shim program creates its own context and a 16 GiB workspace
+        extra["shim"] = shim_numbers()
     if rank == 0:
         line = {
             "metric": METRIC, "value": value, "unit": "ops/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),

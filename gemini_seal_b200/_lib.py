@@ -44,6 +44,7 @@ PROTOTYPES = {
     "gsb_poly_op_dev": (i32, [vp, i32, vp, vp, u64p, vp, sz, sz, sz, vp]),
     "gsb_poly_op_host": (i32, [vp, i32, vp, vp, u64p, vp, sz, sz, sz]),
     "gsb_key_upload": (i32, [vp, i32, u32, vp, sz]),
+    "gsb_key_upload_bundles": (i32, [vp, i32, u32, C.POINTER(vp), sz]),
     "gsb_key_drop": (i32, [vp, i32, u32]),
     "gsb_galois_elt_from_step": (i32, [vp, i32, C.POINTER(u32)]),
     "gsb_galois_table": (i32, [vp, u32, C.POINTER(u32)]),

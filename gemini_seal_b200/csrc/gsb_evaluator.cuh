@@ -705,47 +705,60 @@ int gsb_poly_op_host(
     return g != GSB_OK ? g : rc;
 }
 
-int gsb_key_upload(gsb_ctx *ctx, int kind, uint32_t galois_elt, const uint64_t *key_host, size_t n_bundles)
+// Key upload: the bundles go to the device as they are (one plain H2D copy each); a kernel then checks every
+// word against its limb's modulus (is_buffer_valid, valcheck.cpp) and permutes the 16-byte units inside every
+// 1 KiB block into the bank-conflict-free device layout (key_word_pos, ntt_core.cuh) in place.
+int gsb_key_upload_bundles(gsb_ctx *ctx, int kind, uint32_t galois_elt, const uint64_t *const *bundles, size_t n_bundles)
 {
     return guarded([&] {
-        require(ctx != nullptr && key_host != nullptr, GSB_E_INVALID_ARG, "null argument");
+        require(ctx != nullptr && bundles != nullptr, GSB_E_INVALID_ARG, "null argument");
         require(kind == GSB_KEY_RELIN || kind == GSB_KEY_GALOIS, GSB_E_INVALID_ARG, "key kind");
         require(ctx->K > ctx->k, GSB_E_LOGIC, "keyswitching is not supported by the context");
         // keygenerator.cpp:333-343: one PublicKey per bundle of the first-level modulus
         const size_t beta0 = (ctx->L0 + ctx->k - 1) / ctx->k;
         require(n_bundles == beta0, GSB_E_INVALID_ARG, "kswitch_keys is not valid for encryption parameters");
+        for (size_t j = 0; j < n_bundles; j++)
+            require(bundles[j] != nullptr, GSB_E_INVALID_ARG, "null argument");
         if (kind == GSB_KEY_GALOIS)
             (void)ctx->galois_table(galois_elt); // validates the element and builds its permutation
         GSB_CUDA_CHECK(cudaSetDevice(ctx->device));
-        const size_t words = n_bundles * 2 * ctx->K * ctx->N;
-        // is_buffer_valid (valcheck.cpp): every key word must be a canonical residue
-        for (size_t j = 0; j < n_bundles * 2; j++)
-            for (size_t i = 0; i < ctx->K; i++)
-            {
-                const uint64_t q = ctx->tables[i].mod.q;
-                const uint64_t *p = key_host + (j * ctx->K + i) * ctx->N;
-                for (size_t d = 0; d < ctx->N; d++)
-                    require(p[d] < q, GSB_E_INVALID_ARG, "kswitch_keys is not valid for encryption parameters");
-            }
-        // device layout: 16-byte units swizzled inside every 1 KiB block (key_word_pos, ntt_core.cuh)
-        std::vector<uint64_t> perm(words);
-        for (size_t row = 0; row < n_bundles * 2 * ctx->K; row++)
-        {
-            const uint64_t *src = key_host + row * ctx->N;
-            uint64_t *dst = perm.data() + row * ctx->N;
-            for (size_t w = 0; w < ctx->N; w++)
-                dst[key_word_pos(static_cast<uint32_t>(w))] = src[w];
-        }
+        const size_t per = 2 * ctx->K * ctx->N, words = n_bundles * per;
         uint64_t *d = nullptr;
-        GSB_CUDA_CHECK(cudaMalloc(reinterpret_cast<void **>(&d), words * sizeof(uint64_t)));
-        GSB_CUDA_CHECK(cudaMemcpy(d, perm.data(), words * sizeof(uint64_t), cudaMemcpyHostToDevice));
+        int *d_bad = nullptr;
+        GSB_CUDA_CHECK(cudaMalloc(reinterpret_cast<void **>(&d), words * sizeof(uint64_t) + 256));
+        d_bad = reinterpret_cast<int *>(d + words);
+        struct Guard // frees the allocation unless the upload succeeded
+        {
+            uint64_t *p;
+            ~Guard() { cudaFree(p); }
+        } guard{ d };
+        GSB_CUDA_CHECK(cudaMemsetAsync(d_bad, 0, sizeof(int), nullptr));
+        for (size_t j = 0; j < n_bundles; j++)
+            GSB_CUDA_CHECK(cudaMemcpyAsync(d + j * per, bundles[j], per * sizeof(uint64_t), cudaMemcpyHostToDevice, nullptr));
+        KeySwizzleArgs a{ d, ctx->d_limb, static_cast<uint32_t>(ctx->N), static_cast<uint32_t>(ctx->K), words / 128, d_bad };
+        GSB_LAUNCH("key_swizzle", "", key_swizzle_kernel, dim3(grid_for(a.blocks * 64, 256)), dim3(256), 0, nullptr, a);
+        int bad = 0;
+        GSB_CUDA_CHECK(cudaMemcpyAsync(&bad, d_bad, sizeof(int), cudaMemcpyDeviceToHost, nullptr));
+        GSB_CUDA_CHECK(cudaStreamSynchronize(nullptr));
+        require(bad == 0, GSB_E_INVALID_ARG, "kswitch_keys is not valid for encryption parameters");
         std::lock_guard<std::mutex> lock(ctx->mu);
         SwitchKey &slot = kind == GSB_KEY_RELIN ? ctx->relin[galois_elt] : ctx->galois[galois_elt];
         if (slot.d)
             cudaFree(slot.d);
         slot.d = d;
         slot.bundles = n_bundles;
+        guard.p = nullptr;
     });
+}
+
+int gsb_key_upload(gsb_ctx *ctx, int kind, uint32_t galois_elt, const uint64_t *key_host, size_t n_bundles)
+{
+    if (ctx == nullptr || key_host == nullptr || n_bundles == 0 || n_bundles > 64)
+        return guarded([&] { require(false, GSB_E_INVALID_ARG, ctx && key_host ? "kswitch_keys is not valid for encryption parameters" : "null argument"); });
+    const uint64_t *ptrs[64];
+    for (size_t j = 0; j < n_bundles; j++)
+        ptrs[j] = key_host + j * 2 * ctx->K * ctx->N;
+    return gsb_key_upload_bundles(ctx, kind, galois_elt, ptrs, n_bundles);
 }
 
 int gsb_key_drop(gsb_ctx *ctx, int kind, uint32_t galois_elt)

@@ -866,6 +866,46 @@ namespace gsb
         }
     }
 
+    // ---- switching-key upload: validity check + device layout ------------------------------------------
+    // key = [rows][N] words as copied from the host (rows = bundles * 2 * K, row r uses modulus r % K).  64
+    // threads own one block of 64 16-byte units: each loads its unit, checks both words against the modulus
+    // (is_buffer_valid / is_data_valid_for, valcheck.cpp) and, after the CTA barrier, stores it at unit
+    // swz8(u) of the same block (key_word_pos, ntt_core.cuh) -- an in-place permutation inside the block.
+    struct KeySwizzleArgs
+    {
+        uint64_t *key;
+        const LimbC *limb;
+        uint32_t N, K;
+        size_t blocks; // rows * N / 128
+        int *bad;      // set to 1 if any word is not a canonical residue
+    };
+
+    __global__ void __launch_bounds__(256) key_swizzle_kernel(KeySwizzleArgs p)
+    {
+        const size_t units = p.blocks * 64, stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+        // every thread of a CTA runs the same number of iterations (units is a multiple of 64, the stride of 256)
+        for (size_t base = static_cast<size_t>(blockIdx.x) * blockDim.x; base < units; base += stride)
+        {
+            const size_t u = base + threadIdx.x;
+            ulonglong2 v = make_ulonglong2(0, 0);
+            const bool live = u < units;
+            if (live)
+            {
+                v = *reinterpret_cast<const ulonglong2 *>(p.key + 2 * u);
+                const uint64_t q = p.limb[((2 * u) / p.N) % p.K].q;
+                if (v.x >= q || v.y >= q)
+                    *p.bad = 1;
+            }
+            __syncthreads();
+            if (live)
+            {
+                const size_t dst = (u & ~static_cast<size_t>(63)) | swz8(static_cast<uint32_t>(u & 63));
+                *reinterpret_cast<ulonglong2 *>(p.key + 2 * dst) = v;
+            }
+            __syncthreads();
+        }
+    }
+
     // ---- NTT-form Galois gather (GaloisTool::apply_galois_ntt, util/galois.cpp:188-214) ------------
     // out[z][i][d] = in[z*in_zs + i*N + table[d]] for z < n, i < L.
     struct GatherArgs

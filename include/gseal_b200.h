@@ -127,6 +127,9 @@ int gsb_poly_op_host(
  * relinearizes size 3 -> 2; relinkeys.h:61).  The context keeps a device copy until gsb_key_drop /
  * gsb_ctx_destroy.  Uploading also builds the Galois permutation table (util/galois.cpp:18-47). */
 int gsb_key_upload(gsb_ctx *ctx, int kind, uint32_t galois_elt, const uint64_t *key_host, size_t n_bundles);
+/* The same with one pointer per bundle (what the C++ shim passes: keys.data()[index][j].data().data()), so the
+ * caller does not have to flatten a 120 MiB key first.  bundles[j] = [2][K][N]. */
+int gsb_key_upload_bundles(gsb_ctx *ctx, int kind, uint32_t galois_elt, const uint64_t *const *bundles, size_t n_bundles);
 int gsb_key_drop(gsb_ctx *ctx, int kind, uint32_t galois_elt);
 /* GaloisTool::get_elt_from_step (util/galois.cpp:49-91); GSB_E_INVALID_ARG for |step| >= N/2 */
 int gsb_galois_elt_from_step(const gsb_ctx *ctx, int step, uint32_t *elt);

@@ -65,8 +65,10 @@ namespace gsb_seal
         check(gsb_ctx_create(device, logn, moduli.data(), K_, k_, &ctx_));
     }
 
+    static void drop_pool(gsb_ctx *ctx);
     Evaluator::~Evaluator()
     {
+        drop_pool(ctx_);
         gsb_ctx_destroy(ctx_);
     }
 
@@ -351,16 +353,15 @@ namespace gsb_seal
     // ---- key upload ---------------------------------------------------------------------------------
     void Evaluator::upload_key(int kind, uint32_t slot, const vector<PublicKey> &bundles)
     {
-        const size_t per = 2 * K_ * N_;
-        vector<uint64_t> flat(bundles.size() * per);
+        vector<const uint64_t *> ptrs;
         for (size_t j = 0; j < bundles.size(); j++)
         {
             // evaluator.cpp:2283-2290: only the used component is validated
             if (!is_metadata_valid_for(bundles[j], context_) || !is_buffer_valid(bundles[j]) || bundles[j].data().size() != 2)
                 throw invalid_argument("kswitch_keys is not valid for encryption parameters");
-            memcpy(flat.data() + j * per, bundles[j].data().data(), per * sizeof(uint64_t));
+            ptrs.push_back(bundles[j].data().data());
         }
-        check(gsb_key_upload(ctx_, kind, slot, flat.data(), bundles.size()));
+        check(gsb_key_upload_bundles(ctx_, kind, slot, ptrs.data(), ptrs.size()));
     }
 
     // Which host key sits in a device slot is decided by CONTENT, not by address: SEAL's MemoryPool hands a freed
@@ -772,10 +773,27 @@ namespace gsb_seal
         }
         return *this;
     }
+    // Buffers of released handles are kept per device context and handed to the next handle that fits, so a chain
+    // of handle operations does not pay a cudaMalloc + cudaFree (a device-wide synchronisation) per operation.
+    // Everything runs on the default stream, hence reuse is ordered after the previous owner's kernels.
+    namespace
+    {
+        mutex g_pool_mu;
+        map<gsb_ctx *, vector<pair<uint64_t *, size_t>>> g_pool; // live contexts only
+        constexpr size_t kPoolMax = 8;
+    } // namespace
+
     void DeviceCiphertext::release()
     {
         if (d_)
-            gsb_free(ctx_, d_);
+        {
+            lock_guard<mutex> lock(g_pool_mu);
+            auto it = g_pool.find(ctx_);
+            if (it != g_pool.end() && it->second.size() < kPoolMax)
+                it->second.emplace_back(d_, cap_);
+            else
+                gsb_free(ctx_, d_);
+        }
         d_ = nullptr;
         cap_ = 0;
     }
@@ -784,9 +802,33 @@ namespace gsb_seal
         if (ctx_ == ctx && cap_ >= words)
             return;
         release();
+        {
+            lock_guard<mutex> lock(g_pool_mu);
+            auto &v = g_pool[ctx];
+            size_t best = v.size();
+            for (size_t i = 0; i < v.size(); i++)
+                if (v[i].second >= words && v[i].second <= 2 * words + 4096 && (best == v.size() || v[i].second < v[best].second))
+                    best = i;
+            if (best != v.size())
+            {
+                ctx_ = ctx, d_ = v[best].first, cap_ = v[best].second;
+                v.erase(v.begin() + static_cast<ptrdiff_t>(best));
+                return;
+            }
+        }
         void *p = nullptr;
         check(gsb_malloc(ctx, words * sizeof(uint64_t), &p));
         ctx_ = ctx, d_ = static_cast<uint64_t *>(p), cap_ = words;
+    }
+    static void drop_pool(gsb_ctx *ctx)
+    {
+        lock_guard<mutex> lock(g_pool_mu);
+        auto it = g_pool.find(ctx);
+        if (it == g_pool.end())
+            return;
+        for (auto &b : it->second)
+            gsb_free(ctx, b.first);
+        g_pool.erase(it); // handles that outlive their evaluator free their buffer directly
     }
 
     void Evaluator::own(const DeviceCiphertext &ct, const char *what) const

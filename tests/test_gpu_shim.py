@@ -74,3 +74,24 @@ def test_c_export_layer_against_simulator(simlib):
     p = subprocess.run([CBIN], capture_output=True, text=True, timeout=900, env=env)
     assert p.returncode == 0, p.stdout[-3000:] + p.stderr[-1000:]
     assert "C_LAYER_CHECK PASS" in p.stdout
+
+
+SBIN = os.path.join(ROOT, "oracle", "_ref", "shim_bench")
+
+
+@pytest.mark.gpu
+def test_shim_bench_on_device():
+    """The measurement program of the C++ boundary (shim/shim_bench.cpp) at a reduced batch: every timed result is
+    compared with seal::Evaluator inside the program (parity_ok), and the JSON line it prints is what bench.py embeds
+    as extra.shim."""
+    import json
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    if not os.path.exists(SBIN):
+        pytest.skip("oracle/_ref/shim_bench not built (needs /root/reference at build time)")
+    p = subprocess.run([SBIN, "8", "3", "1"], capture_output=True, text=True, timeout=900)
+    assert p.returncode == 0, p.stdout[-3000:] + p.stderr[-1000:]
+    line = json.loads(p.stdout.strip().splitlines()[-1])
+    print(json.dumps(line))
+    assert line["parity_ok"] is True and line["chain_ops_per_s"] > 0
