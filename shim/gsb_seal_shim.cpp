@@ -1221,33 +1221,97 @@ namespace gsb_seal
                 g_ctx[key] = c;
                 return c;
             }
+
+            // one multi-modulus device context per (log2 N, moduli of the tables array): an RNS or Poly overload is
+            // ONE batched device pass over all its limbs (and polynomials), not a call per limb
+            map<pair<int, vector<uint64_t>>, gsb_ctx *> g_rns_ctx;
+
+            gsb_ctx *ctx_for(seal::util::ConstNTTTablesIter tables, size_t count)
+            {
+                if (count == 0)
+                    throw invalid_argument("coeff_modulus_size");
+                const seal::util::NTTTables *t = *tables;
+                if (count == 1)
+                    return ctx_for(t[0]);
+                vector<uint64_t> q(count);
+                for (size_t i = 0; i < count; i++)
+                {
+                    if (t[i].coeff_count_power() != t[0].coeff_count_power())
+                        throw invalid_argument("tables");
+                    q[i] = t[i].modulus().value();
+                }
+                lock_guard<mutex> lock(g_mu);
+                const auto key = make_pair(t[0].coeff_count_power(), q);
+                auto it = g_rns_ctx.find(key);
+                if (it != g_rns_ctx.end())
+                    return it->second;
+                gsb_ctx *c = nullptr;
+                check(gsb_ctx_create(0, key.first, q.data(), count, 1, &c));
+                g_rns_ctx[key] = c;
+                return c;
+            }
+
+            void run(bool inverse, int mode, uint64_t *data, size_t n_polys, size_t n_limbs, gsb_ctx *c)
+            {
+                check(inverse ? gsb_ntt_inverse_host(c, data, n_polys, n_limbs, 0, mode) : gsb_ntt_forward_host(c, data, n_polys, n_limbs, 0, mode));
+            }
+            // a PolyIter walks polynomials that lie back to back (step = N * coeff_modulus_size, iterator.h:1099-1102)
+            void run_poly(bool inverse, int mode, seal::util::PolyIter operand, size_t size, seal::util::ConstNTTTablesIter tables)
+            {
+                if (size == 0)
+                    return;
+                run(inverse, mode, **(*operand), size, operand.coeff_modulus_size(), ctx_for(tables, operand.coeff_modulus_size()));
+            }
         } // namespace
 
-        void ntt_negacyclic_harvey(uint64_t *operand, const seal::util::NTTTables &tables)
+        // util/ntt.h:189-368: CoeffIter / RNSIter / PolyIter x lazy / strict x forward / inverse
+        void ntt_negacyclic_harvey_lazy(seal::util::CoeffIter operand, const seal::util::NTTTables &tables)
         {
-            check(gsb_ntt_forward_host(ctx_for(tables), operand, 1, 1, 0, GSB_NTT_STRICT));
+            run(false, GSB_NTT_LAZY, *operand, 1, 1, ctx_for(tables));
         }
-        void ntt_negacyclic_harvey_lazy(uint64_t *operand, const seal::util::NTTTables &tables)
+        void ntt_negacyclic_harvey_lazy(seal::util::RNSIter operand, size_t coeff_modulus_size, seal::util::ConstNTTTablesIter tables)
         {
-            check(gsb_ntt_forward_host(ctx_for(tables), operand, 1, 1, 0, GSB_NTT_LAZY));
+            run(false, GSB_NTT_LAZY, **operand, 1, coeff_modulus_size, ctx_for(tables, coeff_modulus_size));
         }
-        void inverse_ntt_negacyclic_harvey(uint64_t *operand, const seal::util::NTTTables &tables)
+        void ntt_negacyclic_harvey_lazy(seal::util::PolyIter operand, size_t size, seal::util::ConstNTTTablesIter tables)
         {
-            check(gsb_ntt_inverse_host(ctx_for(tables), operand, 1, 1, 0, GSB_NTT_STRICT));
+            run_poly(false, GSB_NTT_LAZY, operand, size, tables);
         }
-        void inverse_ntt_negacyclic_harvey_lazy(uint64_t *operand, const seal::util::NTTTables &tables)
+        void ntt_negacyclic_harvey(seal::util::CoeffIter operand, const seal::util::NTTTables &tables)
         {
-            check(gsb_ntt_inverse_host(ctx_for(tables), operand, 1, 1, 0, GSB_NTT_LAZY));
+            run(false, GSB_NTT_STRICT, *operand, 1, 1, ctx_for(tables));
         }
-        void ntt_negacyclic_harvey(uint64_t *operand, size_t coeff_modulus_size, const seal::util::NTTTables *tables)
+        void ntt_negacyclic_harvey(seal::util::RNSIter operand, size_t coeff_modulus_size, seal::util::ConstNTTTablesIter tables)
         {
-            for (size_t i = 0; i < coeff_modulus_size; i++)
-                ntt_negacyclic_harvey(operand + (i << tables[i].coeff_count_power()), tables[i]);
+            run(false, GSB_NTT_STRICT, **operand, 1, coeff_modulus_size, ctx_for(tables, coeff_modulus_size));
         }
-        void inverse_ntt_negacyclic_harvey(uint64_t *operand, size_t coeff_modulus_size, const seal::util::NTTTables *tables)
+        void ntt_negacyclic_harvey(seal::util::PolyIter operand, size_t size, seal::util::ConstNTTTablesIter tables)
         {
-            for (size_t i = 0; i < coeff_modulus_size; i++)
-                inverse_ntt_negacyclic_harvey(operand + (i << tables[i].coeff_count_power()), tables[i]);
+            run_poly(false, GSB_NTT_STRICT, operand, size, tables);
+        }
+        void inverse_ntt_negacyclic_harvey_lazy(seal::util::CoeffIter operand, const seal::util::NTTTables &tables)
+        {
+            run(true, GSB_NTT_LAZY, *operand, 1, 1, ctx_for(tables));
+        }
+        void inverse_ntt_negacyclic_harvey_lazy(seal::util::RNSIter operand, size_t coeff_modulus_size, seal::util::ConstNTTTablesIter tables)
+        {
+            run(true, GSB_NTT_LAZY, **operand, 1, coeff_modulus_size, ctx_for(tables, coeff_modulus_size));
+        }
+        void inverse_ntt_negacyclic_harvey_lazy(seal::util::PolyIter operand, size_t size, seal::util::ConstNTTTablesIter tables)
+        {
+            run_poly(true, GSB_NTT_LAZY, operand, size, tables);
+        }
+        void inverse_ntt_negacyclic_harvey(seal::util::CoeffIter operand, const seal::util::NTTTables &tables)
+        {
+            run(true, GSB_NTT_STRICT, *operand, 1, 1, ctx_for(tables));
+        }
+        void inverse_ntt_negacyclic_harvey(seal::util::RNSIter operand, size_t coeff_modulus_size, seal::util::ConstNTTTablesIter tables)
+        {
+            run(true, GSB_NTT_STRICT, **operand, 1, coeff_modulus_size, ctx_for(tables, coeff_modulus_size));
+        }
+        void inverse_ntt_negacyclic_harvey(seal::util::PolyIter operand, size_t size, seal::util::ConstNTTTablesIter tables)
+        {
+            run_poly(true, GSB_NTT_STRICT, operand, size, tables);
         }
     } // namespace util
 } // namespace gsb_seal

@@ -17,6 +17,7 @@
 #pragma once
 #include "gseal_b200.h"
 #include "seal/seal.h"
+#include "seal/util/iterator.h"
 #include "seal/util/ntt.h"
 #include <cstdint>
 #include <map>
@@ -229,13 +230,21 @@ namespace gsb_seal
 
     namespace util
     {
-        // util/ntt.h:189-368 over one limb (CoeffIter) or an RNS polynomial (RNSIter + tables array);
-        // tables are matched to a cached device context by (coeff_count_power, modulus).
-        void ntt_negacyclic_harvey(std::uint64_t *operand, const seal::util::NTTTables &tables);
-        void ntt_negacyclic_harvey_lazy(std::uint64_t *operand, const seal::util::NTTTables &tables);
-        void inverse_ntt_negacyclic_harvey(std::uint64_t *operand, const seal::util::NTTTables &tables);
-        void inverse_ntt_negacyclic_harvey_lazy(std::uint64_t *operand, const seal::util::NTTTables &tables);
-        void ntt_negacyclic_harvey(std::uint64_t *operand, std::size_t coeff_modulus_size, const seal::util::NTTTables *tables);
-        void inverse_ntt_negacyclic_harvey(std::uint64_t *operand, std::size_t coeff_modulus_size, const seal::util::NTTTables *tables);
+        // util/ntt.h:189-368: the four families (forward / inverse x lazy / strict) over CoeffIter (one limb), RNSIter
+        // (one polynomial over coeff_modulus_size limbs) and PolyIter (size polynomials back to back), with the
+        // reference's own parameter types, so callers of seal::util::ntt_* recompile unchanged.  Tables are matched
+        // to a cached device context by (coeff_count_power, moduli); an RNS / Poly call is one batched device pass.
+        void ntt_negacyclic_harvey_lazy(seal::util::CoeffIter operand, const seal::util::NTTTables &tables);
+        void ntt_negacyclic_harvey_lazy(seal::util::RNSIter operand, std::size_t coeff_modulus_size, seal::util::ConstNTTTablesIter tables);
+        void ntt_negacyclic_harvey_lazy(seal::util::PolyIter operand, std::size_t size, seal::util::ConstNTTTablesIter tables);
+        void ntt_negacyclic_harvey(seal::util::CoeffIter operand, const seal::util::NTTTables &tables);
+        void ntt_negacyclic_harvey(seal::util::RNSIter operand, std::size_t coeff_modulus_size, seal::util::ConstNTTTablesIter tables);
+        void ntt_negacyclic_harvey(seal::util::PolyIter operand, std::size_t size, seal::util::ConstNTTTablesIter tables);
+        void inverse_ntt_negacyclic_harvey_lazy(seal::util::CoeffIter operand, const seal::util::NTTTables &tables);
+        void inverse_ntt_negacyclic_harvey_lazy(seal::util::RNSIter operand, std::size_t coeff_modulus_size, seal::util::ConstNTTTablesIter tables);
+        void inverse_ntt_negacyclic_harvey_lazy(seal::util::PolyIter operand, std::size_t size, seal::util::ConstNTTTablesIter tables);
+        void inverse_ntt_negacyclic_harvey(seal::util::CoeffIter operand, const seal::util::NTTTables &tables);
+        void inverse_ntt_negacyclic_harvey(seal::util::RNSIter operand, std::size_t coeff_modulus_size, seal::util::ConstNTTTablesIter tables);
+        void inverse_ntt_negacyclic_harvey(seal::util::PolyIter operand, std::size_t size, seal::util::ConstNTTTablesIter tables);
     } // namespace util
 } // namespace gsb_seal

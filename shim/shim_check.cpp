@@ -348,6 +348,45 @@ static int run(size_t N, vector<int> bits, int k_special)
         ok = ok && x == y;
         printf("%-34s %s\n", "util::ntt / inverse lazy", ok ? "bit-exact" : "MISMATCH");
         failures += !ok;
+        // the RNSIter and PolyIter overloads of all four families (util/ntt.h:189-368) on a ciphertext's own storage
+        auto ct_tables = seal::util::iter(context->first_context_data()->small_ntt_tables());
+        const size_t Lc = a.coeff_modulus_size();
+        bool ok2 = true;
+        for (int kind = 0; kind < 4; kind++)
+        {
+            Ciphertext p = a, q = a, u = a, v = a; // inputs are canonical residues; lazy outputs are compared as they are
+            switch (kind)
+            {
+            case 0:
+                seal::util::inverse_ntt_negacyclic_harvey(seal::util::PolyIter(p), p.size(), ct_tables);
+                gsb_seal::util::inverse_ntt_negacyclic_harvey(seal::util::PolyIter(q), q.size(), ct_tables);
+                seal::util::inverse_ntt_negacyclic_harvey(*seal::util::PolyIter(u), Lc, ct_tables);
+                gsb_seal::util::inverse_ntt_negacyclic_harvey(*seal::util::PolyIter(v), Lc, ct_tables);
+                break;
+            case 1:
+                seal::util::inverse_ntt_negacyclic_harvey_lazy(seal::util::PolyIter(p), p.size(), ct_tables);
+                gsb_seal::util::inverse_ntt_negacyclic_harvey_lazy(seal::util::PolyIter(q), q.size(), ct_tables);
+                seal::util::inverse_ntt_negacyclic_harvey_lazy(*seal::util::PolyIter(u), Lc, ct_tables);
+                gsb_seal::util::inverse_ntt_negacyclic_harvey_lazy(*seal::util::PolyIter(v), Lc, ct_tables);
+                break;
+            case 2:
+                seal::util::ntt_negacyclic_harvey(seal::util::PolyIter(p), p.size(), ct_tables);
+                gsb_seal::util::ntt_negacyclic_harvey(seal::util::PolyIter(q), q.size(), ct_tables);
+                seal::util::ntt_negacyclic_harvey(*seal::util::PolyIter(u), Lc, ct_tables);
+                gsb_seal::util::ntt_negacyclic_harvey(*seal::util::PolyIter(v), Lc, ct_tables);
+                break;
+            default:
+                seal::util::ntt_negacyclic_harvey_lazy(seal::util::PolyIter(p), p.size(), ct_tables);
+                gsb_seal::util::ntt_negacyclic_harvey_lazy(seal::util::PolyIter(q), q.size(), ct_tables);
+                seal::util::ntt_negacyclic_harvey_lazy(*seal::util::PolyIter(u), Lc, ct_tables);
+                gsb_seal::util::ntt_negacyclic_harvey_lazy(*seal::util::PolyIter(v), Lc, ct_tables);
+                break;
+            }
+            const size_t bytes = p.size() * Lc * N * sizeof(uint64_t);
+            ok2 = ok2 && memcmp(p.data(), q.data(), bytes) == 0 && memcmp(u.data(), v.data(), bytes) == 0;
+        }
+        printf("%-34s %s\n", "util::ntt_* RNSIter / PolyIter x 4", ok2 ? "bit-exact" : "MISMATCH");
+        failures += !ok2;
     }
     // error convention
     {
