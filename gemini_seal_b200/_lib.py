@@ -74,6 +74,12 @@ PROTOTYPES = {
     "gsb_bfv_multiply_sizes_host": (i32, [vp, u64, vp, sz, vp, sz, vp, sz, sz]),
     "gsb_relinearize_sizes_dev": (i32, [vp, vp, vp, sz, vp, sz, sz, i32, vp]),
     "gsb_relinearize_sizes_host": (i32, [vp, vp, sz, vp, sz, sz, i32]),
+    "gsb_bfv_add_plain_dev": (i32, [vp, vp, vp, sz, i32, u64p, u64, u64, u64, sz, vp]),
+    "gsb_bfv_add_plain_host": (i32, [vp, vp, vp, sz, i32, u64p, u64, u64, u64, sz]),
+    "gsb_bfv_plain_to_rns_dev": (i32, [vp, vp, sz, u64, u64p, vp, sz, i32, vp]),
+    "gsb_bfv_plain_to_rns_host": (i32, [vp, vp, sz, u64, u64p, vp, sz, i32]),
+    "gsb_multiply_plain_coeff_dev": (i32, [vp, vp, vp, sz, sz, sz, vp]),
+    "gsb_multiply_plain_coeff_host": (i32, [vp, vp, sz, sz, vp, sz, u64, u64p, i32]),
     "gsb_drop_last_limb_dev": (i32, [vp, vp, vp, sz, sz, vp]),
     "gsb_secret_key_set": (i32, [vp, vp]),
     "gsb_dot_product_ct_sk_dev": (i32, [vp, vp, vp, vp, sz, sz, sz, i32, vp]),

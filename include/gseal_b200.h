@@ -227,6 +227,26 @@ int gsb_relinearize_sizes_host(gsb_ctx *ctx, const uint64_t *in, size_t size, ui
  * [n_polys][L][N] -> out = [n_polys][L-1][N], the first L-1 limbs of every polynomial (device buffers). */
 int gsb_drop_last_limb_dev(gsb_ctx *ctx, const uint64_t *in, uint64_t *out, size_t n_polys, size_t L, void *stream);
 
+/* ---- plaintext operands, BFV ------------------------------------------------------
+ * Evaluator::add_plain_inplace / sub_plain_inplace, BFV branch (evaluator.cpp:1290-1437 ->
+ * multiply_add/sub_plain_with_scaling_variant, util/scalingvariant.cpp:15-95): enc0 = the ciphertext's first
+ * polynomial [L][N], updated in place; plain = [count] coefficients mod t; the three constants are the level's
+ * ContextData::coeff_div_plain_modulus() [L], coeff_modulus_mod_plain_modulus(), plain_upper_half_threshold(). */
+int gsb_bfv_add_plain_dev(gsb_ctx *ctx, uint64_t *enc0, const uint64_t *plain, size_t count, int subtract, const uint64_t *coeff_div_plain_modulus, uint64_t q_mod_t, uint64_t threshold, uint64_t plain_modulus, size_t L, void *stream);
+int gsb_bfv_add_plain_host(gsb_ctx *ctx, uint64_t *enc0, const uint64_t *plain, size_t count, int subtract, const uint64_t *coeff_div_plain_modulus, uint64_t q_mod_t, uint64_t threshold, uint64_t plain_modulus, size_t L);
+/* Evaluator::transform_to_ntt_inplace(Plaintext &, parms_id) for contexts with using_fast_plain_lift
+ * (evaluator.cpp:1648-1744): plain = [count] coefficients mod t -> out = [L][N]; threshold =
+ * plain_upper_half_threshold(), increment = plain_upper_half_increment() [L] (host words); ntt = 0 stops after
+ * the lift (:1722-1736). */
+int gsb_bfv_plain_to_rns_dev(gsb_ctx *ctx, const uint64_t *plain, size_t count, uint64_t threshold, const uint64_t *increment, uint64_t *out, size_t L, int ntt, void *stream);
+int gsb_bfv_plain_to_rns_host(gsb_ctx *ctx, const uint64_t *plain, size_t count, uint64_t threshold, const uint64_t *increment, uint64_t *out, size_t L, int ntt);
+/* Evaluator::multiply_plain_inplace with a coefficient-form plaintext = multiply_plain_normal (evaluator.cpp:
+ * 1475-1603): enc = [batch][size][L][N] coefficient form, in place; plain_ntt = [L][N] from gsb_bfv_plain_to_rns_dev.
+ * The host form takes the raw plaintext [count]: lift = 1 generic branch (:1556-1592), lift = 0 the monomial
+ * branch's unadjusted coefficient (:1534-1546); both give the reference's words (the negacyclic product is exact). */
+int gsb_multiply_plain_coeff_dev(gsb_ctx *ctx, uint64_t *enc, const uint64_t *plain_ntt, size_t batch, size_t size, size_t L, void *stream);
+int gsb_multiply_plain_coeff_host(gsb_ctx *ctx, uint64_t *enc, size_t size, size_t L, const uint64_t *plain, size_t count, uint64_t threshold, const uint64_t *increment, int lift);
+
 /* ---- Decryptor (seal::Decryptor, decryptor.cpp) --------------------------------
  * gsb_secret_key_set: SecretKey::data() in NTT form at key level, sk_host = [K][N] canonical residues
  * (Decryptor::Decryptor, decryptor.cpp:21-58; rejects what is_valid_for(SecretKey) rejects).  Powers

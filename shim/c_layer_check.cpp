@@ -122,6 +122,37 @@ int main()
             err = max(err, fabs(out[i] - va[i] * vb[i]));
         expect("decode(Decryptor_Decrypt(a*b)) == a*b", err < 1e-5);
     }
+    {
+        // plaintext operands, add_many and level switches to a parms_id through the C entry points
+        Ciphertext x, y;
+        ref.add_plain(a, pb, x);
+        expect("Evaluator_AddPlain", Evaluator_AddPlain(ev, &a, &pb, &y) == S_OK && same(x, y));
+        ref.sub_plain(a, pb, x);
+        expect("Evaluator_SubPlain", Evaluator_SubPlain(ev, &a, &pb, &y) == S_OK && same(x, y));
+        vector<Ciphertext> many{ a, b, a };
+        ref.add_many(many, x);
+        void *ptrs[3] = { &many[0], &many[1], &many[2] };
+        expect("Evaluator_AddMany", Evaluator_AddMany(ev, 3, ptrs, &y) == S_OK && same(x, y));
+        auto last = context->last_parms_id();
+        uint64_t id[4];
+        seal::c::CopyParmsId(last, id);
+        ref.mod_switch_to(a, last, x);
+        expect("Evaluator_ModSwitchTo1(last)", Evaluator_ModSwitchTo1(ev, &a, id, &y, nullptr) == S_OK && same(x, y));
+        Plaintext px, py;
+        ref.mod_switch_to_next(pb, px);
+        expect("Evaluator_ModSwitchToNext2 (plain)", Evaluator_ModSwitchToNext2(ev, &pb, &py) == S_OK && px.parms_id() == py.parms_id() &&
+                                                       px.coeff_count() == py.coeff_count() && px.scale() == py.scale() &&
+                                                       memcmp(px.data(), py.data(), px.coeff_count() * sizeof(uint64_t)) == 0);
+        ref.mod_switch_to(pb, last, px);
+        expect("Evaluator_ModSwitchTo2 (plain, last)", Evaluator_ModSwitchTo2(ev, &pb, id, &py) == S_OK && px.parms_id() == py.parms_id() &&
+                                                         px.coeff_count() == py.coeff_count() &&
+                                                         memcmp(px.data(), py.data(), px.coeff_count() * sizeof(uint64_t)) == 0);
+        Ciphertext lower = a;
+        ref.mod_switch_to_next_inplace(lower);
+        uint64_t first_id[4];
+        seal::c::CopyParmsId(context->first_parms_id(), first_id);
+        expect("ModSwitchTo1 to a higher level -> E_INVALIDARG", Evaluator_ModSwitchTo1(ev, &lower, first_id, &y, nullptr) == E_INVALIDARG);
+    }
     // HRESULT conventions (c/defines.h:27-56, c/evaluator.cpp:31-58)
     expect("null thisptr -> E_POINTER", Evaluator_Negate(nullptr, &a, &d) == E_POINTER);
     expect("null operand -> E_POINTER", Evaluator_Multiply(ev, &a, nullptr, &d, nullptr) == E_POINTER);
@@ -133,7 +164,7 @@ int main()
         ref.multiply_inplace(three, b);
         expect("rotate size-3 ciphertext -> E_INVALIDARG", Evaluator_RotateVector(ev, &three, 1, &glk, &x, nullptr) == E_INVALIDARG);
         expect("BFV-only op on CKKS -> COR_E_INVALIDOPERATION", Evaluator_RotateRows(ev, &a, 1, &glk, &x, nullptr) == COR_E_INVALIDOPERATION);
-        expect("unserved op -> COR_E_INVALIDOPERATION", Evaluator_AddPlain(ev, &a, &pa, &x) == COR_E_INVALIDOPERATION);
+        expect("CKKS-only op misuse -> E_INVALIDARG", Evaluator_ModSwitchToNext2(ev, &pa, nullptr) == E_POINTER);
         int budget = 0;
         expect("Decryptor_InvariantNoiseBudget -> unserved", Decryptor_InvariantNoiseBudget(dec, &a, &budget) == COR_E_INVALIDOPERATION);
     }

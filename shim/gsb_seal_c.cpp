@@ -285,15 +285,81 @@ SEAL_C_FUNC Evaluator_ContextUsingKeyswitching(void *thisptr, bool *using_keyswi
     return S_OK;
 }
 
-// Operations of the reference's C layer outside the served path (plaintext add / sub, plaintext level
-// switches, plaintext NTT, add_many, mod_switch_to): reported, not emulated.
-SEAL_C_FUNC Evaluator_AddMany(void *thisptr, uint64_t, void **, void *) { return not_served(thisptr); }
-SEAL_C_FUNC Evaluator_AddPlain(void *thisptr, void *, void *, void *) { return not_served(thisptr); }
-SEAL_C_FUNC Evaluator_SubPlain(void *thisptr, void *, void *, void *) { return not_served(thisptr); }
-SEAL_C_FUNC Evaluator_ModSwitchToNext2(void *thisptr, void *, void *) { return not_served(thisptr); }
-SEAL_C_FUNC Evaluator_ModSwitchTo1(void *thisptr, void *, uint64_t *, void *, void *) { return not_served(thisptr); }
-SEAL_C_FUNC Evaluator_ModSwitchTo2(void *thisptr, void *, uint64_t *, void *) { return not_served(thisptr); }
-SEAL_C_FUNC Evaluator_TransformToNTT1(void *thisptr, void *, uint64_t *, void *, void *) { return not_served(thisptr); }
+// Plaintext operands, add_many and level switches to a given parms_id (c/evaluator.cpp:110-212, 387-459, 542-574)
+SEAL_C_FUNC Evaluator_AddMany(void *thisptr, uint64_t count, void **encrypteds, void *destination)
+{
+    if (any_null(thisptr, encrypteds, destination))
+        return E_POINTER;
+    return run([&] {
+        std::vector<Ciphertext> all;
+        all.reserve(count);
+        for (uint64_t i = 0; i < count; i++)
+            all.emplace_back(ct(encrypteds[i]));
+        ev(thisptr)->add_many(all, ct(destination));
+    });
+}
+
+SEAL_C_FUNC Evaluator_AddPlain(void *thisptr, void *encrypted, void *plain, void *destination)
+{
+    if (any_null(plain))
+        return E_POINTER;
+    return unary(thisptr, encrypted, destination,
+                 [&](gsb_seal::Evaluator &e, Ciphertext &x) { e.add_plain_inplace(x, *FromVoid<Plaintext>(plain)); });
+}
+
+SEAL_C_FUNC Evaluator_SubPlain(void *thisptr, void *encrypted, void *plain, void *destination)
+{
+    if (any_null(plain))
+        return E_POINTER;
+    return unary(thisptr, encrypted, destination,
+                 [&](gsb_seal::Evaluator &e, Ciphertext &x) { e.sub_plain_inplace(x, *FromVoid<Plaintext>(plain)); });
+}
+
+SEAL_C_FUNC Evaluator_ModSwitchToNext2(void *thisptr, void *plain, void *destination)
+{
+    if (any_null(thisptr, plain, destination))
+        return E_POINTER;
+    return run([&] {
+        if (destination != plain)
+            *FromVoid<Plaintext>(destination) = *FromVoid<Plaintext>(plain);
+        ev(thisptr)->mod_switch_to_next_inplace(*FromVoid<Plaintext>(destination));
+    });
+}
+
+SEAL_C_FUNC Evaluator_ModSwitchTo1(void *thisptr, void *encrypted, uint64_t *parms_id, void *destination, void *)
+{
+    if (any_null(parms_id))
+        return E_POINTER;
+    seal::parms_id_type id;
+    seal::c::CopyParmsId(parms_id, id);
+    return unary(thisptr, encrypted, destination, [&](gsb_seal::Evaluator &e, Ciphertext &x) { e.mod_switch_to_inplace(x, id); });
+}
+
+SEAL_C_FUNC Evaluator_ModSwitchTo2(void *thisptr, void *plain, uint64_t *parms_id, void *destination)
+{
+    if (any_null(thisptr, plain, parms_id, destination))
+        return E_POINTER;
+    seal::parms_id_type id;
+    seal::c::CopyParmsId(parms_id, id);
+    return run([&] {
+        if (destination != plain)
+            *FromVoid<Plaintext>(destination) = *FromVoid<Plaintext>(plain);
+        ev(thisptr)->mod_switch_to_inplace(*FromVoid<Plaintext>(destination), id);
+    });
+}
+
+SEAL_C_FUNC Evaluator_TransformToNTT1(void *thisptr, void *plain, uint64_t *parms_id, void *destination_ntt, void *)
+{
+    if (any_null(thisptr, plain, parms_id, destination_ntt))
+        return E_POINTER;
+    seal::parms_id_type id;
+    seal::c::CopyParmsId(parms_id, id);
+    return run([&] {
+        if (destination_ntt != plain)
+            *FromVoid<Plaintext>(destination_ntt) = *FromVoid<Plaintext>(plain);
+        ev(thisptr)->transform_to_ntt_inplace(*FromVoid<Plaintext>(destination_ntt), id);
+    });
+}
 
 // ---- Decryptor (c/decryptor.h:16-22) ---------------------------------------------------------------------
 SEAL_C_FUNC Decryptor_Create(void *context, void *secret_key, void **decryptor)

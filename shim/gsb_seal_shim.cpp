@@ -234,7 +234,14 @@ namespace gsb_seal
         if (!pool)
             throw invalid_argument("pool is uninitialized");
         if (!encrypted.is_ntt_form())
-            throw logic_error("device multiply_plain serves NTT-form operands");
+        {
+            multiply_plain_normal(encrypted, plain);
+#ifdef SEAL_THROW_ON_TRANSPARENT_CIPHERTEXT
+            if (encrypted.is_transparent())
+                throw logic_error("result ciphertext is transparent");
+#endif
+            return;
+        }
         if (encrypted.parms_id() != plain.parms_id())
             throw invalid_argument("encrypted_ntt and plain_ntt parameter mismatch");
         auto &context_data = *context_->get_context_data(encrypted.parms_id());
@@ -249,6 +256,175 @@ namespace gsb_seal
         if (encrypted.is_transparent())
             throw logic_error("result ciphertext is transparent");
 #endif
+    }
+
+    // evaluator.cpp:1475-1603 (coefficient-form ciphertext and plaintext: BFV)
+    void Evaluator::multiply_plain_normal(Ciphertext &encrypted, const Plaintext &plain)
+    {
+        auto &context_data = *context_->get_context_data(encrypted.parms_id());
+        const size_t L = level_limbs(encrypted), size = encrypted.size();
+        if (!seal::util::product_fits_in(size, N_, L))
+            throw logic_error("invalid parameters");
+        const double new_scale = encrypted.scale() * plain.scale();
+        if (new_scale <= 0 || (static_cast<int>(log2(new_scale)) >= context_data.total_coeff_modulus_bit_count()))
+            throw invalid_argument("scale out of bounds");
+        const uint64_t threshold = context_data.plain_upper_half_threshold();
+        const uint64_t *increment = context_data.plain_upper_half_increment();
+        const bool fast_lift = context_data.qualifiers().using_fast_plain_lift;
+        if (plain.nonzero_coeff_count() == 1)
+        {
+            // monomial branch (:1512-1546): the coefficient is used as it is unless it needs the multi-precision lift
+            const size_t e = plain.significant_coeff_count() - 1;
+            if (plain[e] >= threshold && !fast_lift)
+                throw logic_error("device multiply_plain serves contexts with using_fast_plain_lift");
+            vector<uint64_t> mono(e + 1, 0);
+            mono[e] = plain[e];
+            check(gsb_multiply_plain_coeff_host(ctx_, encrypted.data(), size, L, mono.data(), mono.size(), threshold, increment, 0));
+        }
+        else
+        {
+            if (!fast_lift) // the multi-precision lift (:1558-1575) is not served
+                throw logic_error("device multiply_plain serves contexts with using_fast_plain_lift");
+            check(gsb_multiply_plain_coeff_host(ctx_, encrypted.data(), size, L, plain.data(), plain.coeff_count(), threshold, increment, 1));
+        }
+        encrypted.scale() = new_scale; // set before the arithmetic in the reference (:1506); no effect on the words
+    }
+
+    // evaluator.cpp:1290-1437
+    void Evaluator::add_sub_plain(Ciphertext &encrypted, const Plaintext &plain, bool subtract)
+    {
+        validate(encrypted, "encrypted");
+        if (!is_metadata_valid_for(plain, context_) || !is_buffer_valid(plain))
+            throw invalid_argument("plain is not valid for encryption parameters");
+        auto &context_data = *context_->get_context_data(encrypted.parms_id());
+        if (bfv_ && encrypted.is_ntt_form())
+            throw invalid_argument("BFV encrypted cannot be in NTT form");
+        if (!bfv_ && !encrypted.is_ntt_form())
+            throw invalid_argument("CKKS encrypted must be in NTT form");
+        if (plain.is_ntt_form() != encrypted.is_ntt_form())
+            throw invalid_argument("NTT form mismatch");
+        if (encrypted.is_ntt_form() && (encrypted.parms_id() != plain.parms_id()))
+            throw invalid_argument("encrypted and plain parameter mismatch");
+        if (!seal::util::are_close<double>(encrypted.scale(), plain.scale()))
+            throw invalid_argument("scale mismatch");
+        const size_t L = level_limbs(encrypted);
+        if (!seal::util::product_fits_in(N_, L))
+            throw logic_error("invalid parameters");
+        if (bfv_)
+            check(gsb_bfv_add_plain_host(
+                ctx_, encrypted.data(), plain.data(), plain.coeff_count(), subtract ? 1 : 0, context_data.coeff_div_plain_modulus(),
+                context_data.coeff_modulus_mod_plain_modulus(), context_data.plain_upper_half_threshold(), plain_modulus_, L));
+        else
+            check(gsb_poly_op_host(ctx_, subtract ? GSB_OP_SUB : GSB_OP_ADD, encrypted.data(), plain.data(), nullptr, encrypted.data(), 1, L, 0));
+#ifdef SEAL_THROW_ON_TRANSPARENT_CIPHERTEXT
+        if (encrypted.is_transparent())
+            throw logic_error("result ciphertext is transparent");
+#endif
+    }
+
+    void Evaluator::add_plain_inplace(Ciphertext &encrypted, const Plaintext &plain)
+    {
+        add_sub_plain(encrypted, plain, false);
+    }
+
+    void Evaluator::sub_plain_inplace(Ciphertext &encrypted, const Plaintext &plain)
+    {
+        add_sub_plain(encrypted, plain, true);
+    }
+
+    // evaluator.cpp:153-172
+    void Evaluator::add_many(const vector<Ciphertext> &encrypteds, Ciphertext &destination)
+    {
+        if (encrypteds.empty())
+            throw invalid_argument("encrypteds cannot be empty");
+        for (size_t i = 0; i < encrypteds.size(); i++)
+            if (&encrypteds[i] == &destination)
+                throw invalid_argument("encrypteds must be different from destination");
+        destination = encrypteds[0];
+        for (size_t i = 1; i < encrypteds.size(); i++)
+            add_inplace(destination, encrypteds[i]);
+    }
+
+    // evaluator.cpp:1038-1064
+    void Evaluator::mod_switch_to_inplace(Ciphertext &encrypted, parms_id_type parms_id, MemoryPoolHandle pool)
+    {
+        auto context_data_ptr = context_->get_context_data(encrypted.parms_id());
+        auto target_context_data_ptr = context_->get_context_data(parms_id);
+        if (!context_data_ptr)
+            throw invalid_argument("encrypted is not valid for encryption parameters");
+        if (!target_context_data_ptr)
+            throw invalid_argument("parms_id is not valid for encryption parameters");
+        if (context_data_ptr->chain_index() < target_context_data_ptr->chain_index())
+            throw invalid_argument("cannot switch to higher level modulus");
+        while (encrypted.parms_id() != parms_id)
+            mod_switch_to_next_inplace(encrypted, pool);
+    }
+
+    // evaluator.h:430-438 -> mod_switch_drop_to_next(Plaintext &) (evaluator.cpp:958-994): an NTT-form plaintext is
+    // limb-major, so dropping the last prime is a resize
+    void Evaluator::mod_switch_to_next_inplace(Plaintext &plain)
+    {
+        if (!is_valid_for(plain, context_))
+            throw invalid_argument("plain is not valid for encryption parameters");
+        auto context_data_ptr = context_->get_context_data(plain.parms_id());
+        if (!plain.is_ntt_form())
+            throw invalid_argument("plain is not in NTT form");
+        if (!context_data_ptr->next_context_data())
+            throw invalid_argument("end of modulus switching chain reached");
+        auto &next_context_data = *context_data_ptr->next_context_data();
+        if (plain.scale() <= 0 || (static_cast<int>(log2(plain.scale())) >= next_context_data.total_coeff_modulus_bit_count()))
+            throw invalid_argument("scale out of bounds");
+        const size_t dest_size = seal::util::mul_safe(next_context_data.parms().coeff_modulus().size(), N_);
+        plain.parms_id() = parms_id_zero;
+        plain.resize(dest_size);
+        plain.parms_id() = next_context_data.parms_id();
+    }
+
+    // evaluator.cpp:1066-1088
+    void Evaluator::mod_switch_to_inplace(Plaintext &plain, parms_id_type parms_id)
+    {
+        auto context_data_ptr = context_->get_context_data(plain.parms_id());
+        auto target_context_data_ptr = context_->get_context_data(parms_id);
+        if (!context_data_ptr)
+            throw invalid_argument("plain is not valid for encryption parameters");
+        if (!target_context_data_ptr)
+            throw invalid_argument("parms_id is not valid for encryption parameters");
+        if (!plain.is_ntt_form())
+            throw invalid_argument("plain is not in NTT form");
+        if (context_data_ptr->chain_index() < target_context_data_ptr->chain_index())
+            throw invalid_argument("cannot switch to higher level modulus");
+        while (plain.parms_id() != parms_id)
+            mod_switch_to_next_inplace(plain);
+    }
+
+    // evaluator.cpp:1648-1744 (BFV plaintext -> NTT form at the level parms_id)
+    void Evaluator::transform_to_ntt_inplace(Plaintext &plain, parms_id_type parms_id, MemoryPoolHandle pool)
+    {
+        if (!is_valid_for(plain, context_))
+            throw invalid_argument("plain is not valid for encryption parameters");
+        auto context_data_ptr = context_->get_context_data(parms_id);
+        if (!context_data_ptr)
+            throw invalid_argument("parms_id is not valid for the current context");
+        if (plain.is_ntt_form())
+            throw invalid_argument("plain is already in NTT form");
+        if (!pool)
+            throw invalid_argument("pool is uninitialized");
+        auto &context_data = *context_data_ptr;
+        const size_t L = context_data.parms().coeff_modulus().size(), count = plain.coeff_count();
+        if (!seal::util::product_fits_in(N_, L))
+            throw logic_error("invalid parameters");
+        if (!context_data.qualifiers().using_fast_plain_lift) // the multi-precision lift (:1694-1717) is not served
+            throw logic_error("device transform_to_ntt serves contexts with using_fast_plain_lift");
+        vector<uint64_t> raw(plain.data(), plain.data() + count);
+        plain.resize(N_ * L);
+        const int rc = gsb_bfv_plain_to_rns_host(
+            ctx_, raw.data(), count, context_data.plain_upper_half_threshold(), context_data.plain_upper_half_increment(), plain.data(), L, 1);
+        if (rc != GSB_OK)
+        {
+            plain.resize(count);
+            fail(rc);
+        }
+        plain.parms_id() = parms_id;
     }
 
     // evaluator.cpp:529-558: ckks_square / bfv_square give the words of multiply(x, x)

@@ -89,6 +89,20 @@ namespace gsb_seal
         // evaluator.h:780-815 / evaluator.cpp:1438-1475,1605-1646: NTT-form plaintext multiplication
         void multiply_plain_inplace(
             seal::Ciphertext &encrypted, const seal::Plaintext &plain, seal::MemoryPoolHandle pool = seal::MemoryManager::GetPool());
+        // evaluator.h:700-770 / evaluator.cpp:1290-1437: plaintext addition / subtraction (CKKS: NTT-form plaintext;
+        // BFV: multiply_add / sub_plain_with_scaling_variant)
+        void add_plain_inplace(seal::Ciphertext &encrypted, const seal::Plaintext &plain);
+        void sub_plain_inplace(seal::Ciphertext &encrypted, const seal::Plaintext &plain);
+        // evaluator.h:208-220 / evaluator.cpp:153-172
+        void add_many(const std::vector<seal::Ciphertext> &encrypteds, seal::Ciphertext &destination);
+        // evaluator.h:460-540 / evaluator.cpp:1038-1088, 958-994: level switches to a given parms_id, and of plaintexts
+        void mod_switch_to_inplace(
+            seal::Ciphertext &encrypted, seal::parms_id_type parms_id, seal::MemoryPoolHandle pool = seal::MemoryManager::GetPool());
+        void mod_switch_to_next_inplace(seal::Plaintext &plain);
+        void mod_switch_to_inplace(seal::Plaintext &plain, seal::parms_id_type parms_id);
+        // evaluator.h:820-856 / evaluator.cpp:1648-1744: BFV plaintext to NTT form at a level
+        void transform_to_ntt_inplace(
+            seal::Plaintext &plain, seal::parms_id_type parms_id, seal::MemoryPoolHandle pool = seal::MemoryManager::GetPool());
         // evaluator.h:858-930 / evaluator.cpp:1746-1840
         void transform_to_ntt_inplace(seal::Ciphertext &encrypted);
         void transform_from_ntt_inplace(seal::Ciphertext &encrypted_ntt);
@@ -187,6 +201,8 @@ namespace gsb_seal
     private:
         void validate(const seal::Ciphertext &ct, const char *what) const;
         void bfv_multiply(seal::Ciphertext &encrypted1, const seal::Ciphertext &encrypted2);
+        void multiply_plain_normal(seal::Ciphertext &encrypted, const seal::Plaintext &plain);
+        void add_sub_plain(seal::Ciphertext &encrypted, const seal::Plaintext &plain, bool subtract);
         void add_sub(seal::Ciphertext &encrypted1, const seal::Ciphertext &encrypted2, bool subtract);
         std::size_t level_limbs(const seal::Ciphertext &ct) const;
         void ensure_relin(const seal::RelinKeys &keys, std::size_t index);

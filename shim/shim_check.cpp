@@ -305,6 +305,34 @@ static int run(size_t N, vector<int> bits, int k_special)
         same("square + relin + rescale_to(last)", r5, d5);
     }
     {
+        // row f3 remainder: plaintext add / sub, add_many, mod_switch_to (ciphertext and plaintext)
+        Ciphertext r2 = a, d2 = a;
+        ref.add_plain_inplace(r2, pb_ntt);
+        dev.add_plain_inplace(d2, pb_ntt);
+        same("add_plain_inplace", r2, d2);
+        ref.sub_plain_inplace(r2, pa);
+        dev.sub_plain_inplace(d2, pa);
+        same("sub_plain_inplace", r2, d2);
+        vector<Ciphertext> many{ a, b, r2 };
+        Ciphertext rs, ds;
+        ref.add_many(many, rs);
+        dev.add_many(many, ds);
+        same("add_many(3)", rs, ds);
+        rs.scale() = ds.scale() = pow(2.0, 20); // metadata only: the last level of the small test modulus has 40 bits
+        ref.mod_switch_to_inplace(rs, context->last_parms_id());
+        dev.mod_switch_to_inplace(ds, context->last_parms_id());
+        same("mod_switch_to_inplace(last)", rs, ds);
+        Plaintext p1 = pb, p2 = pb;
+        p1.scale() = p2.scale() = pow(2.0, 20);
+        ref.mod_switch_to_inplace(p1, context->last_parms_id());
+        dev.mod_switch_to_inplace(p2, context->last_parms_id());
+        const bool okp = p1.parms_id() == p2.parms_id() && p1.coeff_count() == p2.coeff_count() && p1.scale() == p2.scale() &&
+                         memcmp(p1.data(), p2.data(), p1.coeff_count() * sizeof(uint64_t)) == 0;
+        printf("%-34s %s\n", "mod_switch_to_inplace(Plaintext)", okp ? "bit-exact" : "MISMATCH");
+        failures += !okp;
+        expect_throw("add_plain scale mismatch", [&] { Ciphertext t = a; t.scale() = 2.0; dev.add_plain_inplace(t, pb_ntt); }, 0);
+    }
+    {
         // batched extension vs three reference calls
         vector<Ciphertext> xs(3, a), ys(3, b);
         enc.encrypt(pb, xs[1]);
@@ -542,6 +570,51 @@ static int run_bfv(size_t N)
         ref.add_inplace(want, want);
         dev.download(x, back);
         same("BFV device-resident chain (5 ops)", want, back);
+    }
+    {
+        // row f3 remainder, BFV: scaling-variant plaintext add / sub, coefficient-form multiply_plain (generic and
+        // monomial branches), plaintext transform_to_ntt, NTT-form multiply_plain
+        Ciphertext r2 = a, d2 = a;
+        ref.add_plain_inplace(r2, pb);
+        dev.add_plain_inplace(d2, pb);
+        same("BFV add_plain_inplace", r2, d2);
+        ref.sub_plain_inplace(r2, pa);
+        dev.sub_plain_inplace(d2, pa);
+        same("BFV sub_plain_inplace", r2, d2);
+        ref.multiply_plain_inplace(r2, pb);
+        dev.multiply_plain_inplace(d2, pb);
+        same("BFV multiply_plain (generic)", r2, d2);
+        Plaintext mono_small("5x^3"), mono_big;
+        mono_big.resize(8);
+        mono_big.set_zero();
+        mono_big[7] = 786432; // t - 1: above plain_upper_half_threshold
+        ref.multiply_plain_inplace(r2, mono_small);
+        dev.multiply_plain_inplace(d2, mono_small);
+        same("BFV multiply_plain (monomial)", r2, d2);
+        ref.multiply_plain_inplace(r2, mono_big);
+        dev.multiply_plain_inplace(d2, mono_big);
+        same("BFV multiply_plain (monomial, upper half)", r2, d2);
+        Plaintext t1 = pb, t2 = pb;
+        ref.transform_to_ntt_inplace(t1, context->first_parms_id());
+        dev.transform_to_ntt_inplace(t2, context->first_parms_id());
+        const bool okp = t1.parms_id() == t2.parms_id() && t1.coeff_count() == t2.coeff_count() &&
+                         memcmp(t1.data(), t2.data(), t1.coeff_count() * sizeof(uint64_t)) == 0;
+        printf("%-34s %s\n", "BFV transform_to_ntt(Plaintext)", okp ? "bit-exact" : "MISMATCH");
+        failures += !okp;
+        Ciphertext r3 = a, d3 = a;
+        ref.transform_to_ntt_inplace(r3);
+        dev.transform_to_ntt_inplace(d3);
+        ref.multiply_plain_inplace(r3, t1);
+        dev.multiply_plain_inplace(d3, t2);
+        same("BFV multiply_plain (NTT form)", r3, d3);
+        vector<Ciphertext> many{ a, b, a, b };
+        Ciphertext rs, ds;
+        ref.add_many(many, rs);
+        dev.add_many(many, ds);
+        same("BFV add_many(4)", rs, ds);
+        ref.mod_switch_to_inplace(rs, context->last_parms_id());
+        dev.mod_switch_to_inplace(ds, context->last_parms_id());
+        same("BFV mod_switch_to_inplace(last)", rs, ds);
     }
     expect_throw("BFV rotate_vector (CKKS only)", [&] { Ciphertext t = a; dev.rotate_vector_inplace(t, 1, glk); }, 1);
     return failures;
