@@ -4,11 +4,11 @@ The compute lives in hand-written sm_100a CUDA behind the C ABI of include/gseal
 (gemini_seal_b200/_C/libgseal_b200.so, built by gemini_seal_b200.build).  This package is the thin
 host-side mirror of the reference interface; it never falls back to a CPU implementation.
 """
-from .evaluator import (BfvEvaluator, Context, CudaError, Decryptor, Evaluator, Workspace, inverse_ntt_negacyclic_harvey,  # noqa: F401
+from .evaluator import (BfvEvaluator, Context, CudaError, Decryptor, Evaluator, KeyGenerator, Workspace, inverse_ntt_negacyclic_harvey,  # noqa: F401
                         inverse_ntt_negacyclic_harvey_lazy, ntt_negacyclic_harvey,
                         ntt_negacyclic_harvey_lazy, poly_op)
 
 __all__ = [
-    "Context", "Workspace", "Evaluator", "BfvEvaluator", "Decryptor", "CudaError", "ntt_negacyclic_harvey", "ntt_negacyclic_harvey_lazy",
+    "Context", "Workspace", "Evaluator", "BfvEvaluator", "Decryptor", "KeyGenerator", "CudaError", "ntt_negacyclic_harvey", "ntt_negacyclic_harvey_lazy",
     "inverse_ntt_negacyclic_harvey", "inverse_ntt_negacyclic_harvey_lazy", "poly_op",
 ]

@@ -80,6 +80,8 @@ PROTOTYPES = {
     "gsb_bfv_plain_to_rns_host": (i32, [vp, vp, sz, u64, u64p, vp, sz, i32]),
     "gsb_multiply_plain_coeff_dev": (i32, [vp, vp, vp, sz, sz, sz, vp]),
     "gsb_multiply_plain_coeff_host": (i32, [vp, vp, sz, sz, vp, sz, u64, u64p, i32]),
+    "gsb_kswitch_keygen_dev": (i32, [vp, vp, i32, C.POINTER(u32), sz, vp, vp, vp, i32, vp]),
+    "gsb_kswitch_keygen_host": (i32, [vp, i32, C.POINTER(u32), sz, vp, vp, vp, i32]),
     "gsb_drop_last_limb_dev": (i32, [vp, vp, vp, sz, sz, vp]),
     "gsb_secret_key_set": (i32, [vp, vp]),
     "gsb_dot_product_ct_sk_dev": (i32, [vp, vp, vp, vp, sz, sz, sz, i32, vp]),

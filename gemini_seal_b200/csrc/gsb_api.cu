@@ -556,4 +556,5 @@ int gsb_ctx_fast_ntt(const gsb_ctx *ctx)
 
 #include "gsb_evaluator.cuh"
 #include "gsb_general.cuh"
+#include "gsb_keygen.cuh"
 #include "gsb_noalloc.cuh"

@@ -432,6 +432,42 @@ class BfvEvaluator(Evaluator):
     mul_relin_rescale = rescale_to_next = multiply_plain = _unsupported
 
 
+class KeyGenerator:
+    """Mirror of the arithmetic half of seal::KeyGenerator (keygenerator.cpp:138-180, 51-116, 325-420; SURVEY 8(f)
+    row f2).  The caller supplies the sampled buffers -- `a` uniform residues in NTT form [n][beta][K][N], `e` the
+    noise polynomials as int64 [n][beta][N] -- and gets the switching keys [n][beta][2][K][N]; install=True also
+    places them in the context's key store.  `secret_key` is SecretKey::data(): NTT form at key level, [K][N]."""
+
+    def __init__(self, context, secret_key):
+        self.ctx, self.lib = context, context.lib
+        sk = np.ascontiguousarray(secret_key, dtype=np.uint64)
+        if sk.shape != (context.K, context.N):
+            raise ValueError("secret key is not valid for encryption parameters")
+        _check(self.lib, self.lib.gsb_secret_key_set(context.handle, _ptr(sk)))
+
+    def _run(self, kind, ids, a, e, install):
+        n = len(ids)
+        ctx = self.ctx
+        if tuple(a.shape) != (n, ctx.n_bundles, ctx.K, ctx.N) or tuple(e.shape) != (n, ctx.n_bundles, ctx.N):
+            raise ValueError("sampled buffers do not match the encryption parameters")
+        arr = (C.c_uint32 * n)(*[int(i) for i in ids])
+        out = _empty_like(a, (n, ctx.n_bundles, 2, ctx.K, ctx.N))
+        if _is_torch(a):
+            _check(self.lib, self.lib.gsb_kswitch_keygen_dev(ctx.handle, None, kind, arr, n, _ptr(a), _ptr(e), _ptr(out), int(install), _stream()))
+        else:
+            e = np.ascontiguousarray(e, dtype=np.int64)
+            _check(self.lib, self.lib.gsb_kswitch_keygen_host(ctx.handle, kind, arr, n, _ptr(a), e.ctypes.data, _ptr(out), int(install)))
+        return out
+
+    def relin_keys(self, a, e, count=1, install=False):
+        """relin_keys(count) (keygenerator.cpp:138-180): keys for s^2 .. s^(count+1)."""
+        return self._run(GSB_KEY_RELIN, [p + 2 for p in range(count)], a, e, install)
+
+    def galois_keys(self, galois_elts, a, e, install=False):
+        """galois_keys(galois_elts) (keygenerator.cpp:51-116), one key per element."""
+        return self._run(GSB_KEY_GALOIS, list(galois_elts), a, e, install)
+
+
 class Decryptor:
     """Mirror of seal::Decryptor (decryptor.h / decryptor.cpp; SURVEY 8(f) row f4) on raw limb buffers.
 

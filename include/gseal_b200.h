@@ -247,6 +247,21 @@ int gsb_bfv_plain_to_rns_host(gsb_ctx *ctx, const uint64_t *plain, size_t count,
 int gsb_multiply_plain_coeff_dev(gsb_ctx *ctx, uint64_t *enc, const uint64_t *plain_ntt, size_t batch, size_t size, size_t L, void *stream);
 int gsb_multiply_plain_coeff_host(gsb_ctx *ctx, uint64_t *enc, size_t size, size_t L, const uint64_t *plain, size_t count, uint64_t threshold, const uint64_t *increment, int lift);
 
+/* ---- switching-key generation -------------------------------------------------------
+ * KeyGenerator::generate_kswitch_keys / generate_one_kswitch_key (keygenerator.cpp:325-420) over
+ * util::encrypt_zero_symmetric (util/rlwe.cpp:204-304), batched over n_keys keys.  Randomness stays with the
+ * caller: a = [n_keys][beta][K][N] uniform residues in NTT form (the reference's sample_poly_uniform
+ * output, which becomes component 1 of every bundle), e = [n_keys][beta][N] the noise polynomials as SIGNED
+ * integers (sample_poly_normal writes e or q_i - |e| into every limb, rlwe.cpp:60-84).  The secret key must have
+ * been given with gsb_secret_key_set.  kind GSB_KEY_RELIN: ids[n] = key power >= 2 (new key = s^power,
+ * keygenerator.cpp:256-323; stored under RelinKeys::get_index(power)); kind GSB_KEY_GALOIS: ids[n] = Galois
+ * element (new key = apply_galois_ntt(s), keygenerator.cpp:99-101).  out = [n_keys][beta][2][K][N] exactly as
+ * KSwitchKeys::data()[index] lays its bundles out, or NULL with install = 1; install = 1 also places the keys in
+ * the context's key store (as gsb_key_upload would), so generated keys never have to leave the device.  Same
+ * sampled buffers in -> the reference's key words out. */
+int gsb_kswitch_keygen_dev(gsb_ctx *ctx, gsb_ws *ws, int kind, const uint32_t *ids, size_t n_keys, const uint64_t *a, const int64_t *e, uint64_t *out, int install, void *stream);
+int gsb_kswitch_keygen_host(gsb_ctx *ctx, int kind, const uint32_t *ids, size_t n_keys, const uint64_t *a, const int64_t *e, uint64_t *out, int install);
+
 /* ---- Decryptor (seal::Decryptor, decryptor.cpp) --------------------------------
  * gsb_secret_key_set: SecretKey::data() in NTT form at key level, sk_host = [K][N] canonical residues
  * (Decryptor::Decryptor, decryptor.cpp:21-58; rejects what is_valid_for(SecretKey) rejects).  Powers

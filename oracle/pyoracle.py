@@ -55,6 +55,7 @@ class Oracle:
         lib.so_ctx_destroy.argtypes = [vp]
         lib.so_ckks_multiply.argtypes = [vp, sz, vp, vp, vp]
         lib.so_ckks_multiply_sizes.argtypes = [vp, sz, vp, sz, vp, sz, vp]
+        lib.so_kswitch_keygen.argtypes = [vp, vp, vp, vp, vp, vp]
         lib.so_relinearize_sizes.argtypes = [vp, sz, sz, vp, vp, sz, i32, vp]
         lib.so_bfv_multiply_sizes.argtypes = [i32, C.POINTER(u64), sz, u64, vp, sz, vp, sz, vp]
         lib.so_switch_key.argtypes = [vp, sz, vp, vp, vp]
@@ -185,6 +186,14 @@ class OracleCtx:
         assert self.lib.so_relinearize(self.h, L, _p(c3), _p(key), _p(out)) == 0
         return out
 
+    def kswitch_keygen(self, sk, new_key, a, e):
+        """generate_one_kswitch_key from the sampled a [beta][K][N] (NTT form) and e [beta][N] (int64 noise)."""
+        a = np.ascontiguousarray(a, dtype=np.uint64)
+        e = np.ascontiguousarray(e, dtype=np.int64)
+        out = np.empty((a.shape[0], 2, self.K, self.N), dtype=np.uint64)
+        assert self.lib.so_kswitch_keygen(self.h, _p(np.ascontiguousarray(sk)), _p(np.ascontiguousarray(new_key)), _p(a), e.ctypes.data, _p(out)) == 0
+        return out
+
     def multiply_sizes(self, a, b):
         L, sa, sb = a.shape[1], a.shape[0], b.shape[0]
         out = np.empty((sa + sb - 1, L, self.N), dtype=np.uint64)
@@ -279,6 +288,7 @@ class RefLib:
         lib.ref_set_key.argtypes = [vp, i32, u32, vp]
         lib.ref_multiply.argtypes = [vp, sz, vp, vp, vp]
         lib.ref_set_relin_count.argtypes = [vp, sz]
+        lib.ref_get_secret_key.argtypes = [vp, vp]
         lib.ref_multiply_sizes.argtypes = [vp, sz, vp, sz, vp, sz, vp]
         lib.ref_relinearize_sizes.argtypes = [vp, sz, sz, vp, vp]
         lib.ref_relinearize.argtypes = [vp, sz, vp, vp]
@@ -395,6 +405,11 @@ class RefCtx:
         L = c3.shape[1]
         out = np.empty((2, L, self.N), dtype=np.uint64)
         self._run(self.lib.ref_relinearize(self.h, L, _p(c3), _p(out)))
+        return out
+
+    def secret_key(self):
+        out = np.empty((self.K, self.N), dtype=np.uint64)
+        self._run(self.lib.ref_get_secret_key(self.h, _p(out)))
         return out
 
     def set_relin_count(self, count):

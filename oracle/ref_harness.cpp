@@ -386,6 +386,17 @@ extern "C"
         });
     }
 
+    // SecretKey::data() of the KeyGenerator made by ref_keygen: NTT form at key level, [K][N]
+    int ref_get_secret_key(void *h, uint64_t *out)
+    {
+        auto *c = static_cast<RefCtx *>(h);
+        return guarded([&] {
+            if (!c->keygen)
+                throw std::logic_error("no key generator");
+            std::memcpy(out, c->keygen->secret_key().data().data(), c->K * c->N * 8);
+        });
+    }
+
     // how many relinearization keys ref_keygen / ref_make_synthetic_keys produce from now on (default 1)
     int ref_set_relin_count(void *h, size_t count)
     {

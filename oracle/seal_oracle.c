@@ -905,3 +905,54 @@ int so_mul_relin_rescale(const so_ctx *c, size_t L, const uint64_t *a, const uin
     free(t2);
     return rc;
 }
+
+/* ======================================================================================== */
+/* Switching-key generation                                            */
+/* ======================================================================================== */
+/* KeyGenerator::generate_one_kswitch_key (keygenerator.cpp:325-369) over util::encrypt_zero_symmetric
+ * (util/rlwe.cpp:204-304) with the SAMPLED buffers given: a = [beta][K][N] uniform residues in NTT form (the
+ * reference's c1, :232-241), e = [beta][N] the noise as signed integers (sample_poly_normal, rlwe.cpp:60-84,
+ * writes e or q_i - |e| into every limb).  sk, new_key = [K][N] NTT form at key level.  out = [beta][2][K][N]. */
+int so_kswitch_keygen(const so_ctx *c, const uint64_t *sk, const uint64_t *new_key, const uint64_t *a, const int64_t *e, uint64_t *out)
+{
+    const size_t N = c->N, K = c->K, KN = K * N, beta = (c->L0 + c->k - 1) / c->k;
+    uint64_t *noise = (uint64_t *)malloc(N * 8);
+    if (!noise)
+        return -1;
+    for (size_t j = 0; j < beta; j++)
+    {
+        uint64_t *c0 = out + j * 2 * KN, *c1 = c0 + KN;
+        memcpy(c1, a + j * KN, KN * 8);
+        for (size_t i = 0; i < K; i++)
+        {
+            const uint64_t q = c->q[i];
+            const uint64_t *cr = c->tab[i].cr;
+            for (size_t d = 0; d < N; d++)
+            {
+                const int64_t v = e[j * N + d];
+                noise[d] = v >= 0 ? (uint64_t)v : q - (uint64_t)(-v);
+            }
+            so_ntt_fwd(noise, &c->tab[i]); /* rlwe.cpp:263-266 */
+            for (size_t d = 0; d < N; d++)
+            {
+                uint64_t t = so_multiply_uint_mod(sk[i * N + d], c1[i * N + d], q, cr); /* :259-262 */
+                t = so_add_uint_mod(noise[d], t, q);                                    /* :271-273 */
+                c0[i * N + d] = so_negate_uint_mod(t, q);                               /* :274 */
+            }
+        }
+        /* keygenerator.cpp:346-366 */
+        const size_t rns0 = j * c->k, rns1 = rns0 + c->k < c->L0 ? rns0 + c->k : c->L0;
+        for (size_t rns = rns0; rns < rns1; rns++)
+        {
+            const uint64_t q = c->q[rns];
+            const uint64_t *cr = c->tab[rns].cr;
+            uint64_t factor = 1;
+            for (size_t s = 0; s < c->k; s++)
+                factor = so_multiply_uint_mod(factor, c->q[c->L0 + s], q, cr);
+            for (size_t d = 0; d < N; d++)
+                c0[rns * N + d] = so_add_uint_mod(c0[rns * N + d], so_multiply_uint_mod(new_key[rns * N + d], factor, q, cr), q);
+        }
+    }
+    free(noise);
+    return 0;
+}

@@ -84,6 +84,8 @@ int so_ckks_multiply_sizes(const so_ctx *c, size_t L, const uint64_t *a, size_t 
 int so_switch_key(const so_ctx *c, size_t L, uint64_t *enc, const uint64_t *target, const uint64_t *key);
 /* in [3][L][N] -> out [2][L][N] */
 int so_relinearize(const so_ctx *c, size_t L, const uint64_t *in, const uint64_t *key, uint64_t *out);
+/* row f2: generate_one_kswitch_key given the sampled a (NTT form) and e (signed noise) */
+int so_kswitch_keygen(const so_ctx *c, const uint64_t *sk, const uint64_t *new_key, const uint64_t *a, const int64_t *e, uint64_t *out);
 int so_relinearize_sizes(const so_ctx *c, size_t L, size_t size, const uint64_t *in, const uint64_t *keys, size_t key_words, int is_ckks, uint64_t *out);
 /* in [size][L][N] -> out [size][L-1][N] */
 int so_rescale(const so_ctx *c, size_t L, size_t size, const uint64_t *in, uint64_t *out);

@@ -2,6 +2,8 @@
 // polynomial arithmetic through the C ABI of the B200 library.  No CPU arithmetic fallback.
 #include "gsb_seal_shim.h"
 #include "seal/util/numth.h"
+#include "seal/util/rlwe.h"
+#include "seal/randomgen.h"
 #include "seal/util/uintcore.h"
 #include "seal/valcheck.h"
 #include <cmath>
@@ -1303,6 +1305,146 @@ namespace gsb_seal
     {
         own(e, "encrypted");
         check(gsb_poly_op_dev(ctx_, GSB_OP_NEGATE, e.d_, nullptr, nullptr, e.d_, e.batch_ * e.size_, e.L_, 0, nullptr));
+    }
+
+    // ---- KeyGenerator (keygenerator.cpp:51-180, 325-420) ---------------------------------------------------------
+    static gsb_ctx *keygen_ctx(const shared_ptr<SEALContext> &context, const SecretKey &sk, int device, size_t &N, size_t &K, size_t &beta)
+    {
+        auto &key_parms = context->key_context_data()->parms();
+        if (!context->using_keyswitching())
+            throw logic_error("keyswitching is not supported by the context");
+        N = key_parms.poly_modulus_degree();
+        K = key_parms.coeff_modulus().size();
+        const size_t L0 = context->first_context_data()->parms().coeff_modulus().size(), k = K - L0;
+        beta = (L0 + k - 1) / k;
+        vector<uint64_t> moduli;
+        for (auto &m : key_parms.coeff_modulus())
+            moduli.push_back(m.value());
+        int logn = 0;
+        while ((size_t(1) << logn) < N)
+            logn++;
+        gsb_ctx *c = nullptr;
+        check(gsb_ctx_create(device, logn, moduli.data(), K, k, &c));
+        const int rc = gsb_secret_key_set(c, sk.data().data());
+        if (rc != GSB_OK)
+        {
+            gsb_ctx_destroy(c);
+            raise(rc);
+        }
+        return c;
+    }
+
+    KeyGenerator::KeyGenerator(shared_ptr<SEALContext> context, int device) : context_(context), host_(context)
+    {
+        ctx_ = keygen_ctx(context_, host_.secret_key(), device, N_, K_, beta_);
+    }
+
+    KeyGenerator::KeyGenerator(shared_ptr<SEALContext> context, const SecretKey &secret_key, int device) : context_(context), host_(context, secret_key)
+    {
+        ctx_ = keygen_ctx(context_, host_.secret_key(), device, N_, K_, beta_);
+    }
+
+    KeyGenerator::~KeyGenerator()
+    {
+        gsb_ctx_destroy(ctx_);
+    }
+
+    // noise is secret-key-equivalent material: cleared through a volatile pointer so the stores are not elided
+    static void wipe(void *p, size_t bytes)
+    {
+        volatile unsigned char *v = static_cast<volatile unsigned char *>(p);
+        for (size_t i = 0; i < bytes; i++)
+            v[i] = 0;
+    }
+
+    // destinations[n] = the bundle vector of key n (KSwitchKeys::data()[index])
+    void KeyGenerator::generate(int kind, const vector<uint32_t> &ids, vector<vector<PublicKey> *> &destinations)
+    {
+        auto &key_cd = *context_->key_context_data();
+        auto &parms = key_cd.parms();
+        const size_t n = ids.size(), KN = K_ * N_;
+        if (n == 0)
+            return;
+        // the reference's draws, in its order per bundle: a from a fresh Blake PRNG, then e from the parameters'
+        // generator (util/rlwe.cpp:232-258)
+        vector<uint64_t> a(n * beta_ * KN), noise(KN);
+        vector<int64_t> e(n * beta_ * N_);
+        const uint64_t q0 = parms.coeff_modulus()[0].value();
+        for (size_t r = 0; r < n * beta_; r++)
+        {
+            auto rng_error = parms.random_generator()->create();
+            shared_ptr<UniformRandomGenerator> rng_ciphertext = BlakePRNGFactory().create();
+            seal::util::sample_poly_uniform(rng_ciphertext, parms, a.data() + r * KN);
+            seal::util::sample_poly_normal(rng_error, parms, noise.data());
+            for (size_t d = 0; d < N_; d++) // limb 0 holds e or q_0 - |e| (rlwe.cpp:68-84)
+                e[r * N_ + d] = noise[d] > (q0 >> 1) ? -static_cast<int64_t>(q0 - noise[d]) : static_cast<int64_t>(noise[d]);
+        }
+        wipe(noise.data(), noise.size() * sizeof(uint64_t));
+        vector<uint64_t> out(n * beta_ * 2 * KN);
+        check(gsb_kswitch_keygen_host(ctx_, kind, ids.data(), n, a.data(), e.data(), out.data(), 0));
+        wipe(e.data(), e.size() * sizeof(int64_t));
+        for (size_t i = 0; i < n; i++)
+        {
+            auto &dst = *destinations[i];
+            dst.resize(beta_);
+            for (size_t j = 0; j < beta_; j++)
+            {
+                Ciphertext &ct = dst[j].data(); // what encrypt_zero_symmetric leaves (rlwe.cpp:228-230)
+                ct.resize(context_, key_cd.parms_id(), 2);
+                ct.is_ntt_form() = true;
+                ct.scale() = 1.0;
+                memcpy(ct.data(), out.data() + (i * beta_ + j) * 2 * KN, 2 * KN * sizeof(uint64_t));
+            }
+        }
+    }
+
+    RelinKeys KeyGenerator::relin_keys_local()
+    {
+        RelinKeys keys; // keygenerator.cpp:138-180 with count = 1
+        keys.data().resize(1);
+        vector<vector<PublicKey> *> dst{ &keys.data()[0] };
+        generate(GSB_KEY_RELIN, { 2 }, dst);
+        keys.parms_id() = context_->key_parms_id();
+        return keys;
+    }
+
+    GaloisKeys KeyGenerator::galois_keys_local(const vector<uint32_t> &galois_elts)
+    {
+        auto &context_data = *context_->key_context_data(); // keygenerator.cpp:51-116
+        if (!context_data.qualifiers().using_batching)
+            throw logic_error("encryption parameters do not support batching");
+        GaloisKeys keys;
+        keys.data().resize(N_);
+        vector<uint32_t> ids;
+        vector<vector<PublicKey> *> dst;
+        for (auto elt : galois_elts)
+        {
+            if (!(elt & 1) || (elt >= N_ << 1))
+                throw invalid_argument("Galois element is not valid");
+            const size_t index = GaloisKeys::get_index(elt);
+            bool seen = false;
+            for (auto id : ids)
+                seen = seen || id == elt;
+            if (seen) // "do we already have the key?" (:93-96)
+                continue;
+            ids.push_back(elt);
+            dst.push_back(&keys.data()[index]);
+        }
+        generate(GSB_KEY_GALOIS, ids, dst);
+        keys.parms_id() = context_data.parms_id();
+        return keys;
+    }
+
+    GaloisKeys KeyGenerator::galois_keys_local(const vector<int> &steps)
+    {
+        if (!context_->key_context_data()->qualifiers().using_batching) // keygenerator.h:176-183
+            throw logic_error("encryption parameters do not support batching");
+        return galois_keys_local(context_->key_context_data()->galois_tool()->get_elts_from_steps(steps));
+    }
+
+    GaloisKeys KeyGenerator::galois_keys_local()
+    {
+        return galois_keys_local(context_->key_context_data()->galois_tool()->get_elts_all());
     }
 
     // ---- Decryptor (decryptor.cpp:21-149) ------------------------------------------------------------------

@@ -223,6 +223,35 @@ namespace gsb_seal
         std::map<std::uint32_t, std::uint64_t> relin_loaded_, galois_loaded_;
     };
 
+    // seal::KeyGenerator's switching-key generation (keygenerator.h:82-230 / keygenerator.cpp:51-180, 325-420; SURVEY
+    // 8(f) row f2).  The secret key (and public key) come from the reference's KeyGenerator; randomness comes from the
+    // reference's own samplers (util::sample_poly_uniform / sample_poly_normal, util/rlwe.cpp:60-129) exactly as
+    // encrypt_zero_symmetric draws it; the arithmetic -- noise NTT, -(a s + e), secret-key powers / Galois-permuted
+    // key, the P * s_new add -- runs on the device, all keys of a call in one batched pass.  The returned objects
+    // are ordinary seal::RelinKeys / seal::GaloisKeys.
+    class KeyGenerator
+    {
+    public:
+        explicit KeyGenerator(std::shared_ptr<seal::SEALContext> context, int device = 0);
+        KeyGenerator(std::shared_ptr<seal::SEALContext> context, const seal::SecretKey &secret_key, int device = 0);
+        ~KeyGenerator();
+        KeyGenerator(const KeyGenerator &) = delete;
+        KeyGenerator &operator=(const KeyGenerator &) = delete;
+        const seal::SecretKey &secret_key() const { return host_.secret_key(); }
+        seal::PublicKey public_key() const { return host_.public_key(); }
+        seal::RelinKeys relin_keys_local();
+        seal::GaloisKeys galois_keys_local(const std::vector<std::uint32_t> &galois_elts);
+        seal::GaloisKeys galois_keys_local(const std::vector<int> &steps);
+        seal::GaloisKeys galois_keys_local();
+
+    private:
+        void generate(int kind, const std::vector<std::uint32_t> &ids, std::vector<std::vector<seal::PublicKey> *> &destinations);
+        std::shared_ptr<seal::SEALContext> context_;
+        seal::KeyGenerator host_; // secret / public key and their checks
+        gsb_ctx *ctx_ = nullptr;
+        std::size_t N_ = 0, K_ = 0, beta_ = 0;
+    };
+
     // seal::Decryptor (decryptor.h:62-120 / decryptor.cpp:21-149, 218-265): the secret
     // key's NTT-form limbs live on the device, decrypt() runs the dot product c_0 + c_1 s + ... there
     // (and, for BFV, RNSTool::decrypt_scale_and_round) and fills the same seal::Plaintext the reference

@@ -225,13 +225,31 @@ int main(int argc, char **argv)
             resident_ms = ms_since(t0) / res_reps;
         }
 
+        // ---- key generation (row f2): one relin key + one Galois key, seal::KeyGenerator vs the device route --------
+        double keygen_dev_ms = 0, keygen_ref_ms = 0;
+        {
+            KeyGenerator kg(context);
+            gsb_seal::KeyGenerator dkg(context, kg.secret_key());
+            auto t0 = clk::now();
+            RelinKeys r1 = kg.relin_keys_local();
+            GaloisKeys g1 = kg.galois_keys_local(vector<uint32_t>{ elt });
+            keygen_ref_ms = ms_since(t0);
+            (void)dkg.relin_keys_local(); // warm-up (context tables, workspace)
+            t0 = clk::now();
+            RelinKeys r2 = dkg.relin_keys_local();
+            GaloisKeys g2 = dkg.galois_keys_local(vector<uint32_t>{ elt });
+            keygen_dev_ms = ms_since(t0);
+            parity = parity && is_valid_for(r2, context) && is_valid_for(g2, context) && r1.data()[0].size() == r2.data()[0].size();
+        }
+
         printf("{\"workload\": \"CKKS N=32768 BFVDefault (L=15, K=16): seal::Ciphertext / RelinKeys / GaloisKeys objects, synthetic uniform residues\", "
                "\"parity_ok\": %s, \"batch\": %zu, \"per_call_ms\": {",
                parity ? "true" : "false", B);
         for (size_t i = 0; i < rows.size(); i++)
             printf("%s\"%s\": {\"gsb_seal\": %.3f, \"gsb_seal_first_call\": %.3f, \"seal_cpu_1thread\": %.3f}", i ? ", " : "", rows[i].name,
                    rows[i].dev_ms, rows[i].dev_first_ms, rows[i].ref_ms);
-        printf("}, \"chain_ops_per_s\": %.1f, \"fused_chain_ops_per_s\": %.1f, \"fused_resident_ops_per_s\": %.1f, "
+        printf("}, \"keygen_relin_plus_galois_ms\": {\"gsb_seal\": %.1f, \"seal_cpu_1thread\": %.1f}", keygen_dev_ms, keygen_ref_ms);
+        printf(", \"chain_ops_per_s\": %.1f, \"fused_chain_ops_per_s\": %.1f, \"fused_resident_ops_per_s\": %.1f, "
                "\"chain_ms\": %.3f, \"fused_chain_ms\": %.3f, \"fused_resident_ms\": %.3f, "
                "\"note\": \"per-call = batch 1 on pageable host objects (H2D + kernels + D2H per call, the copy of the operand subtracted); chain = upload "
                "2 x B ciphertexts from pageable seal memory, run, download B; resident = operands already in HBM\"}\n",

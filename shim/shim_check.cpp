@@ -350,6 +350,35 @@ static int run(size_t N, vector<int> bits, int k_special)
         for (size_t i = 0; i < 3; i++)
             same("batched mul+relin+rescale", want[i], xs[i]);
     }
+    {
+        // row f2: switching keys generated on the device (reference samplers for the randomness) must work under the
+        // REFERENCE's evaluator and decryptor: relinearized product and a rotation decrypt to the right values, and
+        // the keys pass the reference's own validity check
+        gsb_seal::KeyGenerator dkg(context, sk);
+        RelinKeys drlk = dkg.relin_keys_local();
+        GaloisKeys dglk = dkg.galois_keys_local(vector<int>{ 1, -2 });
+        // same verdicts as for the reference's own keys (this fork's is_metadata_valid_for rejects its own keys when
+        // there is more than one special prime), canonical data, same bundle count
+        const bool valid = is_valid_for(drlk, context) == is_valid_for(rlk, context) && is_valid_for(dglk, context) == is_valid_for(glk, context) &&
+                           is_data_valid_for(drlk, context) && is_data_valid_for(dglk, context) && is_buffer_valid(drlk) && is_buffer_valid(dglk) &&
+                           drlk.data()[0].size() == rlk.data()[0].size();
+        printf("%-34s %s\n", "device keygen: validity as reference", valid ? "yes" : "NO");
+        failures += !valid;
+        Ciphertext x = a;
+        ref.multiply_inplace(x, b);
+        ref.relinearize_inplace(x, drlk);
+        ref.rescale_to_next_inplace(x);
+        ref.rotate_vector_inplace(x, 1, dglk);
+        Plaintext px;
+        dec.decrypt(x, px);
+        vector<double> ox;
+        encoder.decode(px, ox);
+        double errk = 0;
+        for (size_t i = 0; i < slots; i++)
+            errk = max(errk, fabs(ox[i] - va[(i + 1) % slots] * vb[(i + 1) % slots]));
+        printf("%-34s max |err| = %.3g %s\n", "device keys: relin + rotate decrypt", errk, errk < 1e-4 ? "ok" : "TOO LARGE");
+        failures += !(errk < 1e-4);
+    }
     // semantic check: decrypt the device product
     Plaintext pd;
     dec.decrypt(prod, pd);

@@ -268,3 +268,110 @@ def check_threshold_and_patterns(lib, oracle, logn, literal_too=True, light=Fals
                         want.append(oracle.ntt_rns(logn, mods, oracle.ntt_rns(logn, mods, a, 3), 1))
                     for i, (x, y) in enumerate(zip(got, want)):
                         assert np.array_equal(x, y), (logn, qbig, literal, i)
+
+
+def keygen_inputs_from_key(oracle, logn, mods, k, sk, new_key, key):
+    """Recover what the reference SAMPLED for a switching key it generated (its samplers are not
+    reproducible, but a key stores a = component 1, and e follows from c0 = -(a s + e) + [factor * new_key]):
+    returns a [beta][K][N] and e [beta][N] (int64).  Asserts that e is the same small integer under every limb."""
+    N, K = 1 << logn, len(mods)
+    L0 = K - k
+    beta = key.shape[0]
+    a = np.ascontiguousarray(key[:, 1])
+    e = np.empty((beta, N), dtype=np.int64)
+    for j in range(beta):
+        per_limb = []
+        for i, q in enumerate(mods):
+            c0 = key[j, 0, i]
+            if j * k <= i < min(j * k + k, L0):
+                factor = 1
+                for s in range(k):
+                    factor = factor * mods[L0 + s] % q
+                c0 = oracle.poly_op(2, q, c0, oracle.poly_op(4, q, new_key[i], scalar=factor))       # c0 - factor * new_key
+            t = oracle.poly_op(1, q, c0, oracle.poly_op(0, q, sk[i], a[j, i]))                        # c0 + a s = -e
+            en = oracle.ntt(logn, q, oracle.poly_op(3, q, t), 3).astype(np.int64)                     # strict inverse NTT of e
+            per_limb.append(np.where(en > q // 2, en - q, en))
+        for x in per_limb[1:]:
+            assert np.array_equal(x, per_limb[0])
+        assert np.abs(per_limb[0]).max() < 64  # clipped normal, sigma = 3.2 (util/rlwe.cpp:60-84)
+        e[j] = per_limb[0]
+    return a, e
+
+
+def reference_keys_for_keygen(reflib, oracle, logn, mods, k, steps):
+    """Keys from the reference's own KeyGenerator plus everything needed to regenerate them: (sk, relin key,
+    {elt: galois key}, new keys, sampled a / e per key)."""
+    N = 1 << logn
+    rc = reflib.context(N, mods, k)
+    elts = [rc.elt_from_step(s) for s in steps]
+    rc.keygen(elts)
+    sk = rc.secret_key()
+    out = {"sk": sk, "elts": elts, "keys": [], "new": [], "a": [], "e": []}
+    s2 = np.stack([oracle.poly_op(0, q, sk[i], sk[i]) for i, q in enumerate(mods)])
+    cases = [(rc.get_key(0, 0), s2)]
+    for elt in elts:
+        t = oracle.galois_table_ntt(logn, elt)
+        cases.append((rc.get_key(1, elt), np.ascontiguousarray(sk[:, t])))
+    for key, new in cases:
+        a, e = keygen_inputs_from_key(oracle, logn, mods, k, sk, new, key)
+        out["keys"].append(key), out["new"].append(new), out["a"].append(a), out["e"].append(e)
+    return out
+
+
+def check_keygen_fixture(lib, fx, to_device=None):
+    """Row f2 on the device: the fixture's sampled buffers in -> the reference's key words out (relin key + Galois
+    keys, one batched call each), then an installed key must key-switch like the uploaded one."""
+    import gemini_seal_b200 as g
+    to_device = to_device or (lambda x: x)
+    back = lambda x: x if isinstance(x, np.ndarray) else x.cpu().numpy().view(np.uint64)
+    mods, k, logn = fx["mods"], fx["k"], fx["logn"]
+    N = 1 << logn
+    ctx = g.Context(N, mods, k, lib=lib)
+    kg = g.KeyGenerator(ctx, fx["sk"])
+    dev_e = lambda e: to_device(e) if to_device(e) is e else to_device(e.view(np.uint64))
+    relin = kg.relin_keys(to_device(fx["a"][:1]), dev_e(fx["e"][:1]), count=1, install=True)
+    assert np.array_equal(back(relin)[0], fx["keys"][0]), "relin key"
+    if len(fx["elts"]):
+        gal = kg.galois_keys(fx["elts"], to_device(fx["a"][1:]), dev_e(fx["e"][1:]), install=True)
+        for n, elt in enumerate(fx["elts"]):
+            assert np.array_equal(back(gal)[n], fx["keys"][1 + n]), ("galois key", elt)
+    # the installed keys serve key switching exactly like uploaded ones
+    L = len(mods) - k
+    rng = np.random.default_rng(7)
+    c3 = rand_poly(rng, mods[:L], (2, 3), N)
+    c2 = rand_poly(rng, mods[:L], (2, 2), N)
+    ev = g.Evaluator(ctx)
+    got_r = ev.relinearize(c3)
+    got_g = [ev.apply_galois(c2, elt) for elt in fx["elts"]]
+    ctx2 = g.Context(N, mods, k, lib=lib)
+    ctx2.set_relin_keys(fx["keys"][0])
+    ev2 = g.Evaluator(ctx2)
+    assert np.array_equal(got_r, ev2.relinearize(c3))
+    for n, elt in enumerate(fx["elts"]):
+        ctx2.set_galois_key(elt, fx["keys"][1 + n])
+        assert np.array_equal(got_g[n], ev2.apply_galois(c2, elt))
+    ctx.close()
+    ctx2.close()
+
+
+def load_keygen_fixture(name):
+    import os
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", name + ".npz"))
+    n = z["keys"].shape[0]
+    return {"logn": int(z["logn"]), "mods": [int(q) for q in z["mods"]], "k": int(z["k"]), "sk": z["sk"], "elts": [int(x) for x in z["elts"]],
+            "keys": [z["keys"][i] for i in range(n)], "a": z["a"], "e": z["e"]}
+
+
+def oracle_keygen(oracle, fx_or_ctx, logn, mods, k, sk, ids, galois, a, e):
+    """All keys of a batch through the oracle: ids = key powers (galois False) or Galois elements (True)."""
+    oc = oracle.context(logn, mods, k)
+    out = []
+    for n, ident in enumerate(ids):
+        if galois:
+            new = np.ascontiguousarray(sk[:, oracle.galois_table_ntt(logn, ident)])
+        else:
+            new = sk
+            for _ in range(ident - 1):
+                new = np.stack([oracle.poly_op(0, q, new[i], sk[i]) for i, q in enumerate(mods)])
+        out.append(oc.kswitch_keygen(sk, new, a[n], e[n]))
+    return np.stack(out)

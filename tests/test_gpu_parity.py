@@ -234,6 +234,41 @@ def test_fuzz_against_oracle(cudalib, oracle, seed):
     fuzz_against_oracle(cudalib, oracle, seed=seed, n_configs=12, max_logn=14)
 
 
+@pytest.mark.parametrize("name", ["keygen_n1024_k1", "keygen_n2048_k2_ragged"])
+def test_keygen_reproduces_reference_keys(cudalib, name):
+    """Row f2: the buffers the reference's KeyGenerator sampled in -> its relin and Galois keys out, word for word
+    (host buffers and device buffers); installed keys serve key switching like uploaded ones."""
+    import torch
+    from common import check_keygen_fixture, load_keygen_fixture
+    fx = load_keygen_fixture(name)
+    check_keygen_fixture(cudalib, fx)
+    check_keygen_fixture(cudalib, fx, to_device=lambda x: torch.from_numpy(x.view(np.int64)).cuda())
+
+
+@pytest.mark.parametrize("tag", ["c3", "c4"])
+def test_keygen_full_size_vs_oracle(cudalib, oracle, tag):
+    """Row f2 at the C3 / C4 shapes: a relin key and two Galois keys from synthetic sampled buffers, device (one batched
+    call) against the oracle."""
+    import gemini_seal_b200 as g
+    from common import oracle_keygen
+    n = {"c3": 16384, "c4": 32768}[tag]
+    mods = golden_cases.BFV_DEFAULT[n]
+    logn, K = n.bit_length() - 1, len(mods)
+    beta = K - 1
+    rng = np.random.default_rng(n + 2)
+    sk = rand_poly(rng, mods, (), n)
+    ctx = g.Context(n, mods, 1, lib=cudalib)
+    kg = g.KeyGenerator(ctx, sk)
+    elts = [ctx.galois_elt_from_step(1), 2 * n - 1]
+    a = rand_poly(rng, mods, (3, beta), n)
+    e = rng.integers(-19, 20, size=(3, beta, n), dtype=np.int64)
+    got_r = kg.relin_keys(a[:1], e[:1])
+    got_g = kg.galois_keys(elts, a[1:], e[1:])
+    assert np.array_equal(got_r, oracle_keygen(oracle, None, logn, mods, 1, sk, [2], False, a[:1], e[:1]))
+    assert np.array_equal(got_g, oracle_keygen(oracle, None, logn, mods, 1, sk, elts, True, a[1:], e[1:]))
+    ctx.close()
+
+
 def test_error_convention(cudalib):
     """Argument errors -> ValueError (std::invalid_argument), evaluator.cpp:238-249,781-796,1872-1887."""
     import gemini_seal_b200 as g

@@ -264,3 +264,28 @@ def test_bench_digests_and_synth(oracle):
     want = bench.load_digests()["c3"]
     assert bench.digest(oc.mul_relin_rescale(ca, cb, keys[0])) == want["mrr"]["255"]
     assert bench.digest(oc.apply_galois(ca, oracle.elt_from_step(w.logn, 1), keys[1])) == want["rot"]["255"]
+
+
+@pytest.mark.parametrize("name", ["keygen_n1024_k1", "keygen_n2048_k2_ragged"])
+def test_keygen_oracle_reproduces_reference_keys(oracle, name):
+    """Row f2: the restated generate_one_kswitch_key / encrypt_zero_symmetric, given the buffers the reference sampled
+    (committed fixture, tests/golden/make_keygen_fixtures.py), reproduces the reference KeyGenerator's relin and Galois
+    keys word for word."""
+    from common import load_keygen_fixture, oracle_keygen
+    fx = load_keygen_fixture(name)
+    got = oracle_keygen(oracle, None, fx["logn"], fx["mods"], fx["k"], fx["sk"], [2], False, fx["a"][:1], fx["e"][:1])
+    assert np.array_equal(got[0], fx["keys"][0])
+    got = oracle_keygen(oracle, None, fx["logn"], fx["mods"], fx["k"], fx["sk"], fx["elts"], True, fx["a"][1:], fx["e"][1:])
+    for n in range(len(fx["elts"])):
+        assert np.array_equal(got[n], fx["keys"][1 + n])
+
+
+def test_keygen_oracle_vs_live_reference(oracle, reflib):
+    """The same against keys the reference generates now (fresh randomness), k = 3 with a ragged last bundle."""
+    from common import oracle_keygen, reference_keys_for_keygen
+    logn, k = 10, 3
+    mods = mixed_moduli(logn, [40, 40, 40, 40, 41, 41, 41])
+    fx = reference_keys_for_keygen(reflib, oracle, logn, mods, k, [1])
+    a, e = np.stack(fx["a"]), np.stack(fx["e"])
+    assert np.array_equal(oracle_keygen(oracle, None, logn, mods, k, fx["sk"], [2], False, a[:1], e[:1])[0], fx["keys"][0])
+    assert np.array_equal(oracle_keygen(oracle, None, logn, mods, k, fx["sk"], fx["elts"], True, a[1:], e[1:])[0], fx["keys"][1])

@@ -78,3 +78,10 @@ def test_sim_threshold_primes_and_extreme_patterns(simlib, oracle):
     no-wrap precondition on these inputs (the GPU suite repeats it at N = 2^12, 2^13, 2^15)."""
     from common import check_threshold_and_patterns
     check_threshold_and_patterns(simlib, oracle, 10, light=True)
+
+
+@pytest.mark.parametrize("name", ["keygen_n1024_k1", "keygen_n2048_k2_ragged"])
+def test_sim_keygen_reproduces_reference_keys(simlib, name):
+    """Row f2 under the simulator: sampled buffers of the reference in -> the reference's key words out."""
+    from common import check_keygen_fixture, load_keygen_fixture
+    check_keygen_fixture(simlib, load_keygen_fixture(name))
