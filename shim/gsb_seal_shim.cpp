@@ -8,7 +8,9 @@
 #include "seal/valcheck.h"
 #include <cmath>
 #include <cstring>
+#include <atomic>
 #include <stdexcept>
+#include <thread>
 #include <utility>
 
 using namespace seal;
@@ -1367,19 +1369,42 @@ namespace gsb_seal
             return;
         // the reference's draws, in its order per bundle: a from a fresh Blake PRNG, then e from the parameters'
         // generator (util/rlwe.cpp:232-258)
-        vector<uint64_t> a(n * beta_ * KN), noise(KN);
+        vector<uint64_t> a(n * beta_ * KN);
         vector<int64_t> e(n * beta_ * N_);
         const uint64_t q0 = parms.coeff_modulus()[0].value();
-        for (size_t r = 0; r < n * beta_; r++)
-        {
-            auto rng_error = parms.random_generator()->create();
-            shared_ptr<UniformRandomGenerator> rng_ciphertext = BlakePRNGFactory().create();
-            seal::util::sample_poly_uniform(rng_ciphertext, parms, a.data() + r * KN);
-            seal::util::sample_poly_normal(rng_error, parms, noise.data());
-            for (size_t d = 0; d < N_; d++) // limb 0 holds e or q_0 - |e| (rlwe.cpp:68-84)
-                e[r * N_ + d] = noise[d] > (q0 >> 1) ? -static_cast<int64_t>(q0 - noise[d]) : static_cast<int64_t>(noise[d]);
-        }
-        wipe(noise.data(), noise.size() * sizeof(uint64_t));
+        // every bundle draws from its own freshly seeded generators, so the rows are sampled by a few host threads
+        const size_t rows = n * beta_;
+        const size_t n_threads = max<size_t>(1, min<size_t>({ rows, size_t(thread::hardware_concurrency()), size_t(16) }));
+        atomic<size_t> next{ 0 };
+        atomic<bool> failed{ false };
+        auto worker = [&] {
+            try
+            {
+                vector<uint64_t> noise(KN);
+                for (size_t r = next.fetch_add(1); r < rows; r = next.fetch_add(1))
+                {
+                    auto rng_error = parms.random_generator()->create();
+                    shared_ptr<UniformRandomGenerator> rng_ciphertext = BlakePRNGFactory().create();
+                    seal::util::sample_poly_uniform(rng_ciphertext, parms, a.data() + r * KN);
+                    seal::util::sample_poly_normal(rng_error, parms, noise.data());
+                    for (size_t d = 0; d < N_; d++) // limb 0 holds e or q_0 - |e| (rlwe.cpp:68-84)
+                        e[r * N_ + d] = noise[d] > (q0 >> 1) ? -static_cast<int64_t>(q0 - noise[d]) : static_cast<int64_t>(noise[d]);
+                }
+                wipe(noise.data(), noise.size() * sizeof(uint64_t));
+            }
+            catch (...)
+            {
+                failed = true;
+            }
+        };
+        vector<thread> pool;
+        for (size_t t = 1; t < n_threads; t++)
+            pool.emplace_back(worker);
+        worker();
+        for (auto &t : pool)
+            t.join();
+        if (failed)
+            throw runtime_error("key generation: sampling failed");
         vector<uint64_t> out(n * beta_ * 2 * KN);
         check(gsb_kswitch_keygen_host(ctx_, kind, ids.data(), n, a.data(), e.data(), out.data(), 0));
         wipe(e.data(), e.size() * sizeof(int64_t));
