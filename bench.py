@@ -636,7 +636,28 @@ def run_ours(args):
     e2e_steps = max(1, min(args.steps, 5))
     ms_e2e = timed(step_e2e, e2e_steps)
     e2e_value = world * B * e2e_steps / (ms_e2e / 1e3)
-    del ha, hb, hout
+    # the box's PCIe ceiling for exactly this traffic: every rank copies a step's input bytes host->device and a step's
+    # output bytes device->host concurrently (two streams, pinned memory, no kernels), all ranks at once
+    s_in, s_out = torch.cuda.Stream(), torch.cuda.Stream()
+    da_, db_, dout_ = torch.empty_like(a), torch.empty_like(b), torch.empty_like(out)
+
+    def step_copy():
+        s_in.wait_stream(torch.cuda.current_stream())
+        s_out.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s_in):
+            da_.copy_(ha, non_blocking=True)
+            db_.copy_(hb, non_blocking=True)
+        with torch.cuda.stream(s_out):
+            hout.copy_(dout_, non_blocking=True)
+        torch.cuda.current_stream().wait_stream(s_in)
+        torch.cuda.current_stream().wait_stream(s_out)
+    step_copy()
+    ms_copy = timed(step_copy, e2e_steps)
+    pcie = {"ms_per_step": ms_copy / e2e_steps, "h2d_gbs_aggregate": world * 2 * B * 2 * L * w.limb_bytes * e2e_steps / (ms_copy / 1e3) / 1e9,
+            "d2h_gbs_aggregate": world * B * 2 * (L - 1) * w.limb_bytes * e2e_steps / (ms_copy / 1e3) / 1e9,
+            "ops_per_s_ceiling": world * B * e2e_steps / (ms_copy / 1e3),
+            "what": "the same pinned H2D + D2H bytes per step on every rank at once, no kernels: the host / PCIe ceiling of the e2e number"}
+    del ha, hb, hout, da_, db_, dout_
 
     # ---- secondary numbers (short, outside the headline region)
     extra = {}
@@ -737,7 +758,8 @@ def run_ours(args):
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64",
             "data": "synthetic", "config": config_dict(w, B, world),
             "e2e": {"value": e2e_value, "unit": "ops/s", "h2d_bytes_per_step": 2 * B * 2 * L * w.limb_bytes,
-                    "d2h_bytes_per_step": B * 2 * (L - 1) * w.limb_bytes, "steps": e2e_steps, "ms_per_step": ms_e2e / e2e_steps},
+                    "d2h_bytes_per_step": B * 2 * (L - 1) * w.limb_bytes, "steps": e2e_steps, "ms_per_step": ms_e2e / e2e_steps,
+                    "pcie_ceiling": pcie, "frac_of_pcie_ceiling": e2e_value / pcie["ops_per_s_ceiling"]},
             "gpu_launches": int(launches), "clocks": clocks, "parity_checked": parity, "roofline": roofline, "cpu_baseline": cpu,
             "extra": extra, "kernels": kernels,
         }

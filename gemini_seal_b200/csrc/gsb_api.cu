@@ -256,6 +256,7 @@ int gsb_ctx_create(int device, int logn, const uint64_t *moduli, size_t K, size_
             const u128 beta0 = (ctx->L0 + ctx->k - 1) / ctx->k;
             ctx->fast_ntt = static_cast<u128>(qmax) * growth < (static_cast<u128>(1) << 63);
             ctx->lazy_modup = ctx->fast_ntt;
+            ctx->fast_fwd_public = static_cast<u128>(qmax) * (growth + 2) < (static_cast<u128>(1) << 63);
             ctx->lazy_mac = ctx->fast_ntt && static_cast<u128>(qmax) * qmax <= ~static_cast<u128>(0) / (beta0 * growth);
             // GSB_LITERAL=1 (read at context creation; a testing aid): every congruent-word shortcut off, the
             // kernels carry the reference's own intermediate words.  tests/test_gpu_parity.py runs the full
@@ -266,7 +267,7 @@ int gsb_ctx_create(int device, int logn, const uint64_t *moduli, size_t K, size_
             const char *lit = std::getenv("GSB_LITERAL");
             if (lit && lit[0] == '1')
             {
-                ctx->fast_ntt = ctx->lazy_modup = ctx->lazy_mac = ctx->wide_inv = false;
+                ctx->fast_ntt = ctx->fast_fwd_public = ctx->lazy_modup = ctx->lazy_mac = ctx->wide_inv = false;
                 for (auto &c : limb)
                     c.mu = 0;
             }
@@ -476,7 +477,8 @@ static void ntt_dev(
         }
         else
         {
-            GSB_DISPATCH_LOGN(ctx->logn, ntt_forward_plain<LOGN>(tab, mm, p, per, p, per, static_cast<int>(n_limbs), nz, lazy, st));
+            // strict output is canonical either way: wide-range stages when no word can reach 2^63 from an input < 4q
+            GSB_DISPATCH_LOGN(ctx->logn, ntt_forward_plain<LOGN>(tab, mm, p, per, p, per, static_cast<int>(n_limbs), nz, lazy, st, "plain", !lazy && ctx->fast_fwd_public));
         }
     }
     GSB_CUDA_CHECK(cudaGetLastError());

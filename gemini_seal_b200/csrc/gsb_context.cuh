@@ -97,6 +97,8 @@ struct gsb_ctx
     //   lazy_modup: = fast_ntt                        (single-limb bundle enters the NTT unreduced)
     //   lazy_mac:   beta0 (5n + 2) q_max^2 < 2^128    (sum of beta0 products operand x key)
     bool fast_ntt = false;
+    //   fast_fwd_public: q_max (5n + 4) < 2^63        (the public strict forward NTT may be handed lazy words < 4q)
+    bool fast_fwd_public = false;
     //   wide_inv:   10 q_max < 2^63                   (wide-range inverse butterflies keep words in [0,5q);
     //                                                  no growth, so it also holds for 59-bit moduli)
     bool wide_inv = false;

@@ -297,21 +297,35 @@ namespace gsb
 
     // Plain batched transforms: element (z, y, d) of src/dst at base + z*zs + y*N + d; in place
     // allowed (src == dst with equal strides).
-    template <int LOGN>
-    inline void ntt_forward_plain(
+    // wide: run the wide-range forward butterflies (fwd_round FAST) in every stage but the global last one.
+    // Callers pass it only under gsb_ctx::fast_ntt, for canonical inputs (< q) and only when the output is
+    // strict (canonicalised by finish<OUT_FWD_STRICT>, hence the same words as the literal transform).
+    template <int LOGN, bool FAST>
+    inline void ntt_forward_plain_t(
         const NttTables &tab, const ModMap &mm, const uint64_t *src, size_t src_zs, uint64_t *dst, size_t dst_zs, int ny,
-        int nz, bool lazy, cudaStream_t st, const char *tag = "plain")
+        int nz, bool lazy, cudaStream_t st, const char *tag)
     {
         if constexpr (Split<LOGN>::two_pass)
         {
-            launch_fwd_cols<LOGN>(IoPlain<OUT_RAW>{ src, dst, src_zs, dst_zs }, tab, mm, ny, nz, st, tag);
+            launch_fwd_cols<LOGN, FAST>(IoPlain<OUT_RAW>{ src, dst, src_zs, dst_zs }, tab, mm, ny, nz, st, tag);
             src = dst;
             src_zs = dst_zs;
         }
         if (lazy)
-            launch_fwd_contig<LOGN>(IoPlain<OUT_RAW>{ src, dst, src_zs, dst_zs }, tab, mm, ny, nz, st, tag);
+            launch_fwd_contig<LOGN, FAST>(IoPlain<OUT_RAW>{ src, dst, src_zs, dst_zs }, tab, mm, ny, nz, st, tag);
         else
-            launch_fwd_contig<LOGN>(IoPlain<OUT_FWD_STRICT>{ src, dst, src_zs, dst_zs }, tab, mm, ny, nz, st, tag);
+            launch_fwd_contig<LOGN, FAST>(IoPlain<OUT_FWD_STRICT>{ src, dst, src_zs, dst_zs }, tab, mm, ny, nz, st, tag);
+    }
+
+    template <int LOGN>
+    inline void ntt_forward_plain(
+        const NttTables &tab, const ModMap &mm, const uint64_t *src, size_t src_zs, uint64_t *dst, size_t dst_zs, int ny,
+        int nz, bool lazy, cudaStream_t st, const char *tag = "plain", bool wide = false)
+    {
+        if (wide && !lazy)
+            ntt_forward_plain_t<LOGN, true>(tab, mm, src, src_zs, dst, dst_zs, ny, nz, lazy, st, tag);
+        else
+            ntt_forward_plain_t<LOGN, false>(tab, mm, src, src_zs, dst, dst_zs, ny, nz, lazy, st, tag);
     }
 
     // wide: run the wide-range inverse butterflies (inv_round FAST).  Callers pass it only under

@@ -102,7 +102,9 @@ int gsb_stream_sync(gsb_ctx *ctx, void *stream);
 
 /* ---- NTT: util::ntt_negacyclic_harvey[_lazy] / inverse_... over RNSIter / PolyIter --------------
  * (util/ntt.h:189-368).  data = [n_polys][n_limbs][N]; limb y of every polynomial uses modulus
- * index limb_offset + y.  In place. */
+ * index limb_offset + y.  In place.  The LAZY transforms carry the reference's words for any 64-bit input (mod-2^64
+ * wraps included).  The STRICT transforms return the reference's canonical words for inputs below 4q (forward) /
+ * 2q (inverse), the ranges every transform of the reference and of this library produces. */
 int gsb_ntt_forward_dev(gsb_ctx *ctx, uint64_t *data, size_t n_polys, size_t n_limbs, size_t limb_offset, int mode, void *stream);
 int gsb_ntt_inverse_dev(gsb_ctx *ctx, uint64_t *data, size_t n_polys, size_t n_limbs, size_t limb_offset, int mode, void *stream);
 int gsb_ntt_forward_host(gsb_ctx *ctx, uint64_t *data, size_t n_polys, size_t n_limbs, size_t limb_offset, int mode);
