@@ -3,6 +3,7 @@
 // tensor product (evaluator.cpp:447-527) and the NTT-form Galois gather (util/galois.cpp:188-214).
 // All are pure HBM streams: 128-bit accesses, one pass, grid sized to the data.
 #pragma once
+#include "ntt_kernels.cuh"
 #include "modarith.cuh"
 
 namespace gsb
@@ -53,7 +54,7 @@ namespace gsb
     inline unsigned grid_for(size_t items, unsigned block)
     {
         size_t g = (items + block - 1) / block;
-        const size_t cap = 148u * 16u;
+        const size_t cap = sm_count() * 16u; // grid-stride kernels: 16 CTAs of 256 threads per SM
         return static_cast<unsigned>(g < 1 ? 1 : g > cap ? cap : g);
     }
 

@@ -229,10 +229,30 @@ namespace gsb
         static constexpr int T1 = LOGN - 3; // single-pass T_LOG
     };
 
-    // polynomials per CTA: enough CTAs left for ~8 waves of 148 SMs x 3 resident CTAs
+    // SMs of the current device (the launching thread's current device is the context's: every entry point sets it)
+    inline size_t sm_count()
+    {
+#ifdef GSB_CUSIM
+        return 148;
+#else
+        static thread_local int cached_dev = -1;
+        static thread_local int cached_sms = 148;
+        int dev = 0;
+        if (cudaGetDevice(&dev) == cudaSuccess && dev != cached_dev)
+        {
+            int n = 0;
+            if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && n > 0)
+                cached_sms = n;
+            cached_dev = dev;
+        }
+        return static_cast<size_t>(cached_sms);
+#endif
+    }
+
+    // polynomials per CTA: enough CTAs left for ~8 waves of (SMs x 3 resident CTAs)
     inline int pick_zb(size_t ctas_per_z, int nz)
     {
-        const size_t want = size_t(148) * 3 * 8;
+        const size_t want = sm_count() * 3 * 8;
         size_t zb = (ctas_per_z * static_cast<size_t>(nz)) / want;
         zb = zb < 1 ? 1 : zb > 8 ? 8 : zb;
         return static_cast<int>(zb);
