@@ -157,6 +157,68 @@ def test_full_size_properties(cudalib):
     ctx.close()
 
 
+def test_full_size_chunked_batch(cudalib, oracle):
+    """A batch larger than one 16 GiB scratch chunk (70 ciphertext pairs at N = 2^15, K = 16 -> two balanced chunks of
+    35): elements on both sides of the chunk boundary equal the same ciphertexts run alone, and the first and last
+    equal the oracle.  Also the rotation path (its own chunking) and a batch that does not divide evenly."""
+    import torch
+    import gemini_seal_b200 as g
+    import synth
+    mods = golden_cases.BFV_DEFAULT[32768]
+    N, L, B = 32768, 15, 70
+    ctx = g.Context(N, mods, 1, lib=cudalib)
+    ev = g.Evaluator(ctx)
+    relin, gal = synth.key_numpy(11, mods, 15, N), synth.key_numpy(12, mods, 15, N)
+    ctx.set_relin_keys(relin)
+    elt = ctx.galois_elt_from_step(1)
+    ctx.set_galois_key(elt, gal)
+    a = synth.residues_torch(torch, 21, 0, B, 2, mods[:L], N)
+    b = synth.residues_torch(torch, 22, 0, B, 2, mods[:L], N)
+    out = ev.mul_relin_rescale(a, b)
+    rot = ev.apply_galois(a, elt)
+    torch.cuda.synchronize()
+    for i in (0, 34, 35, 69):
+        assert torch.equal(ev.mul_relin_rescale(a[i:i + 1].contiguous(), b[i:i + 1].contiguous())[0], out[i]), i
+        assert torch.equal(ev.apply_galois(a[i:i + 1].contiguous(), elt)[0], rot[i]), i
+    oc = oracle.context(15, mods, 1)
+    for i in (0, 69):
+        ai, bi = a[i].cpu().numpy().view(np.uint64), b[i].cpu().numpy().view(np.uint64)
+        assert np.array_equal(out[i].cpu().numpy().view(np.uint64), oc.mul_relin_rescale(ai, bi, relin)), i
+        assert np.array_equal(rot[i].cpu().numpy().view(np.uint64), oc.apply_galois(ai, elt, gal)), i
+    ctx.close()
+
+
+@pytest.mark.parametrize("logn,n_limbs", [(12, 48), (13, 30)])
+def test_many_limbs_literal_path(cudalib, oracle, logn, n_limbs):
+    """Maximum-size modulus chains: 48 (single-pass N) and 30 (two-pass N) ciphertext limbs of 59-bit primes plus one
+    special prime -- beta = 48 / 30 bundles, the literal butterflies (59-bit moduli fail the wide-range bound), every
+    evaluator operation against the oracle at the first level and at a ragged lower level."""
+    import gemini_seal_b200 as g
+    N = 1 << logn
+    mods = ntt_primes(logn, 59, n_limbs + 1)
+    ctx = g.Context(N, mods, 1, lib=cudalib)
+    assert cudalib.gsb_ctx_fast_ntt(ctx.handle) == 0
+    oc = oracle.context(logn, mods, 1)
+    rng = np.random.default_rng(logn * 7 + n_limbs)
+    relin, gal = rand_key(rng, mods, n_limbs, N), rand_key(rng, mods, n_limbs, N)
+    ctx.set_relin_keys(relin)
+    elt = ctx.galois_elt_from_step(-1)
+    ctx.set_galois_key(elt, gal)
+    ev = g.Evaluator(ctx)
+    for L in (n_limbs, n_limbs - 3):
+        a, b = rand_poly(rng, mods[:L], (2, 2), N), rand_poly(rng, mods[:L], (2, 2), N)
+        c3 = ev.multiply(a, b)
+        c2, rs, rot, mrr = ev.relinearize(c3), ev.rescale_to_next(c3), ev.apply_galois(a, elt), ev.mul_relin_rescale(a, b)
+        for i in range(2):
+            w3 = oc.multiply(a[i], b[i])
+            assert np.array_equal(c3[i], w3)
+            assert np.array_equal(c2[i], oc.relinearize(w3, relin)), ("relinearize", L)
+            assert np.array_equal(rs[i], oc.rescale(w3)), ("rescale", L)
+            assert np.array_equal(rot[i], oc.apply_galois(a[i], elt, gal)), ("rotate", L)
+            assert np.array_equal(mrr[i], oc.mul_relin_rescale(a[i], b[i], relin)), ("mrr", L)
+    ctx.close()
+
+
 def test_full_size_shortcuts_equal_literal(cudalib):
     """N = 2^15, K = 16: the context with every congruent-word shortcut (wide-range butterflies, skipped
     range reductions, single-high-product Barrett, ...) and a GSB_LITERAL=1 context that carries the
