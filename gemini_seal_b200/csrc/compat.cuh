@@ -29,6 +29,20 @@
 #endif
 
 #define GSB_DEV __device__ __forceinline__
+// Pins a per-polynomial base pointer in a register pair, so that the compiler adds the per-thread word offsets to it
+// with LEA / LEA.HI.X on the ALU pipe instead of folding the base's own multiply, or the scaling of the word index,
+// into one IMAD.WIDE per load on the multiplier pipe that bounds the transforms (scripts/sass_pipes.py).  The
+// pointer comes out of the asm without its address space; the assumption gives it back (LDG / STG, not generic LD).
+#ifdef GSB_CUSIM
+#define GSB_PIN_GLOBAL(p) ((void)0)
+#else
+#define GSB_PIN_GLOBAL(p)                   \
+    do                                      \
+    {                                       \
+        asm("" : "+l"(p));                  \
+        __builtin_assume(__isGlobal(p));    \
+    } while (0)
+#endif
 
 // Range checks that only exist in the test-only simulator build (they compile to nothing for nvcc):
 // used to validate the no-wrap bounds of the wide-range butterflies on real inputs.

@@ -272,6 +272,7 @@ namespace gsb
         ks.k = static_cast<uint32_t>(ctx->k);
         ks.E = static_cast<uint32_t>(L + ctx->k);
         ks.beta = static_cast<uint32_t>((L + ctx->k - 1) / ctx->k);
+        ks.beta_magic = ks.beta > 1 ? static_cast<uint32_t>(((uint64_t(1) << 32) + ks.beta - 1) / ks.beta) : 0u;
         ks.N = static_cast<uint32_t>(ctx->N);
         ks.lazy_modup = ctx->lazy_modup && ctx->k == 1;
         ks.lazy_mac = ctx->lazy_mac && ctx->k == 1;
@@ -311,6 +312,7 @@ namespace gsb
         const KsDev ks = make_ksdev(ctx, L);
         const size_t E = ks.E, beta = ks.beta, k = ks.k;
         require(key.d != nullptr && key.bundles >= beta, GSB_E_INVALID_ARG, "kswitch_keys is not valid for encryption parameters");
+        require(B * beta * beta < (uint64_t(1) << 32), GSB_E_RANGE, "key switching: batch chunk too large for KsDev::beta_magic");
         const NttTables tab = ctx->ntt_tables();
         Arena ar(scratch);
         uint64_t *coef = ar.words(B * L * N);

@@ -17,6 +17,7 @@ namespace gsb
         const uint64_t *neg_hat; // [L][k]
         const uint64_t *inv_p;   // [L][2]
         uint32_t L, L0, k, E, beta, N;
+        uint32_t beta_magic; // ceil(2^32 / beta), 0 for beta = 1: z / beta = hi32(z * beta_magic) while z * beta < 2^32 (make_ksdev)
         // Slack in the lazy ranges, used only where a bound fixed at context creation proves that no
         // 64- or 128-bit intermediate can wrap (gsb_ctx::lazy_modup / lazy_mac): every word then stays
         // congruent to the reference's, and since the inner product ends in a canonical Barrett-128 the
@@ -26,6 +27,14 @@ namespace gsb
         //               (compile-time LAZY of ModupCoreT, selected by the host from this flag).
         //   lazy_mac:   the operand's last NTT stage skips reduceBarrettLazy (util/ntt.cpp:250-253).
         uint32_t lazy_modup, lazy_mac;
+        // z = b * beta + j (one multiply on the uniform path instead of a run-time division per polynomial)
+        GSB_DEV void split_z(int z, int &b, int &j) const
+        {
+            b = z_b(z);
+            j = z - b * static_cast<int>(beta);
+        }
+        GSB_DEV int z_b(int z) const { return beta_magic ? static_cast<int>(__umulhi(static_cast<uint32_t>(z), beta_magic)) : z; }
+        GSB_DEV int z_j(int z) const { return z - z_b(z) * static_cast<int>(beta); }
         GSB_DEV int ext_mod(int kap) const { return kap < static_cast<int>(L) ? kap : static_cast<int>(L0) + kap - static_cast<int>(L); }
     };
 
@@ -94,6 +103,7 @@ namespace gsb
             E = ks.E;
             cnt = s1 - s0;
             src = coef + (static_cast<size_t>(b) * ks.L + s0) * N;
+            GSB_PIN_GLOBAL(src);
             a = ks.modup_a + static_cast<size_t>(j) * ks.k * 2;
             bb = ks.modup_b + static_cast<size_t>(j) * ks.k * E + kap;
             limb = ks.limb + s0;
@@ -140,7 +150,8 @@ namespace gsb
         const uint64_t *coef;
         GSB_DEV bool skip(int y, int z) const
         {
-            const int j = z % static_cast<int>(ks.beta);
+            int b, j;
+            ks.split_z(z, b, j);
             const int s0 = j * static_cast<int>(ks.k);
             return y >= s0 && y < s0 + static_cast<int>(ks.k) && y < static_cast<int>(ks.L);
         }
@@ -150,7 +161,7 @@ namespace gsb
     {
         typedef ModupArgs Args;
         GSB_DEV ModupLoadT(const Args &a, int y, int z, int, const LimbC &c, uint32_t)
-            : ModupCoreT<K1, LAZY>(a.ks, a.coef, z / static_cast<int>(a.ks.beta), z % static_cast<int>(a.ks.beta), y, c)
+            : ModupCoreT<K1, LAZY>(a.ks, a.coef, a.ks.z_b(z), a.ks.z_j(z), y, c)
         {}
     };
 
@@ -606,7 +617,10 @@ namespace gsb
     };
 
     // LAZY (see KsDev::lazy_mac): the operand's last stage skips reduceBarrettLazy.
-    template <int LOGN, bool K1, bool LAZY>
+#ifndef GSB_MAC_FWD_FORM
+#define GSB_MAC_FWD_FORM 3 // fwd_round's FAST form for the operand transform: measured 3.22 / 3.34 / 3.47 / 3.56 ms for 3 / 2 / 1 / 4
+#endif
+    template <int LOGN, bool K1, bool LAZY, int FORM = GSB_MAC_FWD_FORM>
     __global__ void __launch_bounds__(1 << MacPlan<LOGN>::T, MacPlan<LOGN>::T <= 8 ? 2 : 1) ks_mac_kernel(KsMacArgs p, NttTables tab)
     {
         typedef MacPlan<LOGN> MP;
@@ -728,7 +742,7 @@ namespace gsb
             if (!direct)
             {
                 if constexpr (LAZY)
-                    fwd_compute<T, MP::G_HI, 0, false, 0, true>(x, smem, tid, TwPreshifted<typename TP::TwC>{ tw }, c, parity);
+                    fwd_compute<T, MP::G_HI, 0, false, 0, FORM>(x, smem, tid, TwPreshifted<typename TP::TwC>{ tw }, c, parity);
                 else
                     fwd_compute<T, MP::G_HI, 0, true, 0, false>(x, smem, tid, tw, c, parity);
             }

@@ -118,9 +118,14 @@ namespace gsb
     // x*y - 2q*h lies in [0, 5q): congruent to the reference's mulmodLazy word, in a wider range.
     // 5 wide multiplies + 4 IMAD (the exact form is 6 + 4 and four more carry adds).  In SASS (sm_100a,
     // CUDA 12.9) ptxas issues the wide products without addends (IMAD.WIDE / IMAD.HI) and joins them with
-    // three-input IADD3 pairs on the ALU pipe.  `zero` is a run-time zero (LimbC::pad) used as the high
-    // word of the third product's addend: with a literal 0 there the carry word became an IMAD.X on the
-    // multiplier pipe, with a register operand it stays an IADD3.X.
+    // three-input IADD3 pairs on the ALU pipe.  `zero` is a run-time zero (LimbC::pad): the sum
+    // x1*ysh1 + (t >> 32) is written as 32-bit carry chains with both halves of `zero` as third inputs, because
+    // ptxas turns the carry word of every TWO-input 64-bit add into an IMAD.X on the multiplier pipe (the pipe
+    // that bounds these kernels; scripts/sass_pipes.py counts them) and can only use IADD3.X for a three-input one.
+    // H3 = true: the three-input form above.  H3 = false: the high word of the third product's addend is `zero`'s low
+    // half only (mad.wide with a 64-bit addend in PTX), which leaves ptxas free to put that carry on either pipe --
+    // for kernels whose ALU pipe is the fuller one (ks_mac, see DESIGN.md "two-pipe model").
+    template <bool H3 = true>
     GSB_DEV uint64_t mulmod_wide_add(uint64_t x, uint64_t y, uint64_t ysh, uint64_t neg_two_q, uint64_t add, uint64_t zero)
     {
 #ifdef GSB_CUSIM
@@ -131,31 +136,88 @@ namespace gsb
         return x * y + h * neg_two_q + add;
 #else
         uint64_t r;
+        if constexpr (H3)
+        {
+            asm("{\n\t"
+                ".reg .u32 x0, x1, y0, y1, s0, s1, h0, h1, n0, n1, lo, hi, z, z1;\n\t"
+                ".reg .u64 t;\n\t"
+                "mov.b64 {x0, x1}, %1;\n\t"
+                "mov.b64 {y0, y1}, %2;\n\t"
+                "mov.b64 {s0, s1}, %3;\n\t"
+                "mov.b64 {n0, n1}, %4;\n\t"
+                "mul.wide.u32 t, x0, s1;\n\t"
+                "mad.wide.u32 t, x1, s0, t;\n\t"
+                "mov.b64 {lo, hi}, t;\n\t"
+                "mov.b64 {z, z1}, %6;\n\t"
+                "mul.wide.u32 t, x1, s1;\n\t"
+                "mov.b64 {h0, h1}, t;\n\t"
+                "add.cc.u32 h0, h0, hi;\n\t"
+                "addc.u32 h1, h1, z;\n\t"
+                "add.cc.u32 h0, h0, z1;\n\t"
+                "addc.u32 h1, h1, z1;\n\t"
+                "mad.wide.u32 t, x0, y0, %5;\n\t"
+                "mad.wide.u32 t, h0, n0, t;\n\t"
+                "mov.b64 {lo, hi}, t;\n\t"
+                "mad.lo.u32 hi, x0, y1, hi;\n\t"
+                "mad.lo.u32 hi, x1, y0, hi;\n\t"
+                "mad.lo.u32 hi, h0, n1, hi;\n\t"
+                "mad.lo.u32 hi, h1, n0, hi;\n\t"
+                "mov.b64 %0, {lo, hi};\n\t"
+                "}"
+                : "=l"(r)
+                : "l"(x), "l"(y), "l"(ysh), "l"(neg_two_q), "l"(add), "l"(zero));
+        }
+        else
+        {
+            asm("{\n\t"
+                ".reg .u32 x0, x1, y0, y1, s0, s1, h0, h1, n0, n1, lo, hi, z, z1;\n\t"
+                ".reg .u64 t, c;\n\t"
+                "mov.b64 {x0, x1}, %1;\n\t"
+                "mov.b64 {y0, y1}, %2;\n\t"
+                "mov.b64 {s0, s1}, %3;\n\t"
+                "mov.b64 {n0, n1}, %4;\n\t"
+                "mul.wide.u32 t, x0, s1;\n\t"
+                "mad.wide.u32 t, x1, s0, t;\n\t"
+                "mov.b64 {lo, hi}, t;\n\t"
+                "mov.b64 {z, z1}, %6;\n\t"
+                "mov.b64 c, {hi, z};\n\t"
+                "mad.wide.u32 t, x1, s1, c;\n\t"
+                "mov.b64 {h0, h1}, t;\n\t"
+                "mad.wide.u32 t, x0, y0, %5;\n\t"
+                "mad.wide.u32 t, h0, n0, t;\n\t"
+                "mov.b64 {lo, hi}, t;\n\t"
+                "mad.lo.u32 hi, x0, y1, hi;\n\t"
+                "mad.lo.u32 hi, x1, y0, hi;\n\t"
+                "mad.lo.u32 hi, h0, n1, hi;\n\t"
+                "mad.lo.u32 hi, h1, n0, hi;\n\t"
+                "mov.b64 %0, {lo, hi};\n\t"
+                "}"
+                : "=l"(r)
+                : "l"(x), "l"(y), "l"(ysh), "l"(neg_two_q), "l"(add), "l"(zero));
+        }
+        return r;
+#endif
+    }
+
+    // (u + u + k) - s (mod 2^64) as two three-input 64-bit sums (u, u, k) and (., -s, zero): IADD3 / IADD3.X pairs
+    // on the ALU pipe, in this association (NVVM otherwise regroups the C++ expression into two-input sums whose
+    // carry words become IMAD.X).  `zero` is a run-time zero.
+    GSB_DEV uint64_t twice_plus_minus(uint64_t u, uint64_t k, uint64_t s, uint64_t zero)
+    {
+#ifdef GSB_CUSIM
+        GSB_SIM_ASSERT(zero == 0);
+        return u + u + k - s;
+#else
+        uint64_t r;
         asm("{\n\t"
-            ".reg .u32 x0, x1, y0, y1, s0, s1, h0, h1, n0, n1, lo, hi, z, z1;\n\t"
-            ".reg .u64 t, c;\n\t"
-            "mov.b64 {x0, x1}, %1;\n\t"
-            "mov.b64 {y0, y1}, %2;\n\t"
-            "mov.b64 {s0, s1}, %3;\n\t"
-            "mov.b64 {n0, n1}, %4;\n\t"
-            "mul.wide.u32 t, x0, s1;\n\t"
-            "mad.wide.u32 t, x1, s0, t;\n\t"
-            "mov.b64 {lo, hi}, t;\n\t"
-            "mov.b64 {z, z1}, %6;\n\t"
-            "mov.b64 c, {hi, z};\n\t"
-            "mad.wide.u32 t, x1, s1, c;\n\t"
-            "mov.b64 {h0, h1}, t;\n\t"
-            "mad.wide.u32 t, x0, y0, %5;\n\t"
-            "mad.wide.u32 t, h0, n0, t;\n\t"
-            "mov.b64 {lo, hi}, t;\n\t"
-            "mad.lo.u32 hi, x0, y1, hi;\n\t"
-            "mad.lo.u32 hi, x1, y0, hi;\n\t"
-            "mad.lo.u32 hi, h0, n1, hi;\n\t"
-            "mad.lo.u32 hi, h1, n0, hi;\n\t"
-            "mov.b64 %0, {lo, hi};\n\t"
+            ".reg .u64 t;\n\t"
+            "add.u64 t, %1, %1;\n\t"
+            "add.u64 t, t, %2;\n\t"
+            "sub.u64 t, t, %3;\n\t"
+            "add.u64 %0, t, %4;\n\t"
             "}"
             : "=l"(r)
-            : "l"(x), "l"(y), "l"(ysh), "l"(neg_two_q), "l"(add), "l"(zero));
+            : "l"(u), "l"(k), "l"(s), "l"(zero));
         return r;
 #endif
     }

@@ -272,7 +272,11 @@ namespace gsb
     // < in + 5qs.  The global last stage (LAST, g = 0) stays the literal ForwardLazyLast, whose
     // reduceBarrettLazy / exact Shoup product accept any 64-bit word: its outputs are again in
     // [0,4q), the range every epilogue of the reference expects.
-    template <int TOP, int R, int T_LOG, bool LAST, bool FAST, class TW>
+    // FAST is an int: 0 = literal; 1 = wide-range with every 64-bit sum three-input (all carries on the ALU pipe);
+    // 2 = wide-range, sums left to the compiler (some carries become IMAD.X on the multiplier pipe); 3 = three-input
+    // difference only; 4 = three-input quotient carry only.  Which one is fastest depends on which of the two pipes
+    // the rest of the kernel loads more ("two-pipe model"; scripts/sass_pipes.py).
+    template <int TOP, int R, int T_LOG, bool LAST, int FAST, class TW>
     GSB_DEV void fwd_round(uint64_t (&x)[8], uint32_t tid, const TW &tw, const LimbC &c)
     {
         const uint64_t five_q = c.two_q + c.two_q + c.q, neg_two_q = 0 - c.two_q;
@@ -304,15 +308,18 @@ namespace gsb
                         // instead of IMAD.X on the FMA-heavy pipe that bounds these kernels)
                         if (wide)
                         {
-                            const uint64_t s = mulmod_wide_add(x[b], w.x, wsh, neg_two_q, u, c.pad);
-                            x[b] = (u + u + five_q) + (c.pad - s);
+                            const uint64_t s = mulmod_wide_add<(FAST == 1 || FAST == 4)>(x[b], w.x, wsh, neg_two_q, u, c.pad);
+                            if constexpr (FAST == 1 || FAST == 3)
+                                x[b] = twice_plus_minus(u, five_q, s, c.pad);
+                            else
+                                x[b] = (u + u + five_q) + (c.pad - s);
                             x[a] = s;
                             GSB_SIM_ASSERT((x[a] >> 63) == 0 && (x[b] >> 63) == 0);
                         }
                         else
                         {
                             const uint64_t s = mulmod_lazy_add(x[b], w.x, w.y, c.q, u);
-                            x[b] = (u + u + c.two_q) + (c.pad - s);
+                            x[b] = twice_plus_minus(u, c.two_q, s, c.pad);
                             x[a] = s;
                         }
                     }
@@ -552,7 +559,7 @@ namespace gsb
     }
 
     // All rounds of a forward transform; x enters in the first round's layout, leaves in the last's.
-    template <int T_LOG, int G_HI, int G_LO, bool LAST, int IDX, bool FAST = false, class TW>
+    template <int T_LOG, int G_HI, int G_LO, bool LAST, int IDX, int FAST = 0, class TW>
     GSB_DEV void fwd_compute(uint64_t (&x)[8], uint64_t *smem, uint32_t tid, const TW &tw, const LimbC &c, int &parity)
     {
         constexpr int NS = G_HI - G_LO + 1;

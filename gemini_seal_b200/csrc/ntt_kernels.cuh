@@ -45,8 +45,10 @@ namespace gsb
     {
         const uint64_t *p;
         GSB_DEV PlainPro(const uint64_t *base, size_t zs, int y, int z, uint32_t N)
-            : p(base + static_cast<size_t>(z) * zs + static_cast<size_t>(y) * N)
-        {}
+        {
+            p = base + static_cast<size_t>(z) * zs + static_cast<size_t>(y) * N;
+            GSB_PIN_GLOBAL(p);
+        }
         // raw / raw2: the memory loads only; xform: the prologue arithmetic on a loaded word
         GSB_DEV uint64_t raw(uint32_t d) const { return p[d]; }
         GSB_DEV void raw2(uint32_t d, uint64_t &a, uint64_t &b) const
@@ -64,8 +66,11 @@ namespace gsb
         uint64_t *p;
         const LimbC &c;
         GSB_DEV PlainEpi(uint64_t *base, size_t zs, int y, int z, const LimbC &c_, uint32_t N)
-            : p(base + static_cast<size_t>(z) * zs + static_cast<size_t>(y) * N), c(c_)
-        {}
+            : c(c_)
+        {
+            p = base + static_cast<size_t>(z) * zs + static_cast<size_t>(y) * N;
+            GSB_PIN_GLOBAL(p);
+        }
         GSB_DEV void store(uint32_t d, uint64_t v, int) const { p[d] = finish<MODE>(v, c); }
         GSB_DEV void store2(uint32_t d, uint64_t a, uint64_t b, int) const
         {
@@ -115,6 +120,9 @@ namespace gsb
     };
 
     // FAST: wide-range butterflies, see fwd_round / inv_round.
+#ifndef GSB_TILE_FWD_FORM
+#define GSB_TILE_FWD_FORM 3 // which sums of the wide-range forward butterfly are forced onto the ALU pipe (fwd_round)
+#endif
     template <bool INVERSE, int T_LOG, int G_HI, int G_LO, bool LAST, int A, class IO, bool FAST = false>
     __global__ void __launch_bounds__(1 << T_LOG, T_LOG <= 8 ? GSB_TILE_MIN_CTAS : 1) ntt_tile_kernel(IO io, NttTables tab, ModMap mm, int nz, int zb)
     {
@@ -177,7 +185,7 @@ namespace gsb
                 if constexpr (INVERSE)
                     inv_compute<T_LOG, G_HI, G_LO, LAST, 0, FAST>(x, smem, tid, tw, c, parity);
                 else if constexpr (FAST)
-                    fwd_compute<T_LOG, G_HI, G_LO, LAST, 0, true>(x, smem, tid, TwPreshifted<std::decay_t<decltype(tw)>>{ tw }, c, parity);
+                    fwd_compute<T_LOG, G_HI, G_LO, LAST, 0, GSB_TILE_FWD_FORM>(x, smem, tid, TwPreshifted<std::decay_t<decltype(tw)>>{ tw }, c, parity);
                 else
                     fwd_compute<T_LOG, G_HI, G_LO, LAST, 0, false>(x, smem, tid, tw, c, parity);
                 xf_store<T_LOG, G_HI, G_LO, INVERSE>(x, tid, tile, map, epi);

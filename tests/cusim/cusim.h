@@ -164,6 +164,10 @@ namespace cusim
 #define gridDim (::cusim::S().grid)
 #define __syncthreads() ::cusim::syncthreads()
 
+static inline unsigned int __umulhi(unsigned int a, unsigned int b)
+{
+    return static_cast<unsigned int>((static_cast<unsigned long long>(a) * b) >> 32);
+}
 static inline unsigned long long __umul64hi(unsigned long long a, unsigned long long b)
 {
     return (unsigned long long)(((unsigned __int128)a * b) >> 64);
