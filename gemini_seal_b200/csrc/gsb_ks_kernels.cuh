@@ -618,7 +618,7 @@ namespace gsb
 
     // LAZY (see KsDev::lazy_mac): the operand's last stage skips reduceBarrettLazy.
 #ifndef GSB_MAC_FWD_FORM
-#define GSB_MAC_FWD_FORM 3 // fwd_round's FAST form for the operand transform: measured 3.22 / 3.34 / 3.47 / 3.56 ms for 3 / 2 / 1 / 4
+#define GSB_MAC_FWD_FORM 3 // fwd_round's FAST form for the operand transform: measured 3.22 ms for D3 (3), 3.34 plain (1), 3.47 H3 + D3 (4), 3.56 H3 (2), 3.32 D3 + EARLY (7)
 #endif
     template <int LOGN, bool K1, bool LAZY, int FORM = GSB_MAC_FWD_FORM>
     __global__ void __launch_bounds__(1 << MacPlan<LOGN>::T, MacPlan<LOGN>::T <= 8 ? 2 : 1) ks_mac_kernel(KsMacArgs p, NttTables tab)

@@ -125,7 +125,10 @@ namespace gsb
     // H3 = true: the three-input form above.  H3 = false: the high word of the third product's addend is `zero`'s low
     // half only (mad.wide with a 64-bit addend in PTX), which leaves ptxas free to put that carry on either pipe --
     // for kernels whose ALU pipe is the fuller one (ks_mac, see DESIGN.md "two-pipe model").
-    template <bool H3 = true>
+    // EARLY: the two narrow products that do not depend on h (x0*y1, x1*y0) go into the high word of the addend BEFORE
+    // the wide chain, so only two narrow multiplies stay on the critical path behind h (same instruction counts; faster
+    // in the tile kernels, slower in ks_mac, whose register budget is tighter).
+    template <bool H3 = true, bool EARLY = true>
     GSB_DEV uint64_t mulmod_wide_add(uint64_t x, uint64_t y, uint64_t ysh, uint64_t neg_two_q, uint64_t add, uint64_t zero)
     {
 #ifdef GSB_CUSIM
@@ -136,11 +139,44 @@ namespace gsb
         return x * y + h * neg_two_q + add;
 #else
         uint64_t r;
-        if constexpr (H3)
+        if constexpr (H3 && EARLY)
         {
             asm("{\n\t"
-                ".reg .u32 x0, x1, y0, y1, s0, s1, h0, h1, n0, n1, lo, hi, z, z1;\n\t"
-                ".reg .u64 t;\n\t"
+                ".reg .u32 x0, x1, y0, y1, s0, s1, h0, h1, n0, n1, lo, hi, z, z1, a0, a1;\n\t"
+                ".reg .u64 t, c;\n\t"
+                "mov.b64 {x0, x1}, %1;\n\t"
+                "mov.b64 {y0, y1}, %2;\n\t"
+                "mov.b64 {s0, s1}, %3;\n\t"
+                "mov.b64 {n0, n1}, %4;\n\t"
+                "mul.wide.u32 t, x0, s1;\n\t"
+                "mad.wide.u32 t, x1, s0, t;\n\t"
+                "mov.b64 {lo, hi}, t;\n\t"
+                "mov.b64 {z, z1}, %6;\n\t"
+                "mul.wide.u32 t, x1, s1;\n\t"
+                "mov.b64 {h0, h1}, t;\n\t"
+                "add.cc.u32 h0, h0, hi;\n\t"
+                "addc.u32 h1, h1, z;\n\t"
+                "add.cc.u32 h0, h0, z1;\n\t"
+                "addc.u32 h1, h1, z1;\n\t"
+                "mov.b64 {a0, a1}, %5;\n\t"
+                "mad.lo.u32 a1, x0, y1, a1;\n\t"
+                "mad.lo.u32 a1, x1, y0, a1;\n\t"
+                "mov.b64 c, {a0, a1};\n\t"
+                "mad.wide.u32 t, x0, y0, c;\n\t"
+                "mad.wide.u32 t, h0, n0, t;\n\t"
+                "mov.b64 {lo, hi}, t;\n\t"
+                "mad.lo.u32 hi, h0, n1, hi;\n\t"
+                "mad.lo.u32 hi, h1, n0, hi;\n\t"
+                "mov.b64 %0, {lo, hi};\n\t"
+                "}"
+                : "=l"(r)
+                : "l"(x), "l"(y), "l"(ysh), "l"(neg_two_q), "l"(add), "l"(zero));
+        }
+        else if constexpr (H3)
+        {
+            asm("{\n\t"
+                ".reg .u32 x0, x1, y0, y1, s0, s1, h0, h1, n0, n1, lo, hi, z, z1, a0, a1;\n\t"
+                ".reg .u64 t, c;\n\t"
                 "mov.b64 {x0, x1}, %1;\n\t"
                 "mov.b64 {y0, y1}, %2;\n\t"
                 "mov.b64 {s0, s1}, %3;\n\t"
@@ -167,10 +203,40 @@ namespace gsb
                 : "=l"(r)
                 : "l"(x), "l"(y), "l"(ysh), "l"(neg_two_q), "l"(add), "l"(zero));
         }
+        else if constexpr (EARLY)
+        {
+            asm("{\n\t"
+                ".reg .u32 x0, x1, y0, y1, s0, s1, h0, h1, n0, n1, lo, hi, z, z1, a0, a1;\n\t"
+                ".reg .u64 t, c;\n\t"
+                "mov.b64 {x0, x1}, %1;\n\t"
+                "mov.b64 {y0, y1}, %2;\n\t"
+                "mov.b64 {s0, s1}, %3;\n\t"
+                "mov.b64 {n0, n1}, %4;\n\t"
+                "mul.wide.u32 t, x0, s1;\n\t"
+                "mad.wide.u32 t, x1, s0, t;\n\t"
+                "mov.b64 {lo, hi}, t;\n\t"
+                "mov.b64 {z, z1}, %6;\n\t"
+                "mov.b64 c, {hi, z};\n\t"
+                "mad.wide.u32 t, x1, s1, c;\n\t"
+                "mov.b64 {h0, h1}, t;\n\t"
+                "mov.b64 {a0, a1}, %5;\n\t"
+                "mad.lo.u32 a1, x0, y1, a1;\n\t"
+                "mad.lo.u32 a1, x1, y0, a1;\n\t"
+                "mov.b64 c, {a0, a1};\n\t"
+                "mad.wide.u32 t, x0, y0, c;\n\t"
+                "mad.wide.u32 t, h0, n0, t;\n\t"
+                "mov.b64 {lo, hi}, t;\n\t"
+                "mad.lo.u32 hi, h0, n1, hi;\n\t"
+                "mad.lo.u32 hi, h1, n0, hi;\n\t"
+                "mov.b64 %0, {lo, hi};\n\t"
+                "}"
+                : "=l"(r)
+                : "l"(x), "l"(y), "l"(ysh), "l"(neg_two_q), "l"(add), "l"(zero));
+        }
         else
         {
             asm("{\n\t"
-                ".reg .u32 x0, x1, y0, y1, s0, s1, h0, h1, n0, n1, lo, hi, z, z1;\n\t"
+                ".reg .u32 x0, x1, y0, y1, s0, s1, h0, h1, n0, n1, lo, hi, z, z1, a0, a1;\n\t"
                 ".reg .u64 t, c;\n\t"
                 "mov.b64 {x0, x1}, %1;\n\t"
                 "mov.b64 {y0, y1}, %2;\n\t"

@@ -272,10 +272,14 @@ namespace gsb
     // < in + 5qs.  The global last stage (LAST, g = 0) stays the literal ForwardLazyLast, whose
     // reduceBarrettLazy / exact Shoup product accept any 64-bit word: its outputs are again in
     // [0,4q), the range every epilogue of the reference expects.
-    // FAST is an int: 0 = literal; 1 = wide-range with every 64-bit sum three-input (all carries on the ALU pipe);
-    // 2 = wide-range, sums left to the compiler (some carries become IMAD.X on the multiplier pipe); 3 = three-input
-    // difference only; 4 = three-input quotient carry only.  Which one is fastest depends on which of the two pipes
-    // the rest of the kernel loads more ("two-pipe model"; scripts/sass_pipes.py).
+    // FAST is an int: 0 = literal; otherwise 1 + a bit mask of how the wide-range butterfly is written:
+    //   1 (H3)    the quotient's carry word as a three-input sum (mulmod_wide_add): that carry on the ALU pipe;
+    //   2 (D3)    the difference as two three-input sums (twice_plus_minus) instead of the C++ expression, which NVVM
+    //             regroups into two-input sums whose carry words ptxas may turn into IMAD.X on the multiplier pipe;
+    //   4 (EARLY) the h-independent narrow products ahead of the wide chain (mulmod_wide_add).
+    // `true` (= 1) is the plain form.  Which one is fastest depends on which of the two pipes the rest of the kernel
+    // loads more and on its register budget ("two-pipe model"; scripts/sass_pipes.py): the tile
+    // kernels use D3 + EARLY (7), ks_mac D3 (3).
     template <int TOP, int R, int T_LOG, bool LAST, int FAST, class TW>
     GSB_DEV void fwd_round(uint64_t (&x)[8], uint32_t tid, const TW &tw, const LimbC &c)
     {
@@ -308,8 +312,8 @@ namespace gsb
                         // instead of IMAD.X on the FMA-heavy pipe that bounds these kernels)
                         if (wide)
                         {
-                            const uint64_t s = mulmod_wide_add<(FAST == 1 || FAST == 4)>(x[b], w.x, wsh, neg_two_q, u, c.pad);
-                            if constexpr (FAST == 1 || FAST == 3)
+                            const uint64_t s = mulmod_wide_add<(((FAST - 1) & 1) != 0), (((FAST - 1) & 4) != 0)>(x[b], w.x, wsh, neg_two_q, u, c.pad);
+                            if constexpr (((FAST - 1) & 2) != 0)
                                 x[b] = twice_plus_minus(u, five_q, s, c.pad);
                             else
                                 x[b] = (u + u + five_q) + (c.pad - s);

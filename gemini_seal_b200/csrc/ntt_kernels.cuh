@@ -121,7 +121,7 @@ namespace gsb
 
     // FAST: wide-range butterflies, see fwd_round / inv_round.
 #ifndef GSB_TILE_FWD_FORM
-#define GSB_TILE_FWD_FORM 3 // which sums of the wide-range forward butterfly are forced onto the ALU pipe (fwd_round)
+#define GSB_TILE_FWD_FORM 7 // which sums of the wide-range forward butterfly are forced onto the ALU pipe (fwd_round)
 #endif
     template <bool INVERSE, int T_LOG, int G_HI, int G_LO, bool LAST, int A, class IO, bool FAST = false>
     __global__ void __launch_bounds__(1 << T_LOG, T_LOG <= 8 ? GSB_TILE_MIN_CTAS : 1) ntt_tile_kernel(IO io, NttTables tab, ModMap mm, int nz, int zb)

@@ -76,7 +76,7 @@ namespace
         for (int i = 0; i < 8; i++)
             x[i] = threadIdx.x * 8 + i;
         for (int it = 0; it < iters; it++)
-            fwd_round<2, 3, 8, false, FAST>(x, threadIdx.x, tw, c); // 12 butterflies
+            fwd_round<2, 3, 8, false, (FAST ? 7 : 0)>(x, threadIdx.x, tw, c); // 12 butterflies; 7 = the tile kernels' form (GSB_TILE_FWD_FORM)
         uint64_t acc = 0;
 #pragma unroll
         for (int i = 0; i < 8; i++)
