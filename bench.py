@@ -429,6 +429,37 @@ def int_roofline(w, lib, ctx, kernels, B, peaks):
     return roof
 
 
+def two_pipe_bound(w, roof, B, clocks):
+    """The dominant kernel against the two-pipe model of DESIGN.md section 6: scripts/sass_pipes.py counts, from the SASS
+    of the library that just ran, the cycles one iteration of the kernel's hot loop keeps the multiplier (FMA-heavy) pipe
+    and the ALU pipe busy per SM sub-partition (IMAD.WIDE / IMAD.HI 4 + 2, other IMAD 2 + 0, ALU instructions 0 + 2, measured
+    by scripts/exp/pipes.cu); the larger of the two is the floor of an iteration.  frac = that floor over the measured
+    cycles per iteration (launch time x SM clock under load / iterations per sub-partition)."""
+    try:
+        if roof.get("kernel") != "ks_mac" or w.k != 1 or not clocks or not clocks.get("sm_mhz"):
+            return None
+        sys.path.insert(0, os.path.join(ROOT, "scripts"))
+        import sass_pipes
+        from gemini_seal_b200 import _lib
+        hot = sass_pipes.hot_loop(_lib.LIB_PATH, ["ks_mac_kernelILi%dELb1ELb1" % w.logn])
+        if hot is None:
+            return None
+        import torch
+        sms = torch.cuda.get_device_properties(0).multi_processor_count
+        ctas = B * (w.N // 2048) * w.E
+        # iterations of the bundle loop per SM sub-partition; for L of the E slots one of the beta iterations has no
+        # transform (the bundle that contains the slot): counted as 0.3 of an iteration (its 16 multiply-accumulates)
+        warp_iters = ctas * 8 * (w.beta - 0.7 * w.L / w.E) / (sms * 4.0)
+        measured = roof["launch_ms"] * 1e-3 * clocks["sm_mhz"] * 1e6 / warp_iters
+        floor = max(hot["fma_cycles"], hot["alu_cycles"])
+        return {"kernel_loop": "ks_mac bundle loop (one operand tile transform + 16 multiply-accumulates per thread)",
+                "instructions_per_iteration": hot["instr"], "fma_pipe_cycles": hot["fma_cycles"], "alu_pipe_cycles": hot["alu_cycles"],
+                "floor_cycles": floor, "measured_cycles": measured, "frac": floor / measured, "sm_mhz": clocks["sm_mhz"],
+                "what": "static pipe occupancy of the loop body (scripts/sass_pipes.py on the loaded library) over measured cycles per iteration per SM sub-partition"}
+    except Exception as e:  # the number is an explanation, never a reason to lose the bench line
+        return {"error": repr(e)}
+
+
 def run_c3(torch, g, lib, np, timed, world_rank_local, peaks, batch=256):
     """BASELINE config #3 as a measured line (1 GPU): device-resident mul+relin+rescale ops/s at N = 16384, with its own
     parity gate, kernel table and rooflines."""
@@ -729,6 +760,7 @@ def run_ours(args):
             "what": "SURVEY 8(d) butterflies of the reference algorithm (302 limb-NTTs per op at C4) per second over the whole step, "
                     "against the register-resident wide-range butterfly loop"}
         extra["int_peaks"] = {k: v for k, v in peaks.items()}
+        roofline["two_pipe"] = two_pipe_bound(w, roofline, B, clocks)
 
     # ---- CPU baseline on this box's host cores (rank 0, N = 1 only)
     cpu = None

@@ -378,7 +378,7 @@ namespace gsb
                             {
                                 t -= (t >= five_q) ? five_q : 0;
                                 x[a] = t;
-                                x[b] = mulmod_wide_add(u - v + five_q, w.x, wsh, neg_two_q, 0, c.pad);
+                                x[b] = mulmod_wide_add<false, false>(u - v + five_q, w.x, wsh, neg_two_q, 0, c.pad); // the inverse rounds are ALU-bound: carries left to ptxas
                             }
                         }
                         else

@@ -26,7 +26,17 @@ def build(force=False):
         return LIB
     subprocess.run([NVCC, "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-shared",
                     "-Xcompiler", "-fPIC", "-o", LIB, SRC], check=True)
+    build_pipes()
     return LIB
+
+
+def build_pipes():
+    """scripts/exp/pipes.cu -> scripts/_C/pipes.bin (the instruction-mix measurement behind DESIGN.md's two-pipe model):
+    `scripts/_C/pipes.bin > profiles/r2_pipes.txt` on the GPU box."""
+    src, out = os.path.join(HERE, "exp", "pipes.cu"), os.path.join(HERE, "_C", "pipes.bin")
+    if os.path.exists(src) and not (os.path.exists(out) and os.path.getmtime(out) >= os.path.getmtime(src)):
+        subprocess.run([NVCC, "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-o", out, src], check=True)
+    return out
 
 
 def load():

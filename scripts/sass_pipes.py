@@ -82,6 +82,34 @@ def tally(instrs):
     return len(instrs), fma, alu, c
 
 
+def loops_of(body):
+    addr = {a: i for i, (a, _) in enumerate(body)}
+    loops = []
+    for i, (a, t) in enumerate(body):
+        m = re.search(r"BRA(?:\.\w+)*\s+(?:!?U?P\w+,\s*)?0x([0-9a-f]+)", t)
+        if m:
+            tgt = int(m.group(1), 16)
+            if tgt < a and tgt in addr and i - addr[tgt] > 40:
+                loops.append((addr[tgt], i))
+    return loops
+
+
+def hot_loop(path, pats, min_wide=100):
+    """The smallest loop of the (first) matching kernel that holds at least `min_wide` wide multiplies:
+    {"kernel", "instr", "fma_cycles", "alu_cycles", "wide"} per iteration, or None."""
+    for name, body in functions(path):
+        if not all(p in name for p in pats):
+            continue
+        best = None
+        for lo, hi in loops_of(body):
+            n, fma, alu, c = tally(body[lo:hi + 1])
+            wide = c["IMAD.WIDE"] + c["IMAD.HI"]
+            if wide >= min_wide and (best is None or n < best["instr"]):
+                best = {"kernel": name, "instr": n, "fma_cycles": fma, "alu_cycles": alu, "wide": wide}
+        return best
+    return None
+
+
 def main():
     path, pats = sys.argv[1], sys.argv[2:]
     for name, body in functions(path):
@@ -90,15 +118,7 @@ def main():
         print(name)
         n, fma, alu, c = tally(body)
         print(f"  whole function: {n} instr, FMA {fma} cyc, ALU' {alu} cyc")
-        addr = {a: i for i, (a, _) in enumerate(body)}
-        loops = []
-        for i, (a, t) in enumerate(body):
-            m = re.search(r"BRA(?:\.\w+)*\s+(?:!?U?P\w+,\s*)?0x([0-9a-f]+)", t)
-            if m:
-                tgt = int(m.group(1), 16)
-                if tgt < a and tgt in addr and i - addr[tgt] > 40:
-                    loops.append((addr[tgt], i))
-        for lo, hi in loops:
+        for lo, hi in loops_of(body):
             n, fma, alu, c = tally(body[lo:hi + 1])
             top = ", ".join(f"{k} {v}" for k, v in c.most_common(14))
             print(f"  loop {body[lo][0]:#x}..{body[hi][0]:#x}: {n} instr (issue {n} cyc), FMA {fma} cyc, ALU' {alu} cyc\n     {top}")
