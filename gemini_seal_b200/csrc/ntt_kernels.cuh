@@ -123,8 +123,20 @@ namespace gsb
 #ifndef GSB_TILE_FWD_FORM
 #define GSB_TILE_FWD_FORM 7 // which sums of the wide-range forward butterfly are forced onto the ALU pipe (fwd_round)
 #endif
+    // Per-IO tuning: resident CTAs per SM the register allocation aims at, and whether polynomial z+1 is loaded into
+    // registers before the butterflies of z (16 more live registers).  Default 2 CTAs + prefetch; an IO type may
+    // specialise it (the mod-up column pass runs 3 CTAs of 80 registers without prefetch: measured 1.76 vs 1.82 ms,
+    // while the same setting costs the contiguous passes 3 %).
+    template <class IO>
+    struct TileTuning
+    {
+        static constexpr int min_ctas = GSB_TILE_MIN_CTAS;
+        static constexpr bool prefetch = GSB_PREFETCH != 0;
+        static constexpr int fwd_form = GSB_TILE_FWD_FORM; // fwd_round's FAST form of the wide-range forward transforms
+    };
+
     template <bool INVERSE, int T_LOG, int G_HI, int G_LO, bool LAST, int A, class IO, bool FAST = false>
-    __global__ void __launch_bounds__(1 << T_LOG, T_LOG <= 8 ? GSB_TILE_MIN_CTAS : 1) ntt_tile_kernel(IO io, NttTables tab, ModMap mm, int nz, int zb)
+    __global__ void __launch_bounds__(1 << T_LOG, T_LOG <= 8 ? TileTuning<IO>::min_ctas : 1) ntt_tile_kernel(IO io, NttTables tab, ModMap mm, int nz, int zb)
     {
         typedef TilePlan<T_LOG, G_HI, A> TP;
         const int y = blockIdx.y, mod = mm.mod(y);
@@ -172,30 +184,32 @@ namespace gsb
                 int zn = z + 1;
                 while (zn < z1 && io.skip(y, zn))
                     zn++;
-#if GSB_PREFETCH
-                if (zn < z1)
+                if constexpr (TileTuning<IO>::prefetch)
                 {
-                    const typename IO::Pro pro(io, y, zn, mod, c, N);
-                    xf_load_raw<T_LOG, G_HI, G_LO, INVERSE>(xn, tid, tile, map, pro);
+                    if (zn < z1)
+                    {
+                        const typename IO::Pro pro(io, y, zn, mod, c, N);
+                        xf_load_raw<T_LOG, G_HI, G_LO, INVERSE>(xn, tid, tile, map, pro);
+                    }
                 }
-#endif
                 const typename IO::Epi epi(io, y, z, mod, c, N);
                 if constexpr (has_prefetch<typename IO::Epi>::value)
                     xf_prefetch<T_LOG, G_HI, G_LO, INVERSE>(tid, tile, map, epi);
                 if constexpr (INVERSE)
                     inv_compute<T_LOG, G_HI, G_LO, LAST, 0, FAST>(x, smem, tid, tw, c, parity);
                 else if constexpr (FAST)
-                    fwd_compute<T_LOG, G_HI, G_LO, LAST, 0, GSB_TILE_FWD_FORM>(x, smem, tid, TwPreshifted<std::decay_t<decltype(tw)>>{ tw }, c, parity);
+                    fwd_compute<T_LOG, G_HI, G_LO, LAST, 0, TileTuning<IO>::fwd_form>(x, smem, tid, TwPreshifted<std::decay_t<decltype(tw)>>{ tw }, c, parity);
                 else
                     fwd_compute<T_LOG, G_HI, G_LO, LAST, 0, false>(x, smem, tid, tw, c, parity);
                 xf_store<T_LOG, G_HI, G_LO, INVERSE>(x, tid, tile, map, epi);
-#if !GSB_PREFETCH
-                if (zn < z1)
+                if constexpr (!TileTuning<IO>::prefetch)
                 {
-                    const typename IO::Pro pro(io, y, zn, mod, c, N);
-                    xf_load_raw<T_LOG, G_HI, G_LO, INVERSE>(xn, tid, tile, map, pro);
+                    if (zn < z1)
+                    {
+                        const typename IO::Pro pro(io, y, zn, mod, c, N);
+                        xf_load_raw<T_LOG, G_HI, G_LO, INVERSE>(xn, tid, tile, map, pro);
+                    }
                 }
-#endif
                 z = zn;
             }
         };
