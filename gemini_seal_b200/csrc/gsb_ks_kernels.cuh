@@ -604,7 +604,11 @@ namespace gsb
     struct MacPlan
     {
         static constexpr bool two_pass = Split<LOGN>::two_pass;
-        static constexpr int T = two_pass ? 8 : Split<LOGN>::T1;
+#ifndef GSB_MAC_T
+#define GSB_MAC_T 7 // log2(threads) of a two-pass ks_mac CTA (tile = 8 << T words): measured 3.10 ms at 7, 3.14 at 6, 3.22 at 8
+#endif
+        static constexpr int T = two_pass ? GSB_MAC_T : Split<LOGN>::T1;
+        static constexpr int min_ctas = T > 8 ? 1 : T == 8 ? 2 : T == 7 ? 4 : 8; // 512 resident threads per SM
         static constexpr int G_HI = two_pass ? LOGN - Split<LOGN>::A - 1 : LOGN - 1;
         typedef TilePlan<T, G_HI, 0> TP;
         static constexpr uint32_t TILE = 8u << T;
@@ -633,7 +637,7 @@ namespace gsb
 #define GSB_MAC_FWD_FORM 3 // fwd_round's FAST form for the operand transform: measured 3.22 ms for D3 (3), 3.34 plain (1), 3.47 H3 + D3 (4), 3.56 H3 (2), 3.32 D3 + EARLY (7)
 #endif
     template <int LOGN, bool K1, bool LAZY, int FORM = GSB_MAC_FWD_FORM>
-    __global__ void __launch_bounds__(1 << MacPlan<LOGN>::T, MacPlan<LOGN>::T <= 8 ? 2 : 1) ks_mac_kernel(KsMacArgs p, NttTables tab)
+    __global__ void __launch_bounds__(1 << MacPlan<LOGN>::T, MacPlan<LOGN>::min_ctas) ks_mac_kernel(KsMacArgs p, NttTables tab)
     {
         typedef MacPlan<LOGN> MP;
         typedef typename MP::TP TP;

@@ -127,6 +127,11 @@ namespace gsb
     // registers before the butterflies of z (16 more live registers).  Default 2 CTAs + prefetch; an IO type may
     // specialise it (the mod-up column pass runs 3 CTAs of 80 registers without prefetch: measured 1.76 vs 1.82 ms,
     // while the same setting costs the contiguous passes 3 %).
+    // min_ctas is quoted for 256-thread CTAs; smaller CTAs keep the same number of resident threads
+    __host__ __device__ constexpr int tile_min_ctas(int t_log, int per256)
+    {
+        return t_log > 8 ? 1 : t_log == 8 ? per256 : t_log == 7 ? 2 * per256 : 4 * per256;
+    }
     template <class IO>
     struct TileTuning
     {
@@ -136,7 +141,7 @@ namespace gsb
     };
 
     template <bool INVERSE, int T_LOG, int G_HI, int G_LO, bool LAST, int A, class IO, bool FAST = false>
-    __global__ void __launch_bounds__(1 << T_LOG, T_LOG <= 8 ? TileTuning<IO>::min_ctas : 1) ntt_tile_kernel(IO io, NttTables tab, ModMap mm, int nz, int zb)
+    __global__ void __launch_bounds__(1 << T_LOG, tile_min_ctas(T_LOG, TileTuning<IO>::min_ctas)) ntt_tile_kernel(IO io, NttTables tab, ModMap mm, int nz, int zb)
     {
         typedef TilePlan<T_LOG, G_HI, A> TP;
         const int y = blockIdx.y, mod = mm.mod(y);
@@ -240,14 +245,24 @@ namespace gsb
     }
 
     // Two-pass split for a given log2(N): A = log2(rows) of the column pass, TC = T_LOG of the
-    // column pass.  The contiguous pass always uses 2048-word tiles (T_LOG = 8).  A is chosen so the
+    // column pass.  The contiguous pass uses (8 << GSB_CONTIG_T)-word tiles.  A is chosen so the
     // two passes need as few register rounds (<= 3 stages each) as possible.
+    // log2(threads) of the CTAs of a two-pass transform (tile = 8 << T words).  128-thread CTAs (twice as many resident)
+    // measured 3-8 % faster than 256-thread ones in every pass: a barrier or an mbarrier wait holds 4 warps, not 8
+    // (step 6.53 -> 6.44 ms; 64-thread CTAs gain nothing more).
+#ifndef GSB_COLS_T
+#define GSB_COLS_T 7
+#endif
+#ifndef GSB_CONTIG_T
+#define GSB_CONTIG_T 7
+#endif
     template <int LOGN>
     struct Split
     {
         static constexpr bool two_pass = LOGN >= 13;
         static constexpr int A = LOGN == 13 ? 6 : LOGN == 14 ? 6 : LOGN == 15 ? 6 : 8;
-        static constexpr int TC = LOGN == 16 ? 9 : 8;
+        static constexpr int TC = LOGN == 16 ? 9 : GSB_COLS_T;
+        static constexpr int TK = GSB_CONTIG_T; // T_LOG of the contiguous pass of a two-pass transform
         static constexpr int T1 = LOGN - 3; // single-pass T_LOG
     };
 
@@ -310,7 +325,7 @@ namespace gsb
     {
         using SP = Split<LOGN>;
         if constexpr (SP::two_pass)
-            launch_tile<false, 8, LOGN - SP::A - 1, 0, true, 0, FAST>("fwd_contig", tag, io, tab, mm, 1u << (LOGN - 11), ny, nz, st);
+            launch_tile<false, SP::TK, LOGN - SP::A - 1, 0, true, 0, FAST>("fwd_contig", tag, io, tab, mm, 1u << (LOGN - SP::TK - 3), ny, nz, st);
         else
             launch_tile<false, SP::T1, LOGN - 1, 0, true, 0, FAST>("fwd_contig", tag, io, tab, mm, 1u, ny, nz, st);
     }
@@ -322,7 +337,7 @@ namespace gsb
     {
         using SP = Split<LOGN>;
         if constexpr (SP::two_pass)
-            launch_tile<true, 8, LOGN - SP::A - 1, 0, false, 0, FAST>("inv_contig", tag, io, tab, mm, 1u << (LOGN - 11), ny, nz, st);
+            launch_tile<true, SP::TK, LOGN - SP::A - 1, 0, false, 0, FAST>("inv_contig", tag, io, tab, mm, 1u << (LOGN - SP::TK - 3), ny, nz, st);
         else
             launch_tile<true, SP::T1, LOGN - 1, 0, true, 0, FAST>("inv_contig", tag, io, tab, mm, 1u, ny, nz, st);
     }
