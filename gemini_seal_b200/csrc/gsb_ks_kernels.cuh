@@ -165,18 +165,6 @@ namespace gsb
         {}
     };
 
-    // the k = 1 mod-up column pass: 3 resident CTAs, no register prefetch (TileTuning)
-    template <bool LAZY, class EpiF>
-    struct TileTuning<IoPair<ModupLoadT<true, LAZY>, EpiF>>
-    {
-        static constexpr int min_ctas = 3;
-        static constexpr bool prefetch = false;
-#ifndef GSB_MODUP_FWD_FORM
-#define GSB_MODUP_FWD_FORM 7
-#endif
-        static constexpr int fwd_form = GSB_MODUP_FWD_FORM;
-    };
-
     // ---- mod-down prologue (rescale_special_rns_inplace steps 1-2, multi_special_primes.cpp:253-282)
     // grid: y = ciphertext limb i, z = b*2 + l.  red = [B*2][E][N]; its special slots hold the lazy
     // inverse NTT of the reduced accumulators (evaluator.cpp:2353-2357).

@@ -123,10 +123,10 @@ namespace gsb
 #ifndef GSB_TILE_FWD_FORM
 #define GSB_TILE_FWD_FORM 7 // which sums of the wide-range forward butterfly are forced onto the ALU pipe (fwd_round)
 #endif
-    // Per-IO tuning: resident CTAs per SM the register allocation aims at, and whether polynomial z+1 is loaded into
-    // registers before the butterflies of z (16 more live registers).  Default 2 CTAs + prefetch; an IO type may
-    // specialise it (the mod-up column pass runs 3 CTAs of 80 registers without prefetch: measured 1.76 vs 1.82 ms,
-    // while the same setting costs the contiguous passes 3 %).
+    // Per-IO tuning: resident CTAs per SM the register allocation aims at (per 256 threads), whether polynomial z+1 is
+    // loaded into registers before the butterflies of z (16 more live registers), and the butterfly form.  An IO type
+    // may specialise it; none does at present (with 256-thread CTAs the mod-up column pass was faster at 3 CTAs of 80
+    // registers without prefetch, 1.76 vs 1.82 ms; with 128-thread CTAs the default is faster again, 1.73 ms).
     // min_ctas is quoted for 256-thread CTAs; smaller CTAs keep the same number of resident threads
     __host__ __device__ constexpr int tile_min_ctas(int t_log, int per256)
     {
@@ -286,12 +286,15 @@ namespace gsb
 #endif
     }
 
+#ifndef GSB_ZB_MAX
+#define GSB_ZB_MAX 8
+#endif
     // polynomials per CTA: enough CTAs left for ~8 waves of (SMs x 3 resident CTAs)
     inline int pick_zb(size_t ctas_per_z, int nz)
     {
         const size_t want = sm_count() * 3 * 8;
         size_t zb = (ctas_per_z * static_cast<size_t>(nz)) / want;
-        zb = zb < 1 ? 1 : zb > 8 ? 8 : zb;
+        zb = zb < 1 ? 1 : zb > GSB_ZB_MAX ? GSB_ZB_MAX : zb;
         return static_cast<int>(zb);
     }
 
