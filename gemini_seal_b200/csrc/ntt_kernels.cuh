@@ -177,14 +177,16 @@ namespace gsb
                 __syncthreads();
             }
             int parity = 0;
-            while (z < z1)
-            {
+            // One polynomial: `xc` holds its raw words, `xo` receives the next polynomial's.  The loop below calls it
+            // with the two buffers swapped every other time, so the prefetched words are used where they landed
+            // (a single buffer costs 16 register moves per polynomial on the multiplier pipe).
+            auto one = [&](uint64_t (&xc)[8], uint64_t (&xo)[8]) {
                 uint64_t x[8];
                 {
                     const typename IO::Pro pro(io, y, z, mod, c, N);
 #pragma unroll
                     for (int i = 0; i < 8; i++)
-                        x[i] = pro.xform(xn[i]);
+                        x[i] = pro.xform(xc[i]);
                 }
                 int zn = z + 1;
                 while (zn < z1 && io.skip(y, zn))
@@ -194,7 +196,7 @@ namespace gsb
                     if (zn < z1)
                     {
                         const typename IO::Pro pro(io, y, zn, mod, c, N);
-                        xf_load_raw<T_LOG, G_HI, G_LO, INVERSE>(xn, tid, tile, map, pro);
+                        xf_load_raw<T_LOG, G_HI, G_LO, INVERSE>(xo, tid, tile, map, pro);
                     }
                 }
                 const typename IO::Epi epi(io, y, z, mod, c, N);
@@ -212,10 +214,18 @@ namespace gsb
                     if (zn < z1)
                     {
                         const typename IO::Pro pro(io, y, zn, mod, c, N);
-                        xf_load_raw<T_LOG, G_HI, G_LO, INVERSE>(xn, tid, tile, map, pro);
+                        xf_load_raw<T_LOG, G_HI, G_LO, INVERSE>(xo, tid, tile, map, pro);
                     }
                 }
                 z = zn;
+            };
+            uint64_t xm[8];
+            while (z < z1)
+            {
+                one(xn, xm);
+                if (z >= z1)
+                    break;
+                one(xm, xn);
             }
         };
         if constexpr (TP::COLS)
