@@ -10,7 +10,9 @@ for k,v in d["extra"]["ntt_sweep"].items(): print(k, round(v["limb_ntt_per_s"]/1
 print(d["extra"]["bfv_n4096"])
 PY
 ncu --metrics gpu__time_duration.sum --clock-control none --profile-from-start off --csv --log-file gpurun_out/r2_launches_step.csv python scripts/prof_step.py > /dev/null 2>&1
-ncu --set full --clock-control none --import-source on --profile-from-start off -o gpurun_out/r2_step_full python scripts/prof_step.py > gpurun_out/r2_step_full.log 2>&1; tail -1 gpurun_out/r2_step_full.log
+if [ "$1" = "full" ]; then
+ncu --set full --clock-control none --import-source on --profile-from-start off -o gpurun_out/r2_step_full python scripts/prof_step.py > gpurun_out/r2_step_full.log 2>&1; tail -1 gpurun_out/r2_step_full.log; ls -la gpurun_out/
+fi
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/r2_launches_bench.csv python bench.py --steps 2 --warmup 3 --no-cpu-baseline --sustain-s 0 > /dev/null 2>&1
 scripts/_C/pipes.bin > gpurun_out/r2_pipes.txt
 python scripts/int_peak.py > gpurun_out/r2_int_peak.txt

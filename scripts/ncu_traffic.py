@@ -11,7 +11,8 @@ import sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 rep, batch = sys.argv[1], int(sys.argv[2])
 tag = sys.argv[3] if len(sys.argv) > 3 else "r2"
-raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+# a .csv argument is the `ncu -i <rep> --page raw --csv` export itself (a report over 64 MiB does not travel back from the GPU box)
+raw = open(rep).read() if rep.endswith('.csv') else subprocess.run(['ncu', '-i', rep, '--page', 'raw', '--csv'], capture_output=True, text=True).stdout
 rows = list(csv.reader(raw.splitlines()))
 hdr, units = rows[0], rows[1]
 
