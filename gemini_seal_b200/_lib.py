@@ -90,6 +90,7 @@ PROTOTYPES = {
     "gsb_bfv_decrypt_host": (i32, [vp, u64, vp, vp, sz, sz, sz]),
     "gsb_rescale_noalloc_dev": (i32, [vp, vp, vp, sz, sz, sz, vp]),
     "gsb_ctx_fast_ntt": (i32, [vp]),
+    "gsb_ctx_shortcuts": (i32, [vp]),
 }
 # symbols that the test-only simulator build does not provide
 CUDA_ONLY = {"gsb_rescale_noalloc_dev"}  # static __device__ scratch: CUDA build only

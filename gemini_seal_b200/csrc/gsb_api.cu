@@ -554,6 +554,14 @@ int gsb_ctx_fast_ntt(const gsb_ctx *ctx)
     return ctx != nullptr && ctx->fast_ntt ? 1 : 0;
 }
 
+int gsb_ctx_shortcuts(const gsb_ctx *ctx)
+{
+    if (ctx == nullptr)
+        return 0;
+    return (ctx->fast_ntt ? 1 : 0) | (ctx->lazy_modup ? 2 : 0) | (ctx->lazy_mac ? 4 : 0) | (ctx->wide_inv ? 8 : 0) |
+           (ctx->fast_fwd_public ? 16 : 0);
+}
+
 } // extern "C"
 
 #include "gsb_evaluator.cuh"

@@ -300,6 +300,10 @@ int gsb_rescale_noalloc_dev(gsb_ctx *ctx, const uint64_t *in, uint64_t *out, siz
 int gsb_ctx_fast_ntt(const gsb_ctx *ctx);
 /* Testing aid: a context created while the environment variable GSB_LITERAL is "1" takes none of those
  * shortcuts (gsb_ctx_fast_ntt returns 0); outputs are identical either way. */
+/* Which congruent-word shortcuts the context's bounds allow (no reference counterpart, outputs are
+ * identical with any of them on or off): bit 0 fast_ntt, 1 lazy_modup, 2 lazy_mac, 3 wide_inv, 4 fast_fwd_public.
+ * 0 for a null context. */
+int gsb_ctx_shortcuts(const gsb_ctx *ctx);
 
 #ifdef __cplusplus
 }

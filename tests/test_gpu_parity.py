@@ -238,6 +238,8 @@ def test_full_size_shortcuts_equal_literal(cudalib):
         finally:
             os.environ.pop("GSB_LITERAL", None)
         assert cudalib.gsb_ctx_fast_ntt(ctx.handle) == (0 if literal else 1)
+        # the headline configuration runs every shortcut (a bound that silently stops holding would cost speed, not parity)
+        assert cudalib.gsb_ctx_shortcuts(ctx.handle) == (0 if literal else 31)
         ctx.set_relin_keys(relin)
         elt = ctx.galois_elt_from_step(1)
         ctx.set_galois_key(elt, gal)

@@ -50,9 +50,12 @@ def test_sim_fast_flag_and_literal_mode(simlib, oracle):
     import gemini_seal_b200 as g
     from common import mixed_moduli, rand_key, rand_poly
     logn, N = 11, 2048
-    for bits, want in (([56, 55, 56, 56], 1), ([57, 55, 56, 56], 1), ([58, 55, 56, 56], 0), ([59, 58, 59, 59], 0)):
+    # gsb_ctx_shortcuts: bit 0 fast_ntt, 1 lazy_modup, 2 lazy_mac, 3 wide_inv, 4 fast_fwd_public
+    for bits, want, mask in (([56, 55, 56, 56], 1, 31), ([57, 55, 56, 56], 1, 31), ([58, 55, 56, 56], 0, 8), ([59, 58, 59, 59], 0, 8),
+                             ([60, 58, 59, 59], 0, 0)):
         ctx = g.Context(N, mixed_moduli(logn, bits), 1, lib=simlib)
         assert simlib.gsb_ctx_fast_ntt(ctx.handle) == want, bits
+        assert simlib.gsb_ctx_shortcuts(ctx.handle) == mask, (bits, simlib.gsb_ctx_shortcuts(ctx.handle))
         ctx.close()
     mods = mixed_moduli(logn, [50, 40, 45, 51])
     rng = np.random.default_rng(3)
@@ -67,6 +70,7 @@ def test_sim_fast_flag_and_literal_mode(simlib, oracle):
         finally:
             os.environ.pop("GSB_LITERAL", None)
         assert simlib.gsb_ctx_fast_ntt(ctx.handle) == (0 if literal else 1)
+        assert simlib.gsb_ctx_shortcuts(ctx.handle) == (0 if literal else 31)
         ctx.set_relin_keys(relin)
         outs.append(g.Evaluator(ctx).mul_relin_rescale(a, b))
         ctx.close()
