@@ -2,8 +2,8 @@
 //
 //   N <= 2^12 : one pass, the whole limb is one tile (8T = N words, <= 32 KiB).
 //   N >= 2^13 : two passes through L2/HBM.  Forward = column pass (stages with gaps >= N >> A on
-//               2^A x 2^C strided tiles) then contiguous pass (remaining stages on 2048-word
-//               tiles); inverse = contiguous pass then column pass.
+//               2^A x 2^C strided tiles) then contiguous pass (remaining stages on (8 << GSB_CONTIG_T)-word
+//               tiles, 1024 words by default); inverse = contiguous pass then column pass.
 // grid = (tiles per limb, limb slots, polys); the IO policy turns (y, z, coefficient) into memory.
 #pragma once
 #include "ntt_core.cuh"
