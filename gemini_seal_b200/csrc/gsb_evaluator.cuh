@@ -283,7 +283,7 @@ namespace gsb
     static size_t ks_words_per_ct(const gsb_ctx *ctx, size_t L)
     {
         const size_t N = ctx->N, E = L + ctx->k, beta = (L + ctx->k - 1) / ctx->k;
-        const bool two = ctx->logn >= 13;
+        const bool two = ctx->logn >= GSB_TWO_PASS_MIN;
         return L * N + (two ? beta * E * N : 0) + 2 * E * N + (two ? 2 * L * N : 0);
     }
 

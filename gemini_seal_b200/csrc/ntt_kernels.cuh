@@ -1,7 +1,7 @@
 // __global__ wrappers around ntt_core.cuh and the per-N launch plans.
 //
-//   N <= 2^12 : one pass, the whole limb is one tile (8T = N words, <= 32 KiB).
-//   N >= 2^13 : two passes through L2/HBM.  Forward = column pass (stages with gaps >= N >> A on
+//   N <= 2^11 : one pass, the whole limb is one tile (8T = N words).
+//   N >= 2^12 : two passes (GSB_TWO_PASS_MIN) through L2/HBM.  Forward = column pass (stages with gaps >= N >> A on
 //               2^A x 2^C strided tiles) then contiguous pass (remaining stages on (8 << GSB_CONTIG_T)-word
 //               tiles, 1024 words by default); inverse = contiguous pass then column pass.
 // grid = (tiles per limb, limb slots, polys); the IO policy turns (y, z, coefficient) into memory.
@@ -263,14 +263,17 @@ namespace gsb
 #ifndef GSB_COLS_T
 #define GSB_COLS_T 7
 #endif
+#ifndef GSB_TWO_PASS_MIN
+#define GSB_TWO_PASS_MIN 12 // smallest log2 N that runs as two passes (smaller limbs are one tile of N words); 12: +5 % strict NTT, +9 % BFV multiply at N = 4096 over the single 512-thread CTA per limb
+#endif
 #ifndef GSB_CONTIG_T
 #define GSB_CONTIG_T 7
 #endif
     template <int LOGN>
     struct Split
     {
-        static constexpr bool two_pass = LOGN >= 13;
-        static constexpr int A = LOGN == 13 ? 6 : LOGN == 14 ? 6 : LOGN == 15 ? 6 : 8;
+        static constexpr bool two_pass = LOGN >= GSB_TWO_PASS_MIN;
+        static constexpr int A = LOGN <= 12 ? 3 : LOGN == 13 ? 6 : LOGN == 14 ? 6 : LOGN == 15 ? 6 : 8;
         static constexpr int TC = LOGN == 16 ? 9 : GSB_COLS_T;
         static constexpr int TK = GSB_CONTIG_T; // T_LOG of the contiguous pass of a two-pass transform
         static constexpr int T1 = LOGN - 3; // single-pass T_LOG
