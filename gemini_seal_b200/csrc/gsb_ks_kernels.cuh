@@ -836,6 +836,16 @@ namespace gsb
         const LimbC *limb;
         uint32_t N, L;
         size_t pairs; // B*L*N/2
+        // word w of the batch is limb (w >> logn) % L of ciphertext (w >> logn) / L: a shift and a multiply by
+        // l_magic = ceil(2^32 / L) (0 for L = 1; exact while (B L) L < 2^32) instead of two 64-bit divisions per pair
+        uint32_t logn, l_magic;
+        CkksMulArgs(const uint64_t *a_, const uint64_t *b_, uint64_t *out_, const LimbC *limb_, uint32_t N_, uint32_t L_, size_t pairs_)
+            : a(a_), b(b_), out(out_), limb(limb_), N(N_), L(L_), pairs(pairs_), logn(0),
+              l_magic(L_ > 1 ? static_cast<uint32_t>(((uint64_t(1) << 32) + L_ - 1) / L_) : 0u)
+        {
+            while ((1u << logn) < N_)
+                logn++;
+        }
     };
 
     // FASTRED: operands are canonical residues and the limb has c.mu (every modulus of <= 60 bits): the
@@ -865,8 +875,10 @@ namespace gsb
              i += static_cast<size_t>(gridDim.x) * blockDim.x)
         {
             const size_t w = i << 1;
-            const size_t ct = w / LN, rem = w - ct * LN;
-            const LimbC c = p.limb[rem / p.N];
+            const uint32_t row = static_cast<uint32_t>(w >> p.logn); // ct * L + limb
+            const uint32_t ct32 = p.l_magic ? __umulhi(row, p.l_magic) : row;
+            const size_t ct = ct32, rem = w - ct * LN;
+            const LimbC c = p.limb[row - ct32 * p.L];
             const uint64_t *pa = p.a + ct * 2 * LN + rem, *pb = p.b + ct * 2 * LN + rem;
             uint64_t *po = p.out + ct * 3 * LN + rem;
             const ulonglong2 a0 = *reinterpret_cast<const ulonglong2 *>(pa), a1 = *reinterpret_cast<const ulonglong2 *>(pa + LN);
