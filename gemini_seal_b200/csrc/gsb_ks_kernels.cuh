@@ -475,7 +475,7 @@ namespace gsb
         for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < a.total;
              i += static_cast<size_t>(gridDim.x) * blockDim.x)
         {
-            const size_t z = i / a.N, d = i - z * a.N;
+            const size_t z = i >> (31 - __clz(a.N)), d = i & (a.N - 1); // N is a power of two
             uint64_t *pu = a.buf + (z * 2) * a.N + d, *ps = pu + a.N;
             const uint64_t s = *ps;
             GSB_SIM_ASSERT(s < a.sp.two_q && *pu < a.last.two_q);
@@ -954,7 +954,9 @@ namespace gsb
         for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < p.total;
              i += static_cast<size_t>(gridDim.x) * blockDim.x)
         {
-            const size_t z = i / LN, rem = i - z * LN;
+            // N is a power of two: row = z * L + limb by a shift, z by one 32-bit division (not two 64-bit ones)
+            const uint32_t row = static_cast<uint32_t>(i >> (31 - __clz(p.N))), zz = row / p.L;
+            const size_t z = zz, rem = i - z * LN;
             const uint32_t d = static_cast<uint32_t>(rem & (p.N - 1));
             p.out[i] = p.in[z * p.in_zs + (rem - d) + __ldg(p.table + d)];
         }

@@ -164,6 +164,10 @@ namespace cusim
 #define gridDim (::cusim::S().grid)
 #define __syncthreads() ::cusim::syncthreads()
 
+static inline int __clz(int x)
+{
+    return x == 0 ? 32 : __builtin_clz(static_cast<unsigned int>(x));
+}
 static inline unsigned int __umulhi(unsigned int a, unsigned int b)
 {
     return static_cast<unsigned int>((static_cast<unsigned long long>(a) * b) >> 32);
